@@ -1,0 +1,191 @@
+/*
+ * kirstine_b200.h -- C ABI of the B200 engine behind Kirstine.jl's design-objective hot path.
+ *
+ * The reference (lsandig/Kirstine.jl v0.5.0) is pure Julia and has no FFI; its plugin surface
+ * is Julia multiple dispatch.  Each entry point below names the reference function(s) it
+ * stands in for (paths relative to the reference checkout).  INTEGRATION.md shows the ccall
+ * stubs a Kirstine maintainer would add, and the ctypes binding used by this repo's tests.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative KST_E* code otherwise;
+ *    kst_last_error() returns a thread-local message for the last failure;
+ *  - no exceptions, Julia or Python objects cross the boundary; the caller owns every buffer
+ *    it passes, the handle owns all device memory, streams and (optionally) one communicator;
+ *  - one handle drives ONE GPU; a handle is single-threaded like the reference's Workspaces;
+ *  - all floating point is IEEE double; matrices are column-major like Julia's Matrix{Float64};
+ *  - "points" of a design measure are d x K column-major (DesignMeasure.points,
+ *    src/designmeasure.jl:19-42), i.e. point k occupies points[k*d .. k*d+d-1];
+ *  - there is no CPU fallback: every entry point needs a CUDA device.
+ */
+#ifndef KIRSTINE_B200_H
+#define KIRSTINE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KST_VERSION 100
+
+#if defined(__GNUC__)
+#define KST_API __attribute__((visibility("default")))
+#else
+#define KST_API
+#endif
+
+/* error codes */
+#define KST_OK 0
+#define KST_EINVAL (-1)   /* bad argument / unsupported combination */
+#define KST_ECUDA (-2)    /* CUDA runtime failure (message has the cudaError string) */
+#define KST_ENOMEM (-3)
+#define KST_ESTATE (-4)   /* call order violated (e.g. gateaux_eval before gateaux_prepare) */
+#define KST_ENCCL (-5)    /* NCCL unavailable or failed */
+#define KST_ELIMIT (-6)   /* size beyond a documented fixed limit */
+
+/* Registered model families = device functors standing in for the user's jacobianmatrix!,
+ * update_model_vcov!, unit_length, dimension (src/user.jl:18-98).  The reference ships no
+ * concrete models; these restate its test/doc models:
+ *   KST_MODEL_EMAX     test/example-emax.jl:4-47         params {sigma_squared},  theta = (e0, emax, ec50)
+ *   KST_MODEL_SIGEMAX  docs/src/tutorial.md:107-142      params {sigma},          theta = (e0, emax, ed50, h)
+ *   KST_MODEL_TPC      test/example-compartment.jl:10-21 params {sigma},          theta = (a, e, s)
+ *   KST_MODEL_VU       test/example-vector.jl:9-41       params {sigma_squared},  theta = (a, e, s), unit length m
+ * Unregistered model types must keep using stock Kirstine. */
+#define KST_MODEL_EMAX 1
+#define KST_MODEL_SIGEMAX 2
+#define KST_MODEL_TPC 3
+#define KST_MODEL_VU 4
+
+/* covariate parameterizations = map_to_covariate! (src/user.jl:68):
+ *   KST_CP_COPY      CopyDose / CopyTime / JustCopy: covariate = design point (src/user.jl:185-216)
+ *   KST_CP_EQUITIME  EquiTime (test/example-vector.jl:45-50): time_i = (i-1) * z[1], i = 1..m */
+#define KST_CP_COPY 0
+#define KST_CP_EQUITIME 1
+
+#define KST_CRIT_D 0 /* DCriterion, src/criterion-d.jl:29 */
+#define KST_CRIT_A 1 /* ACriterion, src/criterion-a.jl:29 */
+
+#define KST_TRAFO_IDENTITY 0 /* Identity,    src/transformation.jl:11 */
+#define KST_TRAFO_DELTA 1    /* DeltaMethod, src/transformation.jl:59-61 */
+
+#define KST_PSO_MODE_OBJECTIVE 0 /* particles are K-point designs, f = objective!        */
+#define KST_PSO_MODE_GATEAUX 1   /* particles are one-point designs, f = gateauxderivative! */
+
+/* fixed limits of this build */
+#define KST_MAX_R 5      /* parameter dimension */
+#define KST_MAX_D 4      /* design-region dimension */
+#define KST_MAX_UNIT 16  /* unit length m */
+#define KST_MAX_ROWS 128 /* K * m per design measure */
+
+typedef struct kst_problem kst_problem;
+
+KST_API const char *kst_last_error(void);
+KST_API int kst_version(void);
+
+/* Number of visible CUDA devices (0 if none). */
+KST_API int kst_device_count(int *count);
+
+/*
+ * DesignProblem (src/designproblem.jl:22-79) restricted to what the hot path reads: model,
+ * covariate parameterization, criterion, transformation, prior sample, design region.
+ * Replaces allocate_workspaces (src/designproblem.jl:130-138) and trafo_constants
+ * (src/transformation.jl:71-92): the caller evaluates DeltaMethod's Jacobian on the host for
+ * every draw (arbitrary user closure) and passes the result.
+ *
+ *  theta    N*r doubles, array-of-structs exactly like Julia's Vector{P} of isbits parameter
+ *           structs (PriorSample.p, src/priorknowledge.jl:11-38); transposed to SoA on upload
+ *  prior_w  N prior weights (PriorSample.weight)
+ *  dt_jm    N*(t*r) doubles, per draw one column-major t x r Matrix{Float64}
+ *           (TCDeltaMethod.jm, src/transformation.jl:67-69); NULL for KST_TRAFO_IDENTITY
+ *  t        codomain dimension (== r for identity)
+ *  lb, ub   d lower / upper bounds of the DesignInterval (src/designregion.jl:22-51)
+ *
+ * With several GPUs each process passes only ITS shard of (theta, prior_w, dt_jm); see
+ * kst_comm_init.
+ */
+KST_API int kst_problem_create(int model_id, const double *model_params, int n_model_params, int cp_id,
+                       int criterion_id, int trafo_id, int r, int t, int m, int d, int64_t N,
+                       const double *theta, const double *prior_w, const double *dt_jm,
+                       const double *lb, const double *ub, int device_id, kst_problem **out);
+KST_API int kst_problem_destroy(kst_problem *h);
+
+/*
+ * Multi-GPU: the prior sample is sharded over processes (one per GPU); per swarm evaluation the
+ * S partial objectives are summed with one ncclAllReduce (double, sum) on the handle's stream.
+ * The reference has no counterpart (it is serial: src/pso.jl:173-179, src/designproblem.jl:205-215).
+ * kst_comm_unique_id fills a 128-byte ncclUniqueId on rank 0; the host broadcasts it by any
+ * means (torch.distributed, MPI, a file) and every rank calls kst_comm_init.  NCCL is loaded
+ * with dlopen("libnccl.so.2") on first use, so single-GPU users need no NCCL.
+ */
+KST_API int kst_comm_unique_id(void *id128);
+KST_API int kst_comm_init(kst_problem *h, int nranks, int rank, const void *id128);
+
+/*
+ * pso_evaluate_objective! (src/pso.jl:173-179) calling objective! (src/designproblem.jl:192-224)
+ * for S design measures of K points each, all at once.
+ *  points   S*K*d doubles (per particle d x K column-major), weights S*K, fx S (out).
+ * fx is -Inf where the reference returns -Inf (PosDefException / SingularException / log_det!
+ * of a singular matrix); NaN propagates like in the reference (e.g. prior weight 0 on a
+ * singular draw).  Host-buffer variant: copies in, evaluates, all-reduces if a communicator is
+ * attached, copies out, synchronises.
+ */
+KST_API int kst_objective_batch(kst_problem *h, int S, int K, const double *points, const double *weights,
+                        double *fx);
+/* Same with buffers already in device memory of the handle's GPU; asynchronous on the handle's
+ * stream (kst_stream_synchronize waits). */
+KST_API int kst_objective_batch_device(kst_problem *h, int S, int K, const double *d_points,
+                               const double *d_weights, double *d_fx);
+KST_API int kst_stream_synchronize(kst_problem *h);
+/* The handle's cudaStream_t, for callers that enqueue their own work or copies in order. */
+KST_API void *kst_stream(kst_problem *h);
+
+/* informationmatrix (src/design-common.jl:96-112) for draw `draw_index` (0-based) of the prior
+ * sample: full symmetric r x r matrix. */
+KST_API int kst_informationmatrix(kst_problem *h, int K, const double *points, const double *weights,
+                          int64_t draw_index, double *M);
+
+/*
+ * gateaux_constants (src/criterion-d.jl:43-87, src/criterion-a.jl:47-77) at design `at`; the
+ * constants stay on the device.  *singular = 1 where the reference throws SingularException
+ * (then kst_gateaux_eval fills NaN like gateauxderivative, src/designproblem.jl:281-284).
+ */
+KST_API int kst_gateaux_prepare(kst_problem *h, int K, const double *points, const double *weights,
+                        int *singular);
+/* GCPriorSample copy-out (src/design-common.jl:29-32): A = N*(r*r) column-major dense, trB = N. */
+KST_API int kst_gateaux_constants(kst_problem *h, double *A, double *tr_B);
+/* gateauxderivative! (src/designproblem.jl:239-258) for G one-point directions dirs[G*d]. */
+KST_API int kst_gateaux_eval(kst_problem *h, int64_t G, const double *dirs, double *gd);
+
+/*
+ * optimizer_state (src/pso.jl:83-125): particle i < P is prototype i, the others are prototype
+ * 0 randomised by ap_rand! (src/designmeasure-abstractpoint.jl:73-107); v = 0; evaluate; best.
+ * fixw / fixp: DesignConstraints (src/designmeasure-abstractpoint.jl:23-58), K ints each.
+ * *status: 0 ok, 1 "infinite objective value at best initial point", 2 "objective evaluates to
+ * NaN on all initial points" (the reference's two ErrorExceptions).
+ * The swarm lives on the device from here on.
+ */
+KST_API int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, const double *proto_points,
+                 const double *proto_weights, int P, const int *fixw, const int *fixp,
+                 uint64_t seed, int mode, int *status);
+/*
+ * n_iters times tick! (src/pso.jl:127-141).  trace_fx[n_iters], trace_points[n_iters*K*d],
+ * trace_weights[n_iters*K] receive maximum/maximizer after each tick (optimize's trace_fx /
+ * trace_x, src/optimize.jl:54-57); any of them may be NULL.
+ */
+KST_API int kst_pso_run(kst_problem *h, int n_iters, double *trace_fx, double *trace_points,
+                double *trace_weights);
+/* PsoState copy-out (src/pso.jl:63-76), what trace_state = true deep-copies; NULL skips. */
+KST_API int kst_pso_get_state(kst_problem *h, double *x_points, double *x_weights, double *p_points,
+                      double *p_weights, double *g_points, double *g_weights, double *v_points,
+                      double *v_weights, double *fx, double *fp, double *fg, int64_t *n_eval);
+
+/* measurement helpers (bench.py): CUDA-event timing of the evaluation kernel on the handle's
+ * stream, and a DFMA micro-kernel that measures this GPU's FP64 pipe peak. */
+KST_API int kst_profile_enable(kst_problem *h, int on);
+KST_API int kst_profile_read(kst_problem *h, double *total_ms, int64_t *launches);
+KST_API int kst_fp64_peak_probe(int device_id, double *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,252 @@
+"""ctypes binding of libkirstine_b200.so (include/kirstine_b200.h).
+
+There is no CPU fallback: loading fails loudly when the library has not been built, and every
+compute call fails loudly when no CUDA device is present.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libkirstine_b200.so")
+
+MODEL_EMAX, MODEL_SIGEMAX, MODEL_TPC, MODEL_VU = 1, 2, 3, 4
+CP_COPY, CP_EQUITIME = 0, 1
+CRIT_D, CRIT_A = 0, 1
+TRAFO_IDENTITY, TRAFO_DELTA = 0, 1
+PSO_MODE_OBJECTIVE, PSO_MODE_GATEAUX = 0, 1
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+_vp = C.c_void_p
+
+# name -> (restype, argtypes); every symbol include/kirstine_b200.h declares
+SIGNATURES = {
+    "kst_last_error": (C.c_char_p, []),
+    "kst_version": (C.c_int, []),
+    "kst_device_count": (C.c_int, [_ip]),
+    "kst_problem_create": (C.c_int, [C.c_int, _dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                     C.c_int, C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_int, C.POINTER(_vp)]),
+    "kst_problem_destroy": (C.c_int, [_vp]),
+    "kst_comm_unique_id": (C.c_int, [_vp]),
+    "kst_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "kst_objective_batch": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
+    "kst_objective_batch_device": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
+    "kst_stream_synchronize": (C.c_int, [_vp]),
+    "kst_stream": (_vp, [_vp]),
+    "kst_informationmatrix": (C.c_int, [_vp, C.c_int, _dp, _dp, C.c_int64, _dp]),
+    "kst_gateaux_prepare": (C.c_int, [_vp, C.c_int, _dp, _dp, _ip]),
+    "kst_gateaux_constants": (C.c_int, [_vp, _dp, _dp]),
+    "kst_gateaux_eval": (C.c_int, [_vp, C.c_int64, _dp, _dp]),
+    "kst_pso_init": (C.c_int, [_vp, C.c_int, C.c_int, C.c_double, C.c_double, _dp, _dp, C.c_int, _ip, _ip,
+                               C.c_uint64, C.c_int, _ip]),
+    "kst_pso_run": (C.c_int, [_vp, C.c_int, _dp, _dp, _dp]),
+    "kst_pso_get_state": (C.c_int, [_vp] + [_dp] * 11 + [C.POINTER(C.c_int64)]),
+    "kst_profile_enable": (C.c_int, [_vp, C.c_int]),
+    "kst_profile_read": (C.c_int, [_vp, _dp, C.POINTER(C.c_int64)]),
+    "kst_fp64_peak_probe": (C.c_int, [C.c_int, _dp]),
+}
+
+_lib = None
+
+
+class EngineError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("kirstine_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def lib():
+    """Load the shared library (no CUDA call is made by loading)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                "libkirstine_b200.so is not built (%s); run `python __graft_entry__.py build` -- "
+                "this engine has no CPU fallback" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise EngineError(rc, lib().kst_last_error().decode())
+
+
+def f64(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64))
+
+
+def i32(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.int32))
+
+
+def ptr(a):
+    return a.ctypes.data_as(_dp) if a is not None else None
+
+
+def device_count():
+    n = C.c_int(0)
+    check(lib().kst_device_count(C.byref(n)))
+    return n.value
+
+
+class ProblemHandle:
+    """Owns one kst_problem (one GPU, one shard of the prior sample).
+
+    theta (N, r); prior_weights (N,); dt (N, t, r) or None.  Point arrays are (..., K, d).
+    """
+
+    def __init__(self, model_id, model_params, theta, prior_weights, crit, dt, lb, ub, m=1, cp_id=CP_COPY,
+                 device=0):
+        theta = f64(theta)
+        if theta.ndim != 2:
+            raise ValueError("theta must be (N, r)")
+        self.N, self.r = theta.shape
+        pw = f64(prior_weights)
+        lb, ub = f64(lb).ravel(), f64(ub).ravel()
+        self.d = len(lb)
+        self.m = int(m)
+        self.crit = crit
+        if dt is None:
+            self.trafo, self.t, dtc = TRAFO_IDENTITY, self.r, None
+        else:
+            dt = f64(dt)
+            self.trafo, self.t = TRAFO_DELTA, dt.shape[1]
+            dtc = f64(np.transpose(dt, (0, 2, 1)))  # per draw column-major t x r
+        mp = f64(model_params).ravel()
+        h = _vp()
+        check(lib().kst_problem_create(model_id, ptr(mp), len(mp), cp_id, crit, self.trafo, self.r, self.t, self.m,
+                                       self.d, self.N, ptr(theta), ptr(pw), ptr(dtc), ptr(lb), ptr(ub), device,
+                                       C.byref(h)))
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().kst_problem_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- multi-GPU ------------------------------------------------------------------------
+    @staticmethod
+    def comm_unique_id():
+        buf = (C.c_char * 128)()
+        check(lib().kst_comm_unique_id(C.cast(buf, _vp)))
+        return bytes(buf)
+
+    def comm_init(self, nranks, rank, unique_id):
+        buf = C.create_string_buffer(unique_id, 128)
+        check(lib().kst_comm_init(self._h, nranks, rank, C.cast(buf, _vp)))
+
+    # -- objective --------------------------------------------------------------------------
+    def objective_batch(self, points, weights):
+        w = f64(weights)
+        w = w.reshape(-1, w.shape[-1])
+        S, K = w.shape
+        pts = f64(points).reshape(S, K, self.d)
+        fx = np.empty(S)
+        check(lib().kst_objective_batch(self._h, S, K, pts.ctypes.data, w.ctypes.data, fx.ctypes.data))
+        return fx
+
+    def objective_batch_raw(self, S, K, points_ptr, weights_ptr, fx_ptr):
+        """Host pointers as integers (e.g. pinned torch tensors' data_ptr())."""
+        check(lib().kst_objective_batch(self._h, S, K, points_ptr, weights_ptr, fx_ptr))
+
+    def objective_batch_device(self, S, K, d_points, d_weights, d_fx):
+        check(lib().kst_objective_batch_device(self._h, S, K, d_points, d_weights, d_fx))
+
+    def synchronize(self):
+        check(lib().kst_stream_synchronize(self._h))
+
+    def stream(self):
+        return lib().kst_stream(self._h)
+
+    def informationmatrix(self, points, weights, draw=0):
+        w = f64(weights).ravel()
+        pts = f64(points).reshape(len(w), self.d)
+        M = np.empty((self.r, self.r))
+        check(lib().kst_informationmatrix(self._h, len(w), ptr(pts), ptr(w), draw, ptr(M)))
+        return M
+
+    # -- Gateaux ----------------------------------------------------------------------------
+    def gateaux_prepare(self, points, weights):
+        w = f64(weights).ravel()
+        pts = f64(points).reshape(len(w), self.d)
+        s = C.c_int(0)
+        check(lib().kst_gateaux_prepare(self._h, len(w), ptr(pts), ptr(w), C.byref(s)))
+        return bool(s.value)
+
+    def gateaux_constants(self):
+        A = np.empty((self.N, self.r, self.r))
+        trB = np.empty(self.N)
+        check(lib().kst_gateaux_constants(self._h, ptr(A), ptr(trB)))
+        return np.transpose(A, (0, 2, 1)).copy(), trB
+
+    def gateaux_eval(self, directions):
+        dirs = f64(directions).reshape(-1, self.d)
+        out = np.empty(len(dirs))
+        check(lib().kst_gateaux_eval(self._h, len(dirs), ptr(dirs), ptr(out)))
+        return out
+
+    # -- PSO ----------------------------------------------------------------------------------
+    def pso_init(self, S, K, proto_points, proto_weights, fixw=None, fixp=None, seed=1, c1=2.05, c2=2.05,
+                 mode=PSO_MODE_OBJECTIVE):
+        pw = f64(proto_weights).reshape(-1, K)
+        P = len(pw)
+        pp = f64(proto_points).reshape(P, K, self.d)
+        fw = i32(np.zeros(K) if fixw is None else fixw)
+        fp = i32(np.zeros(K) if fixp is None else fixp)
+        st = C.c_int(0)
+        check(lib().kst_pso_init(self._h, S, K, c1, c2, ptr(pp), ptr(pw), P, fw.ctypes.data_as(_ip),
+                                 fp.ctypes.data_as(_ip), seed, mode, C.byref(st)))
+        self._pso_dims = (S, K)
+        return st.value
+
+    def pso_run(self, n_iters):
+        S, K = self._pso_dims
+        tfx = np.empty(n_iters)
+        tp = np.empty((n_iters, K, self.d))
+        tw = np.empty((n_iters, K))
+        check(lib().kst_pso_run(self._h, n_iters, ptr(tfx), ptr(tp), ptr(tw)))
+        return tfx, tp, tw
+
+    def pso_state(self):
+        S, K = self._pso_dims
+        d = self.d
+        st = dict(x_pts=np.empty((S, K, d)), x_w=np.empty((S, K)), p_pts=np.empty((S, K, d)), p_w=np.empty((S, K)),
+                  g_pts=np.empty((K, d)), g_w=np.empty(K), v_pts=np.empty((S, K, d)), v_w=np.empty((S, K)),
+                  fx=np.empty(S), fp=np.empty(S))
+        fg = np.empty(1)
+        ne = C.c_int64(0)
+        check(lib().kst_pso_get_state(self._h, ptr(st["x_pts"]), ptr(st["x_w"]), ptr(st["p_pts"]), ptr(st["p_w"]),
+                                      ptr(st["g_pts"]), ptr(st["g_w"]), ptr(st["v_pts"]), ptr(st["v_w"]),
+                                      ptr(st["fx"]), ptr(st["fp"]), ptr(fg), C.byref(ne)))
+        st["fg"], st["n_eval"] = float(fg[0]), ne.value
+        return st
+
+    # -- measurement --------------------------------------------------------------------------
+    def profile_enable(self, on=True):
+        check(lib().kst_profile_enable(self._h, int(on)))
+
+    def profile_read(self):
+        ms = C.c_double(0)
+        n = C.c_int64(0)
+        check(lib().kst_profile_read(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+
+def fp64_peak_probe(device=0):
+    tf = C.c_double(0)
+    check(lib().kst_fp64_peak_probe(device, C.byref(tf)))
+    return tf.value

@@ -1,0 +1,610 @@
+// C ABI of libkirstine_b200.so (declared in include/kirstine_b200.h): handle management,
+// host<->device staging, the PSO driver loop, and the optional NCCL communicator.
+#include <dlfcn.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <new>
+
+#include "kst_common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void kst_set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char *kst_last_error(void) { return g_err; }
+extern "C" int kst_version(void) { return KST_VERSION; }
+
+extern "C" int kst_device_count(int *count)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        n = 0;
+    }
+    if (count) *count = n;
+    return KST_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// NCCL through dlopen: no link-time dependency, single-GPU users never load it
+// ---------------------------------------------------------------------------------------
+namespace {
+typedef struct { char internal[128]; } kst_nccl_id;
+typedef int (*fn_get_unique_id)(kst_nccl_id *);
+typedef int (*fn_comm_init_rank)(void **, int, kst_nccl_id, int);
+typedef int (*fn_comm_destroy)(void *);
+typedef int (*fn_all_reduce)(const void *, void *, size_t, int, int, void *, cudaStream_t);
+typedef const char *(*fn_get_error_string)(int);
+struct NcclApi {
+    void *lib = nullptr;
+    fn_get_unique_id get_unique_id = nullptr;
+    fn_comm_init_rank comm_init_rank = nullptr;
+    fn_comm_destroy comm_destroy = nullptr;
+    fn_all_reduce all_reduce = nullptr;
+    fn_get_error_string get_error_string = nullptr;
+} g_nccl;
+const int KST_NCCL_FLOAT64 = 8, KST_NCCL_SUM = 0;  // ncclDataType_t / ncclRedOp_t values (stable ABI)
+
+int load_nccl()
+{
+    if (g_nccl.lib) return KST_OK;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    void *lib = nullptr;
+    for (const char *n : names) {
+        lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (lib) break;
+    }
+    if (!lib) {
+        kst_set_error("NCCL not found: %s", dlerror());
+        return KST_ENCCL;
+    }
+    g_nccl.get_unique_id = (fn_get_unique_id)dlsym(lib, "ncclGetUniqueId");
+    g_nccl.comm_init_rank = (fn_comm_init_rank)dlsym(lib, "ncclCommInitRank");
+    g_nccl.comm_destroy = (fn_comm_destroy)dlsym(lib, "ncclCommDestroy");
+    g_nccl.all_reduce = (fn_all_reduce)dlsym(lib, "ncclAllReduce");
+    g_nccl.get_error_string = (fn_get_error_string)dlsym(lib, "ncclGetErrorString");
+    if (!g_nccl.get_unique_id || !g_nccl.comm_init_rank || !g_nccl.comm_destroy || !g_nccl.all_reduce) {
+        kst_set_error("NCCL symbols missing");
+        return KST_ENCCL;
+    }
+    g_nccl.lib = lib;
+    return KST_OK;
+}
+int nccl_fail(const char *what, int rc)
+{
+    kst_set_error("%s failed: %s", what, g_nccl.get_error_string ? g_nccl.get_error_string(rc) : "?");
+    return KST_ENCCL;
+}
+}  // namespace
+
+extern "C" int kst_comm_unique_id(void *id128)
+{
+    int rc = load_nccl();
+    if (rc) return rc;
+    kst_nccl_id id;
+    rc = g_nccl.get_unique_id(&id);
+    if (rc) return nccl_fail("ncclGetUniqueId", rc);
+    memcpy(id128, &id, sizeof(id));
+    return KST_OK;
+}
+
+extern "C" int kst_comm_init(kst_problem *h, int nranks, int rank, const void *id128)
+{
+    if (!h || nranks < 1 || rank < 0 || rank >= nranks) {
+        kst_set_error("comm_init: bad arguments");
+        return KST_EINVAL;
+    }
+    if (nranks == 1) return KST_OK;
+    int rc = load_nccl();
+    if (rc) return rc;
+    KST_CUDA(cudaSetDevice(h->device));
+    kst_nccl_id id;
+    memcpy(&id, id128, sizeof(id));
+    rc = g_nccl.comm_init_rank(&h->comm, nranks, id, rank);
+    if (rc) return nccl_fail("ncclCommInitRank", rc);
+    h->nranks = nranks;
+    h->rank = rank;
+    return KST_OK;
+}
+
+int kst_allreduce_sum(kst_problem *h, double *d_buf, size_t count)
+{
+    if (!h->comm) return KST_OK;
+    const int rc = g_nccl.all_reduce(d_buf, d_buf, count, KST_NCCL_FLOAT64, KST_NCCL_SUM, h->comm, h->stream);
+    if (rc) return nccl_fail("ncclAllReduce", rc);
+    return KST_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// problem handle
+// ---------------------------------------------------------------------------------------
+static int model_dims(int model_id, int *r, int *ndc)
+{
+    switch (model_id) {
+    case KST_MODEL_EMAX: *r = KstEmax::R; *ndc = KstEmax::NDC; return 0;
+    case KST_MODEL_SIGEMAX: *r = KstSigEmax::R; *ndc = KstSigEmax::NDC; return 0;
+    case KST_MODEL_TPC: *r = KstTpc::R; *ndc = KstTpc::NDC; return 0;
+    case KST_MODEL_VU: *r = KstVu::R; *ndc = KstVu::NDC; return 0;
+    }
+    return -1;
+}
+
+extern "C" int kst_problem_destroy(kst_problem *h)
+{
+    if (!h) return KST_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->comm && g_nccl.comm_destroy) g_nccl.comm_destroy(h->comm);
+    kst_pso_free(h);
+    void *ptrs[] = {h->theta, h->pw, h->dc, h->cs, h->aux, h->partials, h->stage_pts, h->stage_w, h->stage_fx,
+                    h->gA, h->gtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return KST_OK;
+}
+
+extern "C" int kst_problem_create(int model_id, const double *model_params, int n_model_params, int cp_id,
+                                  int criterion_id, int trafo_id, int r, int t, int m, int d, int64_t N,
+                                  const double *theta, const double *prior_w, const double *dt_jm, const double *lb,
+                                  const double *ub, int device_id, kst_problem **out)
+{
+    if (!out) { kst_set_error("problem_create: out is NULL"); return KST_EINVAL; }
+    *out = nullptr;
+    int mr = 0, ndc = 0;
+    if (model_dims(model_id, &mr, &ndc)) { kst_set_error("unregistered model id %d", model_id); return KST_EINVAL; }
+    if (r != mr) { kst_set_error("model %d has parameter dimension %d, got r = %d", model_id, mr, r); return KST_EINVAL; }
+    if (criterion_id != KST_CRIT_D && criterion_id != KST_CRIT_A) { kst_set_error("unknown criterion %d", criterion_id); return KST_EINVAL; }
+    if (trafo_id == KST_TRAFO_IDENTITY) {
+        if (t != r) { kst_set_error("identity transformation needs t == r"); return KST_EINVAL; }
+    } else if (trafo_id == KST_TRAFO_DELTA) {
+        if (!dt_jm) { kst_set_error("DeltaMethod needs dt_jm"); return KST_EINVAL; }
+        // more rows than columns makes every information matrix singular (src/transformation.jl:86-88)
+        if (t < 1 || t > r) { kst_set_error("DeltaMethod needs 1 <= t <= r, got t = %d", t); return KST_EINVAL; }
+    } else { kst_set_error("unknown transformation %d", trafo_id); return KST_EINVAL; }
+    const bool vector_unit = model_id == KST_MODEL_VU;
+    if (m < 1 || m > KST_MAX_UNIT || (!vector_unit && m != 1)) { kst_set_error("bad unit length m = %d for model %d", m, model_id); return KST_EINVAL; }
+    if ((vector_unit && cp_id != KST_CP_EQUITIME) || (!vector_unit && cp_id != KST_CP_COPY)) {
+        kst_set_error("covariate parameterization %d not registered for model %d", cp_id, model_id);
+        return KST_EINVAL;
+    }
+    if (d < 1 || d > KST_MAX_D || d != 1) { kst_set_error("design-region dimension d = %d not supported by model %d", d, model_id); return KST_EINVAL; }
+    if (N < 1 || !theta || !prior_w || !lb || !ub) { kst_set_error("problem_create: empty prior sample or NULL buffer"); return KST_EINVAL; }
+    if (n_model_params < 1 || !model_params) { kst_set_error("problem_create: model_params missing"); return KST_EINVAL; }
+    for (int j = 0; j < d; j++)
+        if (!(ub[j] > lb[j])) { kst_set_error("upper bounds must be strictly larger than lower bounds"); return KST_EINVAL; }
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+        cudaGetLastError();
+        kst_set_error("no CUDA device: this engine has no CPU fallback");
+        return KST_ECUDA;
+    }
+    if (device_id < 0 || device_id >= ndev) { kst_set_error("device %d out of range (have %d)", device_id, ndev); return KST_EINVAL; }
+    KST_CUDA(cudaSetDevice(device_id));
+
+    kst_problem *h = new (std::nothrow) kst_problem();
+    if (!h) { kst_set_error("out of host memory"); return KST_ENOMEM; }
+    h->device = device_id;
+    h->model_id = model_id; h->crit = criterion_id; h->trafo = trafo_id;
+    h->r = r; h->t = t; h->m = m; h->d = d; h->N = N;
+    h->ld = ((size_t)N + 31) / 32 * 32;
+    for (int i = 0; i < 4; i++) h->mp.v[i] = i < n_model_params ? model_params[i] : 0.0;
+    h->mp.m = m; h->mp.cp = cp_id; h->mp.d = d;
+    for (int j = 0; j < d; j++) { h->lb[j] = lb[j]; h->ub[j] = ub[j]; }
+    h->n_aux = trafo_id == KST_TRAFO_DELTA ? t * r : (criterion_id == KST_CRIT_A ? r : 0);
+
+    int rc = KST_OK;
+    double *d_theta_aos = nullptr, *d_dt = nullptr;
+#define KST_TRY(call)                        \
+    do {                                     \
+        cudaError_t e__ = (call);            \
+        if (e__ != cudaSuccess) {            \
+            kst_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            rc = KST_ECUDA;                  \
+            goto fail;                       \
+        }                                    \
+    } while (0)
+    {
+        cudaDeviceProp prop;
+        KST_TRY(cudaGetDeviceProperties(&prop, device_id));
+        h->sm_count = prop.multiProcessorCount;
+    }
+    KST_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    KST_TRY(cudaMalloc(&h->theta, sizeof(double) * r * h->ld));
+    KST_TRY(cudaMalloc(&h->pw, sizeof(double) * h->ld));
+    KST_TRY(cudaMalloc(&h->dc, sizeof(double) * ndc * h->ld));
+    KST_TRY(cudaMalloc(&h->cs, sizeof(double) * r * h->ld));
+    if (h->n_aux) KST_TRY(cudaMalloc(&h->aux, sizeof(double) * h->n_aux * h->ld));
+    KST_TRY(cudaMalloc(&h->d_flag, sizeof(int)));
+    KST_TRY(cudaMalloc(&d_theta_aos, sizeof(double) * N * r));
+    KST_TRY(cudaMemsetAsync(h->pw, 0, sizeof(double) * h->ld, h->stream));
+    KST_TRY(cudaMemcpyAsync(d_theta_aos, theta, sizeof(double) * N * r, cudaMemcpyHostToDevice, h->stream));
+    KST_TRY(cudaMemcpyAsync(h->pw, prior_w, sizeof(double) * N, cudaMemcpyHostToDevice, h->stream));
+    if (trafo_id == KST_TRAFO_DELTA) {
+        KST_TRY(cudaMalloc(&d_dt, sizeof(double) * N * t * r));
+        KST_TRY(cudaMemcpyAsync(d_dt, dt_jm, sizeof(double) * N * t * r, cudaMemcpyHostToDevice, h->stream));
+    }
+    rc = kst_launch_prep_draws(h, d_theta_aos, d_dt);
+    if (rc) goto fail;
+    KST_TRY(cudaStreamSynchronize(h->stream));
+    cudaFree(d_theta_aos);
+    if (d_dt) cudaFree(d_dt);
+    *out = h;
+    return KST_OK;
+fail:
+    if (d_theta_aos) cudaFree(d_theta_aos);
+    if (d_dt) cudaFree(d_dt);
+    kst_problem_destroy(h);
+    return rc;
+#undef KST_TRY
+}
+
+int kst_ensure_partials(kst_problem *h, size_t n)
+{
+    if (n <= h->partials_cap) return KST_OK;
+    if (h->partials) KST_CUDA(cudaFree(h->partials));
+    h->partials = nullptr;
+    h->partials_cap = 0;
+    KST_CUDA(cudaMalloc(&h->partials, sizeof(double) * n));
+    h->partials_cap = n;
+    return KST_OK;
+}
+
+static int ensure_stage(kst_problem *h, size_t particles, size_t rows)
+{
+    if (particles > h->stage_cap_particles) {
+        if (h->stage_fx) KST_CUDA(cudaFree(h->stage_fx));
+        h->stage_fx = nullptr;
+        KST_CUDA(cudaMalloc(&h->stage_fx, sizeof(double) * particles));
+        h->stage_cap_particles = particles;
+    }
+    if (rows > h->stage_cap_rows) {
+        if (h->stage_pts) KST_CUDA(cudaFree(h->stage_pts));
+        if (h->stage_w) KST_CUDA(cudaFree(h->stage_w));
+        h->stage_pts = h->stage_w = nullptr;
+        KST_CUDA(cudaMalloc(&h->stage_pts, sizeof(double) * rows * h->d));
+        KST_CUDA(cudaMalloc(&h->stage_w, sizeof(double) * rows));
+        h->stage_cap_rows = rows;
+    }
+    return KST_OK;
+}
+
+#define KST_CHECK_HANDLE(h)                                  \
+    do {                                                     \
+        if (!(h)) { kst_set_error("NULL problem handle"); return KST_EINVAL; } \
+        KST_CUDA(cudaSetDevice((h)->device));                \
+    } while (0)
+
+extern "C" void *kst_stream(kst_problem *h) { return h ? (void *)h->stream : nullptr; }
+
+extern "C" int kst_stream_synchronize(kst_problem *h)
+{
+    KST_CHECK_HANDLE(h);
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    return KST_OK;
+}
+
+extern "C" int kst_objective_batch_device(kst_problem *h, int S, int K, const double *d_points, const double *d_weights,
+                                          double *d_fx)
+{
+    KST_CHECK_HANDLE(h);
+    if (!d_points || !d_weights || !d_fx) { kst_set_error("objective_batch_device: NULL buffer"); return KST_EINVAL; }
+    int rc = kst_launch_objective(h, S, K, d_points, d_weights, d_fx);
+    if (rc) return rc;
+    return kst_allreduce_sum(h, d_fx, (size_t)S);
+}
+
+extern "C" int kst_objective_batch(kst_problem *h, int S, int K, const double *points, const double *weights, double *fx)
+{
+    KST_CHECK_HANDLE(h);
+    if (!points || !weights || !fx) { kst_set_error("objective_batch: NULL buffer"); return KST_EINVAL; }
+    if (S < 1 || K < 1) { kst_set_error("objective_batch: need S >= 1 and K >= 1"); return KST_EINVAL; }
+    int rc = ensure_stage(h, (size_t)S, (size_t)S * K);
+    if (rc) return rc;
+    KST_CUDA(cudaMemcpyAsync(h->stage_pts, points, sizeof(double) * S * K * h->d, cudaMemcpyHostToDevice, h->stream));
+    KST_CUDA(cudaMemcpyAsync(h->stage_w, weights, sizeof(double) * S * K, cudaMemcpyHostToDevice, h->stream));
+    rc = kst_objective_batch_device(h, S, K, h->stage_pts, h->stage_w, h->stage_fx);
+    if (rc) return rc;
+    KST_CUDA(cudaMemcpyAsync(fx, h->stage_fx, sizeof(double) * S, cudaMemcpyDeviceToHost, h->stream));
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    return KST_OK;
+}
+
+extern "C" int kst_informationmatrix(kst_problem *h, int K, const double *points, const double *weights,
+                                     int64_t draw_index, double *M)
+{
+    KST_CHECK_HANDLE(h);
+    if (!points || !weights || !M || K < 1) { kst_set_error("informationmatrix: bad arguments"); return KST_EINVAL; }
+    int rc = ensure_stage(h, (size_t)(h->r * h->r), (size_t)K);
+    if (rc) return rc;
+    KST_CUDA(cudaMemcpyAsync(h->stage_pts, points, sizeof(double) * K * h->d, cudaMemcpyHostToDevice, h->stream));
+    KST_CUDA(cudaMemcpyAsync(h->stage_w, weights, sizeof(double) * K, cudaMemcpyHostToDevice, h->stream));
+    rc = kst_launch_infomatrix(h, K, h->stage_pts, h->stage_w, draw_index, h->stage_fx);
+    if (rc) return rc;
+    KST_CUDA(cudaMemcpyAsync(M, h->stage_fx, sizeof(double) * h->r * h->r, cudaMemcpyDeviceToHost, h->stream));
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    return KST_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// Gateaux derivative
+// ---------------------------------------------------------------------------------------
+extern "C" int kst_gateaux_prepare(kst_problem *h, int K, const double *points, const double *weights, int *singular)
+{
+    KST_CHECK_HANDLE(h);
+    if (!points || !weights || K < 1) { kst_set_error("gateaux_prepare: bad arguments"); return KST_EINVAL; }
+    int rc = ensure_stage(h, 1, (size_t)K);
+    if (rc) return rc;
+    KST_CUDA(cudaMemcpyAsync(h->stage_pts, points, sizeof(double) * K * h->d, cudaMemcpyHostToDevice, h->stream));
+    KST_CUDA(cudaMemcpyAsync(h->stage_w, weights, sizeof(double) * K, cudaMemcpyHostToDevice, h->stream));
+    rc = kst_launch_gateaux_prepare(h, K, h->stage_pts, h->stage_w);
+    if (rc) return rc;
+    if (h->comm) {
+        // every rank must agree on "singular": sum the per-shard flags
+        double f = (double)h->g_singular, *d_f = h->stage_fx;
+        KST_CUDA(cudaMemcpyAsync(d_f, &f, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        rc = kst_allreduce_sum(h, d_f, 1);
+        if (rc) return rc;
+        KST_CUDA(cudaMemcpyAsync(&f, d_f, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        KST_CUDA(cudaStreamSynchronize(h->stream));
+        h->g_singular = f != 0.0;
+    }
+    if (singular) *singular = h->g_singular;
+    return KST_OK;
+}
+
+__global__ void k_unscale_gconst(const double *__restrict__ gA, const double *__restrict__ cs, size_t ld, int64_t N, int r,
+                                 double *__restrict__ out)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= N) return;
+    for (int a = 0; a < r; a++)
+        for (int b = 0; b < r; b++)
+            out[j * r * r + a + b * r] = gA[(size_t)(a * r + b) * ld + j] / (cs[(size_t)a * ld + j] * cs[(size_t)b * ld + j]);
+}
+
+extern "C" int kst_gateaux_constants(kst_problem *h, double *A, double *tr_B)
+{
+    KST_CHECK_HANDLE(h);
+    if (!h->g_ready) { kst_set_error("gateaux_constants before gateaux_prepare"); return KST_ESTATE; }
+    if (A) {
+        double *d_out = nullptr;
+        KST_CUDA(cudaMalloc(&d_out, sizeof(double) * h->N * h->r * h->r));
+        k_unscale_gconst<<<(unsigned)((h->N + 127) / 128), 128, 0, h->stream>>>(h->gA, h->cs, h->ld, h->N, h->r, d_out);
+        KST_CUDA(cudaGetLastError());
+        KST_CUDA(cudaMemcpyAsync(A, d_out, sizeof(double) * h->N * h->r * h->r, cudaMemcpyDeviceToHost, h->stream));
+        KST_CUDA(cudaStreamSynchronize(h->stream));
+        KST_CUDA(cudaFree(d_out));
+    }
+    if (tr_B) {
+        KST_CUDA(cudaMemcpyAsync(tr_B, h->gtrB, sizeof(double) * h->N, cudaMemcpyDeviceToHost, h->stream));
+        KST_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    return KST_OK;
+}
+
+extern "C" int kst_gateaux_eval(kst_problem *h, int64_t G, const double *dirs, double *gd)
+{
+    KST_CHECK_HANDLE(h);
+    if (!dirs || !gd || G < 1) { kst_set_error("gateaux_eval: bad arguments"); return KST_EINVAL; }
+    if ((size_t)G > h->gd_cap) {
+        if (h->gd_dirs) KST_CUDA(cudaFree(h->gd_dirs));
+        if (h->gd_out) KST_CUDA(cudaFree(h->gd_out));
+        h->gd_dirs = h->gd_out = nullptr;
+        h->gd_cap = 0;
+        KST_CUDA(cudaMalloc(&h->gd_dirs, sizeof(double) * G * h->d));
+        KST_CUDA(cudaMalloc(&h->gd_out, sizeof(double) * G));
+        h->gd_cap = (size_t)G;
+    }
+    KST_CUDA(cudaMemcpyAsync(h->gd_dirs, dirs, sizeof(double) * G * h->d, cudaMemcpyHostToDevice, h->stream));
+    int rc = kst_launch_gateaux_eval(h, G, h->gd_dirs, h->gd_out);
+    if (rc) return rc;
+    rc = kst_allreduce_sum(h, h->gd_out, (size_t)G);
+    if (rc) return rc;
+    KST_CUDA(cudaMemcpyAsync(gd, h->gd_out, sizeof(double) * G, cudaMemcpyDeviceToHost, h->stream));
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    return KST_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// PSO driver
+// ---------------------------------------------------------------------------------------
+static int pso_evaluate(kst_problem *h)
+{
+    KstPso &p = h->pso;
+    int rc;
+    if (p.mode == KST_PSO_MODE_OBJECTIVE)
+        rc = kst_launch_objective(h, p.S, p.K, p.x_pts, p.x_w, p.fx);
+    else
+        rc = kst_launch_gateaux_eval(h, p.S, p.x_pts, p.fx);
+    if (rc) return rc;
+    rc = kst_allreduce_sum(h, p.fx, (size_t)p.S);
+    p.n_eval += p.S;
+    return rc;
+}
+
+extern "C" int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, const double *proto_points,
+                            const double *proto_weights, int P, const int *fixw, const int *fixp, uint64_t seed, int mode,
+                            int *status)
+{
+    KST_CHECK_HANDLE(h);
+    // Pso constructor checks, src/pso.jl:35-43; prototypes check, src/pso.jl:89-91
+    if (S <= 1) { kst_set_error("swarmsize must be at least 2"); return KST_EINVAL; }
+    if (c1 < 0 || c2 < 0 || c1 + c2 <= 4) { kst_set_error("c1 and c2 must be non-negative and, c1 + c2 > 4"); return KST_EINVAL; }
+    if (P < 1 || S < P) { kst_set_error("swarmsize must be >= number of prototype particles"); return KST_EINVAL; }
+    if (K < 1 || K * h->m > KST_MAX_ROWS || !proto_points || !proto_weights || !fixw || !fixp) { kst_set_error("pso_init: bad arguments"); return KST_EINVAL; }
+    if (mode == KST_PSO_MODE_GATEAUX) {
+        if (K != 1) { kst_set_error("derivative only implemented for one-point directions"); return KST_EINVAL; }
+        if (!h->g_ready) { kst_set_error("pso_init(gateaux) before gateaux_prepare"); return KST_ESTATE; }
+    } else if (mode != KST_PSO_MODE_OBJECTIVE) { kst_set_error("unknown pso mode %d", mode); return KST_EINVAL; }
+    // check_compatible (src/designmeasure-abstractpoint.jl:60-71)
+    for (int i = 0; i < P * K; i++)
+        for (int j = 0; j < h->d; j++) {
+            const double x = proto_points[(size_t)i * h->d + j];
+            if (!(x >= h->lb[j] && x <= h->ub[j])) { kst_set_error("design point is outside design region"); return KST_EINVAL; }
+        }
+    int rc = kst_pso_alloc(h, S, K);
+    if (rc) return rc;
+    KstPso &p = h->pso;
+    p.mode = mode; p.c1 = c1; p.c2 = c2; p.seed = seed; p.iter = 0; p.n_eval = 0;
+    // "fixing all weights but one is equivalent to fixing them all" (src/designmeasure-abstractpoint.jl:51-56)
+    int fw[KST_MAX_ROWS], nfix = 0;
+    for (int k = 0; k < K; k++) { fw[k] = fixw[k] != 0; nfix += fw[k]; }
+    if (nfix == K - 1)
+        for (int k = 0; k < K; k++) fw[k] = 1;
+    KST_CUDA(cudaMemcpyAsync(p.fixw, fw, sizeof(int) * K, cudaMemcpyHostToDevice, h->stream));
+    KST_CUDA(cudaMemcpyAsync(p.fixp, fixp, sizeof(int) * K, cudaMemcpyHostToDevice, h->stream));
+    rc = ensure_stage(h, 1, (size_t)P * K);
+    if (rc) return rc;
+    KST_CUDA(cudaMemcpyAsync(h->stage_pts, proto_points, sizeof(double) * P * K * h->d, cudaMemcpyHostToDevice, h->stream));
+    KST_CUDA(cudaMemcpyAsync(h->stage_w, proto_weights, sizeof(double) * P * K, cudaMemcpyHostToDevice, h->stream));
+    KST_CUDA(cudaStreamSynchronize(h->stream));  // fw is a stack buffer
+    rc = kst_launch_pso_init(h, h->stage_pts, h->stage_w, P);
+    if (rc) return rc;
+    rc = pso_evaluate(h);
+    if (rc) return rc;
+    rc = kst_launch_pso_best(h, 1, -1);
+    if (rc) return rc;
+    int st = 0;
+    KST_CUDA(cudaMemcpyAsync(&st, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    p.iter = 1;
+    if (status) *status = st;
+    return KST_OK;
+}
+
+extern "C" int kst_pso_run(kst_problem *h, int n_iters, double *trace_fx, double *trace_points, double *trace_weights)
+{
+    KST_CHECK_HANDLE(h);
+    KstPso &p = h->pso;
+    if (p.iter < 1) { kst_set_error("pso_run before pso_init"); return KST_ESTATE; }
+    if (n_iters < 0) { kst_set_error("pso_run: n_iters < 0"); return KST_EINVAL; }
+    if (n_iters == 0) return KST_OK;
+    if (n_iters > p.tr_cap) {
+        if (p.tr_fx) { KST_CUDA(cudaFree(p.tr_fx)); KST_CUDA(cudaFree(p.tr_pts)); KST_CUDA(cudaFree(p.tr_w)); }
+        p.tr_fx = p.tr_pts = p.tr_w = nullptr;
+        p.tr_cap = 0;
+        KST_CUDA(cudaMalloc(&p.tr_fx, sizeof(double) * n_iters));
+        KST_CUDA(cudaMalloc(&p.tr_pts, sizeof(double) * n_iters * p.K * h->d));
+        KST_CUDA(cudaMalloc(&p.tr_w, sizeof(double) * n_iters * p.K));
+        p.tr_cap = n_iters;
+    }
+    for (int it = 0; it < n_iters; it++) {
+        int rc = kst_launch_pso_move(h);
+        if (rc) return rc;
+        rc = pso_evaluate(h);
+        if (rc) return rc;
+        rc = kst_launch_pso_best(h, 0, it);
+        if (rc) return rc;
+        p.iter++;
+    }
+    if (trace_fx) KST_CUDA(cudaMemcpyAsync(trace_fx, p.tr_fx, sizeof(double) * n_iters, cudaMemcpyDeviceToHost, h->stream));
+    if (trace_points)
+        KST_CUDA(cudaMemcpyAsync(trace_points, p.tr_pts, sizeof(double) * n_iters * p.K * h->d, cudaMemcpyDeviceToHost, h->stream));
+    if (trace_weights)
+        KST_CUDA(cudaMemcpyAsync(trace_weights, p.tr_w, sizeof(double) * n_iters * p.K, cudaMemcpyDeviceToHost, h->stream));
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    return KST_OK;
+}
+
+extern "C" int kst_pso_get_state(kst_problem *h, double *x_points, double *x_weights, double *p_points, double *p_weights,
+                                 double *g_points, double *g_weights, double *v_points, double *v_weights, double *fx,
+                                 double *fp, double *fg, int64_t *n_eval)
+{
+    KST_CHECK_HANDLE(h);
+    KstPso &p = h->pso;
+    if (p.iter < 1) { kst_set_error("pso_get_state before pso_init"); return KST_ESTATE; }
+    const size_t np = (size_t)p.S * p.K * h->d, nw = (size_t)p.S * p.K;
+    struct { double *dst; const double *src; size_t n; } cp[] = {
+        {x_points, p.x_pts, np}, {x_weights, p.x_w, nw}, {p_points, p.p_pts, np}, {p_weights, p.p_w, nw},
+        {g_points, p.g_pts, (size_t)p.K * h->d}, {g_weights, p.g_w, (size_t)p.K}, {v_points, p.v_pts, np},
+        {v_weights, p.v_w, nw}, {fx, p.fx, (size_t)p.S}, {fp, p.fp, (size_t)p.S}, {fg, p.fg, 1}};
+    for (auto &c : cp)
+        if (c.dst) KST_CUDA(cudaMemcpyAsync(c.dst, c.src, sizeof(double) * c.n, cudaMemcpyDeviceToHost, h->stream));
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    if (n_eval) *n_eval = p.n_eval;
+    return KST_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// measurement helpers
+// ---------------------------------------------------------------------------------------
+extern "C" int kst_profile_enable(kst_problem *h, int on)
+{
+    KST_CHECK_HANDLE(h);
+    h->prof_on = on != 0;
+    return KST_OK;
+}
+
+extern "C" int kst_profile_read(kst_problem *h, double *total_ms, int64_t *launches)
+{
+    KST_CHECK_HANDLE(h);
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    double tot = 0.0;
+    for (size_t i = 0; i + 1 < h->prof_events.size(); i += 2) {
+        float ms = 0.f;
+        KST_CUDA(cudaEventElapsedTime(&ms, h->prof_events[i], h->prof_events[i + 1]));
+        tot += ms;
+    }
+    if (total_ms) *total_ms = tot;
+    if (launches) *launches = (int64_t)(h->prof_events.size() / 2);
+    for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
+    h->prof_events.clear();
+    return KST_OK;
+}
+
+// DFMA throughput probe: 8 independent FMA chains per thread, enough CTAs to fill every SM.
+__global__ void __launch_bounds__(256) k_dfma_probe(double *out, int iters, double a, double b)
+{
+    double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+            x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+        }
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+}
+
+extern "C" int kst_fp64_peak_probe(int device_id, double *tflops)
+{
+    KST_CUDA(cudaSetDevice(device_id));
+    cudaDeviceProp prop;
+    KST_CUDA(cudaGetDeviceProperties(&prop, device_id));
+    const int blocks = prop.multiProcessorCount * 8, nt = 256, iters = 2048;
+    double *d_out = nullptr;
+    KST_CUDA(cudaMalloc(&d_out, sizeof(double) * blocks * nt));
+    cudaEvent_t e0, e1;
+    KST_CUDA(cudaEventCreate(&e0));
+    KST_CUDA(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 5; rep++) {
+        KST_CUDA(cudaEventRecord(e0, 0));
+        k_dfma_probe<<<blocks, nt>>>(d_out, iters, 0.999999, 1e-9);
+        KST_CUDA(cudaEventRecord(e1, 0));
+        KST_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        KST_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double flops = 2.0 * 8 * 16 * (double)iters * nt * blocks;
+        const double tf = flops / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    KST_CUDA(cudaGetLastError());
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d_out);
+    if (tflops) *tflops = best;
+    return KST_OK;
+}

@@ -1,0 +1,119 @@
+// Shared host-side definitions of libkirstine_b200.so (handle layout, error helpers,
+// launch interfaces between the translation units).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <vector>
+
+#include "../../include/kirstine_b200.h"
+#include "kst_models.cuh"
+
+#define KST_NT 256          // threads per CTA of the evaluation kernels
+#define KST_TILE_P 8        // particles per CTA tile (objective kernel)
+#define KST_GD_NT 128       // threads (= directions) per CTA of the Gateaux kernel
+#define KST_GD_CHUNK 64     // draws staged per shared-memory chunk in the Gateaux kernel
+
+void kst_set_error(const char *fmt, ...);
+
+#define KST_CUDA(call)                                                                      \
+    do {                                                                                    \
+        cudaError_t e__ = (call);                                                           \
+        if (e__ != cudaSuccess) {                                                           \
+            kst_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            return KST_ECUDA;                                                               \
+        }                                                                                   \
+    } while (0)
+
+// dispatch on the registered model family; the body sees the functor type as MF
+#define KST_MODEL_SWITCH(id, ...)                                        \
+    switch (id) {                                                        \
+    case KST_MODEL_EMAX: { using MF = KstEmax; __VA_ARGS__; } break;     \
+    case KST_MODEL_SIGEMAX: { using MF = KstSigEmax; __VA_ARGS__; } break; \
+    case KST_MODEL_TPC: { using MF = KstTpc; __VA_ARGS__; } break;       \
+    case KST_MODEL_VU: { using MF = KstVu; __VA_ARGS__; } break;         \
+    default: kst_set_error("unregistered model id %d", id); return KST_EINVAL; \
+    }
+
+struct KstPso {
+    int S = 0, K = 0, mode = 0, iter = 0;
+    double c1 = 0, c2 = 0;
+    uint64_t seed = 0;
+    int64_t n_eval = 0;
+    // device state: points are [S][K][d], weights [S][K]
+    double *x_pts = nullptr, *x_w = nullptr, *p_pts = nullptr, *p_w = nullptr, *v_pts = nullptr,
+           *v_w = nullptr, *g_pts = nullptr, *g_w = nullptr, *fx = nullptr, *fp = nullptr,
+           *fg = nullptr;
+    int *fixw = nullptr, *fixp = nullptr;
+    // per-run trace buffers (device), grown on demand
+    double *tr_fx = nullptr, *tr_pts = nullptr, *tr_w = nullptr;
+    int tr_cap = 0;
+};
+
+struct kst_problem {
+    int device = 0;
+    int model_id = 0, crit = 0, trafo = 0;
+    int r = 0, t = 0, m = 0, d = 0;
+    int64_t N = 0;      // draws held by this handle (its shard)
+    size_t ld = 0;      // padded leading dimension of the per-draw SoA arrays
+    KstModelParams mp{};
+    double lb[KST_MAX_D]{}, ub[KST_MAX_D]{};
+    cudaStream_t stream = nullptr;
+    int sm_count = 0;
+
+    // per-draw SoA arrays, each [rows][ld]
+    double *theta = nullptr;   // r   raw parameters
+    double *pw = nullptr;      // 1   prior weights
+    double *dc = nullptr;      // NDC hoisted per-draw constants of the model functor
+    double *cs = nullptr;      // r   column scales
+    double *aux = nullptr;     // A/Identity: r (1/cs^2); DeltaMethod: t*r (DT/cs); else unused
+    int n_aux = 0;
+    double offset = 0.0;       // sum_j pw_j * 2 sum_i log|cs_ij|  (D / Identity), else 0
+
+    // scratch for the objective kernel: partial sums [S][n_blk]
+    double *partials = nullptr;
+    size_t partials_cap = 0;
+    // staging for the host-buffer entry points
+    double *stage_pts = nullptr, *stage_w = nullptr, *stage_fx = nullptr;
+    size_t stage_cap_particles = 0, stage_cap_rows = 0;
+
+    // Gateaux constants at the last prepared design: At [r*r][ld] (scaled space), trB [ld]
+    double *gA = nullptr, *gtrB = nullptr;
+    int g_ready = 0, g_singular = 0;
+    double g_offset = 0.0;     // sum_j pw_j trB_j
+    int *d_flag = nullptr;     // device flag word (singular detection)
+    double *gd_dirs = nullptr, *gd_out = nullptr, *gd_partials = nullptr;
+    size_t gd_cap = 0, gd_partials_cap = 0;
+
+    KstPso pso;
+
+    // communicator (optional)
+    void *comm = nullptr;
+    int nranks = 1, rank = 0;
+
+    // profiling of the evaluation kernel
+    int prof_on = 0;
+    std::vector<cudaEvent_t> prof_events;  // start/stop pairs, resolved by kst_profile_read
+};
+
+// kst_objective.cu
+int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const double *d_dt);
+int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, const double *d_w,
+                         double *d_fx);
+int kst_launch_infomatrix(kst_problem *h, int K, const double *d_pts, const double *d_w,
+                          int64_t draw, double *d_M);
+int kst_objective_grid(const kst_problem *h, int S, int *n_blk);
+int kst_sum_fixed(kst_problem *h, const double *d_x, int64_t n, double *host_out);
+// kst_gateaux.cu
+int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const double *d_w);
+int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, double *d_out);
+// kst_pso.cu
+int kst_pso_alloc(kst_problem *h, int S, int K);
+void kst_pso_free(kst_problem *h);
+int kst_launch_pso_init(kst_problem *h, const double *d_proto_pts, const double *d_proto_w, int P);
+int kst_launch_pso_move(kst_problem *h);
+int kst_launch_pso_best(kst_problem *h, int init, int trace_slot);
+// kst_api.cu
+int kst_allreduce_sum(kst_problem *h, double *d_buf, size_t count);
+int kst_ensure_partials(kst_problem *h, size_t n);

@@ -1,0 +1,394 @@
+// Gateaux derivative of the design objective.
+//
+//   gateaux_constants  src/criterion-d.jl:43-87, src/criterion-a.jl:47-77  -> k_gateaux_prepare
+//   gateauxderivative! src/designproblem.jl:239-258 (+ gateaux_integrand / tr_prod,
+//                      src/design-common.jl:66-68,224-248)                  -> k_gateaux_eval
+//
+// Everything is done in the column-scaled space of kst_models.cuh: with M = D Mt D and
+// DTt = DT D^-1 the constants become
+//   At = Mt^-1 Smat Mt^-1,   Smat = DTt' W DTt,
+//   W  = I (A criterion)  or  (DTt Mt^-1 DTt')^-1 (D criterion);  Identity: DTt = D^-1
+// and tr[A M(delta)] = sum_rows omega * gt' At gt for a one-point direction delta.
+// A_j of the reference is recovered as D^-1 At D^-1 on copy-out (kst_gateaux_constants).
+//
+// Evaluation mapping: one thread per direction (no cross-thread reduction at all), draws are
+// staged chunk-wise in shared memory and read as broadcasts, so the per-draw constants
+// (8*(NDC + r(r+1)/2) bytes) are loaded once per CTA of KST_GD_NT directions instead of once
+// per (direction, draw) pair.  The draw range is split over gridDim.y for small G; partial sums
+// are combined in fixed order.
+#include "kst_common.cuh"
+#include "kst_linalg.cuh"
+
+// rows of one design measure (single thread): map_to_covariate! + update_model_vcov! + compaction
+template <class MF>
+__device__ __forceinline__ int kst_build_rows(double *rows, double &sw, const double *pts, const double *w, int K,
+                                              const KstModelParams &mp)
+{
+    constexpr int RW = 1 + MF::NPC;
+    int na = 0;
+    sw = 0.0;
+    for (int k = 0; k < K; k++) {
+        const double *z = pts + (size_t)k * mp.d;
+        for (int i = 0; i < mp.m; i++) {
+            double pc[MF::NPC], varfac;
+            const bool trivial = MF::prep_row(z, i, mp, pc, varfac);
+            const double om = w[k] * varfac;
+            sw += om;
+            if (!trivial) {
+                rows[na * RW] = om;
+                for (int c = 0; c < MF::NPC; c++) rows[na * RW + 1 + c] = pc[c];
+                na++;
+            }
+        }
+    }
+    return na;
+}
+
+// One thread per draw.  Writes At (full symmetric, [R*R][ld]) and trB; sets *flag on failure.
+template <class MF>
+__global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *__restrict__ cs,
+                                  const double *__restrict__ aux, const double *__restrict__ pw, size_t ld,
+                                  int64_t N, int crit, int trafo, int t, const double *__restrict__ pts,
+                                  const double *__restrict__ w, int K, KstModelParams mp, double *__restrict__ gA,
+                                  double *__restrict__ gtrB, double *__restrict__ wtrB, int *flag)
+{
+    constexpr int R = MF::R, RW = 1 + MF::NPC;
+    extern __shared__ double smem[];  // rows[K*m][RW], sw, na
+    double *rows = smem;
+    double *s_sw = smem + (size_t)K * mp.m * RW;
+    int *s_na = (int *)(s_sw + 1);
+    if (threadIdx.x == 0) {
+        double sw;
+        *s_na = kst_build_rows<MF>(rows, sw, pts, w, K, mp);
+        *s_sw = sw;
+    }
+    __syncthreads();
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= N) return;
+    double dcv[MF::NDC], M[KstPacked<R>::N];
+#pragma unroll
+    for (int c = 0; c < MF::NDC; c++) dcv[c] = dc[(size_t)c * ld + j];
+#pragma unroll
+    for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
+    const int na = *s_na;
+    for (int i = 0; i < na; i++) {
+        double g[R];
+        MF::row(rows + i * RW + 1, dcv, g);
+        kst_accum<R, MF::CONST_COL>(M, rows[i * RW], g);
+    }
+    constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
+    if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = *s_sw;
+
+    double L[R][R], dv[R], dinv[R];
+    bool ok = kst_ldlt<R>(M, L, dv, dinv, true);
+    // Mt^-1 = Li' diag(dinv) Li with Li = L^-1 (unit lower)
+    double Li[R][R];
+#pragma unroll
+    for (int a = 0; a < R; a++) {
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            double v = (k == a) ? 1.0 : 0.0;
+            if (k > a) {
+#pragma unroll
+                for (int l = 0; l < k; l++)
+                    if (l >= a) v = fma(-L[k][l], Li[l][a], v);
+            }
+            Li[k][a] = v;
+        }
+    }
+    double Mi[R][R];
+#pragma unroll
+    for (int a = 0; a < R; a++)
+#pragma unroll
+        for (int b = a; b < R; b++) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < R; k++)
+                if (k >= b) s = fma(Li[k][a] * dinv[k], Li[k][b], s);
+            Mi[a][b] = s;
+            Mi[b][a] = s;
+        }
+    // DTt (tt x R)
+    double DTt[R][R];
+    const int tt = trafo == KST_TRAFO_IDENTITY ? R : t;
+    if (trafo == KST_TRAFO_IDENTITY) {
+#pragma unroll
+        for (int a = 0; a < R; a++)
+#pragma unroll
+            for (int i = 0; i < R; i++) DTt[a][i] = (a == i) ? 1.0 / cs[(size_t)i * ld + j] : 0.0;
+    } else {
+#pragma unroll
+        for (int a = 0; a < R; a++)
+#pragma unroll
+            for (int i = 0; i < R; i++) DTt[a][i] = a < tt ? aux[(size_t)(a * R + i) * ld + j] : 0.0;
+    }
+    double At[R][R];
+    double trB;
+    if (crit == KST_CRIT_D && trafo == KST_TRAFO_IDENTITY) {
+#pragma unroll
+        for (int a = 0; a < R; a++)
+#pragma unroll
+            for (int b = 0; b < R; b++) At[a][b] = Mi[a][b];
+        trB = (double)R;
+    } else {
+        // P = DTt Mt^-1 (tt x R), C = P DTt' (tt x tt)
+        double P[R][R], C[R][R], W[R][R];
+#pragma unroll
+        for (int a = 0; a < R; a++)
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                double s = 0.0;
+#pragma unroll
+                for (int k = 0; k < R; k++) s = fma(DTt[a][k], Mi[k][i], s);
+                P[a][i] = s;
+            }
+#pragma unroll
+        for (int a = 0; a < R; a++)
+#pragma unroll
+            for (int b = 0; b < R; b++) {
+                double s = 0.0;
+#pragma unroll
+                for (int k = 0; k < R; k++) s = fma(P[a][k], DTt[b][k], s);
+                C[a][b] = s;
+            }
+        if (crit == KST_CRIT_A) {
+            trB = 0.0;
+#pragma unroll
+            for (int a = 0; a < R; a++) {
+                if (a < tt) trB += C[a][a];
+#pragma unroll
+                for (int b = 0; b < R; b++) W[a][b] = (a == b && a < tt) ? 1.0 : 0.0;
+            }
+        } else {
+            // W = C^-1 (tt x tt, symmetric positive definite) by Gauss-Jordan without pivoting
+            trB = (double)tt;
+#pragma unroll
+            for (int a = 0; a < R; a++)
+#pragma unroll
+                for (int b = 0; b < R; b++) W[a][b] = (a == b) ? 1.0 : 0.0;
+#pragma unroll
+            for (int c = 0; c < R; c++) {
+                if (c < tt) {
+                    const double piv = C[c][c];
+                    ok = ok && (piv > 0.0);
+                    const double ip = 1.0 / piv;
+#pragma unroll
+                    for (int b = 0; b < R; b++) { C[c][b] *= ip; W[c][b] *= ip; }
+#pragma unroll
+                    for (int a = 0; a < R; a++) {
+                        if (a != c && a < tt) {
+                            const double f = C[a][c];
+#pragma unroll
+                            for (int b = 0; b < R; b++) {
+                                C[a][b] = fma(-f, C[c][b], C[a][b]);
+                                W[a][b] = fma(-f, W[c][b], W[a][b]);
+                            }
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int a = 0; a < R; a++)
+#pragma unroll
+                for (int b = 0; b < R; b++)
+                    if (a >= tt || b >= tt) W[a][b] = 0.0;
+        }
+        // At = P' W P
+        double WP[R][R];
+#pragma unroll
+        for (int a = 0; a < R; a++)
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                double s = 0.0;
+#pragma unroll
+                for (int b = 0; b < R; b++) s = fma(W[a][b], P[b][i], s);
+                WP[a][i] = s;
+            }
+#pragma unroll
+        for (int i = 0; i < R; i++)
+#pragma unroll
+            for (int k = 0; k < R; k++) {
+                double s = 0.0;
+#pragma unroll
+                for (int a = 0; a < R; a++) s = fma(P[a][i], WP[a][k], s);
+                At[i][k] = s;
+            }
+    }
+    if (!ok) atomicExch(flag, 1);
+#pragma unroll
+    for (int a = 0; a < R; a++)
+#pragma unroll
+        for (int b = 0; b < R; b++) gA[(size_t)(a * R + b) * ld + j] = At[a][b];
+    gtrB[j] = trB;
+    wtrB[j] = pw[j] * trB;
+}
+
+// One thread per direction; draws staged in shared memory.
+template <class MF>
+__global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__restrict__ dc, const double *__restrict__ pw,
+                                                            const double *__restrict__ gA, size_t ld, int64_t N,
+                                                            const double *__restrict__ dirs, int64_t G,
+                                                            KstModelParams mp, double *__restrict__ partials)
+{
+    constexpr int R = MF::R, RW = 1 + MF::NPC, NP = KstPacked<R>::N, NS = MF::NDC + NP;
+    extern __shared__ double smem[];
+    double *s_draw = smem;                                  // [NS][KST_GD_CHUNK]
+    double *s_rows = smem + (size_t)NS * KST_GD_CHUNK;      // [m][RW][KST_GD_NT]
+    const int m = mp.m;
+    const int64_t g = (int64_t)blockIdx.x * KST_GD_NT + threadIdx.x;
+    const bool live = g < G;
+
+    // rows of this thread's direction (weight 1); trivial rows get omega = 0 and benign pc
+    double sw_triv = 0.0;
+    for (int i = 0; i < m; i++) {
+        double pc[MF::NPC], varfac = 0.0;
+        bool trivial = true;
+        if (live) trivial = MF::prep_row(dirs + g * mp.d, i, mp, pc, varfac);
+        if (trivial) {
+            sw_triv += varfac;
+            varfac = 0.0;
+            for (int c = 0; c < MF::NPC; c++) pc[c] = 1.0;
+        }
+        s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x] = varfac;
+        for (int c = 0; c < MF::NPC; c++) s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x] = pc[c];
+    }
+
+    // this CTA's draw range
+    const int64_t per = (N + gridDim.y - 1) / gridDim.y;
+    const int64_t j0 = per * blockIdx.y, j1 = min(N, j0 + per);
+    double acc = 0.0;
+    for (int64_t jb = j0; jb < j1; jb += KST_GD_CHUNK) {
+        const int nj = (int)min((int64_t)KST_GD_CHUNK, j1 - jb);
+        __syncthreads();
+        for (int e = threadIdx.x; e < NS * KST_GD_CHUNK; e += KST_GD_NT) {
+            const int c = e / KST_GD_CHUNK, jj = e % KST_GD_CHUNK;
+            double v = 0.0;
+            if (jj < nj) {
+                const int64_t j = jb + jj;
+                if (c < MF::NDC) {
+                    v = dc[(size_t)c * ld + j];
+                } else {
+                    // packed upper of pw_j * At_j, off-diagonals doubled
+                    int q = c - MF::NDC, a = 0;
+                    while (q >= R - a) { q -= R - a; a++; }
+                    const int b = a + q;
+                    v = pw[j] * gA[(size_t)(a * R + b) * ld + j] * (a == b ? 1.0 : 2.0);
+                }
+            }
+            s_draw[e] = v;
+        }
+        __syncthreads();
+        for (int jj = 0; jj < nj; jj++) {
+            double dcv[MF::NDC], Ap[NP];
+#pragma unroll
+            for (int c = 0; c < MF::NDC; c++) dcv[c] = s_draw[c * KST_GD_CHUNK + jj];
+#pragma unroll
+            for (int c = 0; c < NP; c++) Ap[c] = s_draw[(MF::NDC + c) * KST_GD_CHUNK + jj];
+            for (int i = 0; i < m; i++) {
+                double pc[MF::NPC], gv[R];
+                const double om = s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x];
+#pragma unroll
+                for (int c = 0; c < MF::NPC; c++) pc[c] = s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x];
+                MF::row(pc, dcv, gv);
+                double q = 0.0;
+#pragma unroll
+                for (int a = 0; a < R; a++) {
+                    double s = 0.0;
+#pragma unroll
+                    for (int b = a; b < R; b++) s = fma(Ap[kst_pidx<R>(a, b)], gv[b], s);
+                    q = fma(s, gv[a], q);
+                }
+                acc = fma(om, q, acc);
+            }
+            constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
+            if (MF::CONST_COL >= 0) acc = fma(sw_triv, Ap[kst_pidx<R>(cc, cc)], acc);
+        }
+    }
+    if (live) partials[g * gridDim.y + blockIdx.y] = acc;
+}
+
+__global__ void k_gd_finish(const double *__restrict__ partials, int n_split, double offset, int singular,
+                            double *__restrict__ out, int64_t G)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G) return;
+    if (singular) {
+        out[g] = __longlong_as_double(0x7ff8000000000000LL);
+        return;
+    }
+    double s = 0.0;
+    for (int b = 0; b < n_split; b++) s += partials[g * n_split + b];
+    out[g] = s - offset;
+}
+
+
+int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const double *d_w)
+{
+    if (K < 1 || K * h->m > KST_MAX_ROWS) {
+        kst_set_error("gateaux_prepare: need K >= 1 and K*m <= %d", KST_MAX_ROWS);
+        return KST_EINVAL;
+    }
+    if (!h->gA) {
+        KST_CUDA(cudaMalloc(&h->gA, sizeof(double) * h->r * h->r * h->ld));
+        KST_CUDA(cudaMalloc(&h->gtrB, sizeof(double) * h->ld));
+    }
+    double *wtrB = nullptr;
+    KST_CUDA(cudaMalloc(&wtrB, sizeof(double) * h->N));
+    KST_CUDA(cudaMemsetAsync(h->d_flag, 0, sizeof(int), h->stream));
+    const int nt = 128;
+    const unsigned nb = (unsigned)((h->N + nt - 1) / nt);
+    KST_MODEL_SWITCH(h->model_id, {
+        const size_t smem = sizeof(double) * ((size_t)K * h->m * (1 + MF::NPC) + 2);
+        k_gateaux_prepare<MF><<<nb, nt, smem, h->stream>>>(h->dc, h->cs, h->aux, h->pw, h->ld, h->N, h->crit, h->trafo,
+                                                           h->t, d_pts, d_w, K, h->mp, h->gA, h->gtrB, wtrB, h->d_flag);
+    });
+    KST_CUDA(cudaGetLastError());
+    int rc = kst_sum_fixed(h, wtrB, h->N, &h->g_offset);
+    cudaFree(wtrB);
+    if (rc) return rc;
+    int flag = 0;
+    KST_CUDA(cudaMemcpyAsync(&flag, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    h->g_singular = flag;
+    h->g_ready = 1;
+    return KST_OK;
+}
+
+int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, double *d_out)
+{
+    if (!h->g_ready) {
+        kst_set_error("gateaux_eval before gateaux_prepare");
+        return KST_ESTATE;
+    }
+    if (G < 1) {
+        kst_set_error("gateaux_eval: need G >= 1");
+        return KST_EINVAL;
+    }
+    const int64_t gblocks = (G + KST_GD_NT - 1) / KST_GD_NT;
+    const int64_t max_split = (h->N + KST_GD_CHUNK - 1) / KST_GD_CHUNK;
+    int64_t n_split = (4LL * h->sm_count + gblocks - 1) / gblocks;
+    if (n_split > max_split) n_split = max_split;
+    if (n_split < 1) n_split = 1;
+    if (n_split > 65535) n_split = 65535;
+    const size_t need = (size_t)G * n_split;
+    if (need > h->gd_partials_cap) {
+        if (h->gd_partials) KST_CUDA(cudaFree(h->gd_partials));
+        h->gd_partials = nullptr;
+        KST_CUDA(cudaMalloc(&h->gd_partials, sizeof(double) * need));
+        h->gd_partials_cap = need;
+    }
+    const dim3 grid((unsigned)gblocks, (unsigned)n_split);
+    if (!h->g_singular) {
+        KST_MODEL_SWITCH(h->model_id, {
+            constexpr int NS = MF::NDC + KstPacked<MF::R>::N;
+            const size_t smem = sizeof(double) * ((size_t)NS * KST_GD_CHUNK + (size_t)h->m * (1 + MF::NPC) * KST_GD_NT);
+            k_gateaux_eval<MF><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->pw, h->gA, h->ld, h->N, d_dirs, G, h->mp,
+                                                                     h->gd_partials);
+        });
+        KST_CUDA(cudaGetLastError());
+    }
+    k_gd_finish<<<(unsigned)((G + 127) / 128), 128, 0, h->stream>>>(h->gd_partials, (int)n_split, h->g_offset,
+                                                                   h->g_singular, d_out, G);
+    KST_CUDA(cudaGetLastError());
+    return KST_OK;
+}

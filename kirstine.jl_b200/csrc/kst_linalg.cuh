@@ -1,0 +1,166 @@
+// In-register FP64 small-matrix code for the evaluation kernels.
+//
+// Replaces the BLAS/LAPACK calls of the reference hot path: syrk! ->
+// kst_accum, potrf!/log_det! -> kst_ldlt + one log of the pivot product, posv! + mul! ->
+// forward substitution on the unit-lower factor, potri! + tr -> columns of L^-1.
+// All loops are compile-time unrolled so every matrix entry lives in a register.
+//
+// Factorisation: square-root-free Cholesky  Mt = L diag(dv) L'.  The pivots dv[j] are the
+// squares of the diagonal of the reference's upper Cholesky factor, so "pivot <= 0 or NaN"
+// is exactly the reference's "potrf! failed / U[i,i] <= 0" condition.
+#pragma once
+#include <math.h>
+
+#define KST_INF (__longlong_as_double(0x7ff0000000000000LL))
+
+template <int R>
+__device__ __forceinline__ constexpr int kst_pidx(int i, int j)  // i <= j, packed upper, row-major
+{
+    return i * R - (i * (i - 1)) / 2 + (j - i);
+}
+template <int R>
+struct KstPacked {
+    static constexpr int N = R * (R + 1) / 2;
+};
+
+// Mt += w * g g'  (upper triangle).  g[CC] is the compile-time constant 1 when CC >= 0; the
+// (CC, CC) entry is not accumulated at all: it is the per-particle sum of row weights.
+template <int R, int CC>
+__device__ __forceinline__ void kst_accum(double *M, double w, const double *g)
+{
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+        const double wg = (i == CC) ? w : w * g[i];
+#pragma unroll
+        for (int j = i; j < R; j++) {
+            if (i == CC && j == CC) continue;
+            if (j == CC)
+                M[kst_pidx<R>(i, j)] += wg;
+            else
+                M[kst_pidx<R>(i, j)] = fma(wg, g[j], M[kst_pidx<R>(i, j)]);
+        }
+    }
+}
+
+// Mt (packed upper) -> unit lower L (strictly lower part used), pivots dv, 1/dv.
+// Returns false at the first pivot that is not > 0 (also catches NaN).
+template <int R>
+__device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], double (&dv)[R],
+                                         double (&dinv)[R], bool need_last_inv)
+{
+    double W[R][R];  // W[i][j] = L[i][j] * dv[j]
+    bool ok = true;
+#pragma unroll
+    for (int j = 0; j < R; j++) {
+        double dj = M[kst_pidx<R>(j, j)];
+#pragma unroll
+        for (int k = 0; k < j; k++) dj = fma(-L[j][k], W[j][k], dj);
+        dv[j] = dj;
+        ok = ok && (dj > 0.0);
+        if (j < R - 1 || need_last_inv) dinv[j] = 1.0 / dj;
+#pragma unroll
+        for (int i = j + 1; i < R; i++) {
+            double v = M[kst_pidx<R>(j, i)];
+#pragma unroll
+            for (int k = 0; k < j; k++) v = fma(-L[i][k], W[j][k], v);
+            W[i][j] = v;
+            L[i][j] = v * dinv[j];
+        }
+    }
+    return ok;
+}
+
+// log of a product of positive pivots with one log call; falls back to a sum of logs when the
+// product leaves the normal range (never on well-scaled information matrices).
+template <int R>
+__device__ __forceinline__ double kst_log_prod(const double (&dv)[R])
+{
+    double prod = dv[0];
+#pragma unroll
+    for (int j = 1; j < R; j++) prod *= dv[j];
+    if (prod > 1e-290 && prod < 1e290) return log(prod);
+    double s = 0.0;
+#pragma unroll
+    for (int j = 0; j < R; j++) s += log(dv[j]);
+    return s;
+}
+
+// Per-(particle, draw) criterion value from the accumulated Mt.
+//
+// CRIT 0 = D, 1 = A.  T = 0: Identity; T >= 1: DeltaMethod with codomain dimension T.
+// aux points at this draw's auxiliary constants with stride `ld` between entries:
+//   A / Identity : R doubles  s_i = 1/cs_i^2                       (tr M^-1 = sum s_i (Mt^-1)_ii)
+//   DeltaMethod  : T*R doubles DTt[a][i] = DT[a][i]/cs_i, a-major   (DT M^-1 DT' = DTt Mt^-1 DTt')
+// exc is set where the reference throws (PosDefException from posv!, src/design-common.jl:197;
+// SingularException from potri!, src/criterion-a.jl:39): objective! then returns -Inf no matter
+// the prior weight (src/designproblem.jl:217-223).  Silent failures (log_det!,
+// src/design-common.jl:213-220) just return -Inf, which the caller multiplies by the weight.
+template <int R, int CRIT, int T>
+__device__ __forceinline__ double kst_criterion(const double *M, const double *aux, size_t ld, bool &exc)
+{
+    double L[R][R], dv[R], dinv[R];
+    exc = false;
+    if (CRIT == 0 && T == 0) {
+        const bool ok = kst_ldlt<R>(M, L, dv, dinv, false);
+        return ok ? kst_log_prod<R>(dv) : -KST_INF;
+    }
+    const bool ok = kst_ldlt<R>(M, L, dv, dinv, true);
+    if (!ok) {
+        exc = true;
+        return -KST_INF;
+    }
+    if (T == 0) {
+        // A / Identity: -tr(M^-1) = -sum_a s_a * sum_{k>=a} (L^-1)[k][a]^2 / dv[k]
+        double tr = 0.0;
+#pragma unroll
+        for (int a = 0; a < R; a++) {
+            double y[R];
+            y[a] = 1.0;
+            double ta = dinv[a];
+#pragma unroll
+            for (int k = a + 1; k < R; k++) {
+                double v = -L[k][a];
+#pragma unroll
+                for (int l = a + 1; l < k; l++) v = fma(-L[k][l], y[l], v);
+                y[k] = v;
+                ta = fma(v * v, dinv[k], ta);
+            }
+            tr = fma(aux[(size_t)a * ld], ta, tr);
+        }
+        return -tr;
+    }
+    // DeltaMethod: Y = L^-1 DTt' (R x T), MTinv = Y' diag(1/dv) Y  (T x T)
+    constexpr int TT = T > 0 ? T : 1;
+    double Y[TT][R];
+#pragma unroll
+    for (int a = 0; a < TT; a++) {
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            double v = aux[(size_t)(a * R + k) * ld];
+#pragma unroll
+            for (int l = 0; l < k; l++) v = fma(-L[k][l], Y[a][l], v);
+            Y[a][k] = v;
+        }
+    }
+    if (CRIT == 1) {
+        double tr = 0.0;
+#pragma unroll
+        for (int a = 0; a < TT; a++)
+#pragma unroll
+            for (int k = 0; k < R; k++) tr = fma(Y[a][k] * Y[a][k], dinv[k], tr);
+        return -tr;
+    }
+    double Mi[KstPacked<TT>::N];
+#pragma unroll
+    for (int a = 0; a < TT; a++)
+#pragma unroll
+        for (int b = a; b < TT; b++) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < R; k++) s = fma(Y[a][k] * dinv[k], Y[b][k], s);
+            Mi[kst_pidx<TT>(a, b)] = s;
+        }
+    double L2[TT][TT], dv2[TT], dinv2[TT];
+    const bool ok2 = kst_ldlt<TT>(Mi, L2, dv2, dinv2, false);
+    return ok2 ? -kst_log_prod<TT>(dv2) : -KST_INF;
+}

@@ -1,0 +1,143 @@
+// Device functors for the registered model families.
+//
+// A functor replaces the user callbacks of the reference (src/user.jl:18-98: unit_length,
+// jacobianmatrix!, map_to_covariate!, update_model_vcov!, dimension) for one family.
+//
+// Design (not a translation of jacobianmatrix!): every Jacobian row is factored as
+//     g(c, theta) = diag(cs(theta)) * gt(pc(c), dc(theta))
+// with
+//   cs  per-draw column scales  (depend on theta only, computed once per problem),
+//   dc  per-draw constants      (theta-only transcendentals hoisted out of the hot loop),
+//   pc  per-row constants       (covariate-only transcendentals, once per particle),
+//   gt  the reduced row, the only thing evaluated per (row, draw).
+// The normalised information matrix is then M = D Mt D with D = diag(cs) and
+// Mt = sum_rows omega * gt gt'; log det, traces of inverses and DeltaMethod products are taken
+// on Mt with D folded into per-draw constants (kst_linalg.cuh).  1/sigma of the unit covariance
+// is folded into cs as well, so omega = w_k * varfac with varfac = 1 for constant variance.
+//
+// "Trivial" rows have gt = e_CONST_COL (or 0 when the family has no constant column): they
+// contribute nothing to the per-draw accumulators and are compacted away per particle.
+#pragma once
+#include <math.h>
+
+struct KstModelParams {
+    double v[4];
+    int m;   // unit length
+    int cp;  // covariate parameterization id
+    int d;   // design-region dimension
+    int pad;
+};
+
+// Emax: test/example-emax.jl:41-47.  row = [1, x/(x+ec50), -emax x/(x+ec50)^2]
+struct KstEmax {
+    static constexpr int R = 3, NDC = 1, NPC = 1, CONST_COL = 0, D_MIN = 1;
+    __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
+    {
+        const double isig = 1.0 / sqrt(mp.v[0]);  // v[0] = sigma_squared
+        dc[0] = th[2];
+        cs[0] = isig;
+        cs[1] = isig;
+        cs[2] = -th[1] * isig;
+    }
+    // returns true when the row is trivial
+    __device__ static bool prep_row(const double *z, int, const KstModelParams &, double *pc, double &varfac)
+    {
+        pc[0] = z[0];
+        varfac = 1.0;
+        return z[0] == 0.0;
+    }
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g)
+    {
+        const double rho = 1.0 / (pc[0] + dc[0]);
+        const double a = pc[0] * rho;
+        g[0] = 1.0;
+        g[1] = a;
+        g[2] = a * rho;
+    }
+};
+
+// sigmoid Emax: docs/src/tutorial.md:127-142.
+//   A = x^h/(x^h+ed50^h) = 1/(1+e),  e = exp(-h (log x - log ed50)),  A B = emax e/(1+e)^2
+//   row = [1, A, -A B h/ed50, A B log(x/ed50)],  dose == 0 -> [1, 0, 0, 0]
+struct KstSigEmax {
+    static constexpr int R = 4, NDC = 2, NPC = 1, CONST_COL = 0, D_MIN = 1;
+    __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
+    {
+        const double isig = 1.0 / fabs(mp.v[0]);  // v[0] = sigma
+        dc[0] = log(th[2]);
+        dc[1] = th[3];
+        cs[0] = isig;
+        cs[1] = isig;
+        cs[2] = -th[1] * th[3] / th[2] * isig;
+        cs[3] = th[1] * isig;
+    }
+    __device__ static bool prep_row(const double *z, int, const KstModelParams &, double *pc, double &varfac)
+    {
+        pc[0] = log(z[0]);
+        varfac = 1.0;
+        return z[0] == 0.0;
+    }
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g)
+    {
+        const double L = pc[0] - dc[0];
+        // clamp keeps e finite so that u = e/(1+e)^2 never becomes Inf*0
+        const double e = exp(fmin(-dc[1] * L, 700.0));
+        const double rr = 1.0 / (1.0 + e);
+        const double u = e * rr * rr;
+        g[0] = 1.0;
+        g[1] = rr;
+        g[2] = u;
+        g[3] = u * L;
+    }
+};
+
+// one-compartment model (Atkinson et al. 1993): test/example-compartment.jl:14-21
+//   row = [A s t, -E s t, E - A],  A = exp(-a t), E = exp(-e t)
+// VUMod (test/example-vector.jl:9-50) is the same row at times (i-1)*z with unit covariance
+// diag(sigma_squared (1 + t_i)).
+struct KstTpc {
+    static constexpr int R = 3, NDC = 2, NPC = 1, CONST_COL = -1, D_MIN = 1;
+    __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
+    {
+        const double isig = 1.0 / fabs(mp.v[0]);  // v[0] = sigma
+        dc[0] = th[0];
+        dc[1] = th[1];
+        cs[0] = th[2] * isig;
+        cs[1] = -th[2] * isig;
+        cs[2] = isig;
+    }
+    __device__ static bool prep_row(const double *z, int, const KstModelParams &, double *pc, double &varfac)
+    {
+        pc[0] = z[0];
+        varfac = 1.0;
+        return z[0] == 0.0;
+    }
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g)
+    {
+        const double t = pc[0];
+        const double A = exp(-dc[0] * t);
+        const double E = exp(-dc[1] * t);
+        g[0] = A * t;
+        g[1] = E * t;
+        g[2] = E - A;
+    }
+};
+
+struct KstVu : KstTpc {
+    __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
+    {
+        const double isig = 1.0 / sqrt(mp.v[0]);  // v[0] = sigma_squared
+        dc[0] = th[0];
+        dc[1] = th[1];
+        cs[0] = th[2] * isig;
+        cs[1] = -th[2] * isig;
+        cs[2] = isig;
+    }
+    __device__ static bool prep_row(const double *z, int i, const KstModelParams &, double *pc, double &varfac)
+    {
+        const double t = (double)i * z[0];
+        pc[0] = t;
+        varfac = 1.0 / (1.0 + t);
+        return t == 0.0;
+    }
+};

@@ -1,0 +1,359 @@
+// Objective evaluation: for every particle (design measure) of a swarm and every prior draw,
+// accumulate the weighted Fisher information, apply the transformation, evaluate the D / A
+// criterion, and prior-average.  Replaces the three nested serial loops of the reference:
+//   pso_evaluate_objective!  src/pso.jl:173-179            (particles)
+//   objective!               src/designproblem.jl:192-224  (prior draws)
+//   average_fishermatrix!    src/model-nonlinear-regression.jl:60-86 (design points)
+//
+// Mapping: CTA = (tile of KST_TILE_P particles) x (strided set of draw chunks).  Lanes run
+// along draws (coalesced SoA loads of the per-draw constants); all lanes of a warp share the
+// particle, so its compacted row list is read from shared memory as a broadcast.  The r x r
+// matrix, its LDL' factor and everything after live in FP64 registers.  Per particle one
+// fixed-order block reduction; per-CTA partial sums go to scratch [S][n_blk] and are summed in
+// fixed order by k_obj_finish, so results are bit-reproducible run to run.
+#include "kst_common.cuh"
+#include "kst_linalg.cuh"
+
+struct KstObjParams {
+    const double *pw, *dc, *aux;
+    size_t ld;
+    int64_t N;
+    const double *pts, *w;  // [S][K][d], [S][K]
+    int S, K;
+    double *partials;       // [S][n_blk]
+    KstModelParams mp;
+};
+
+// ------------------------------------------------------------------------------------------
+// per-draw preparation (once per problem)
+// ------------------------------------------------------------------------------------------
+template <class MF>
+__global__ void k_prep_draws(const double *__restrict__ theta_aos, const double *__restrict__ pw,
+                             const double *__restrict__ dt, int64_t N, size_t ld, int crit, int trafo,
+                             int t, KstModelParams mp, double *__restrict__ theta, double *__restrict__ dc,
+                             double *__restrict__ cs, double *__restrict__ aux, double *__restrict__ woff)
+{
+    constexpr int R = MF::R;
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= N) return;
+    double th[R], dcv[MF::NDC], csv[R];
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+        th[i] = theta_aos[j * R + i];
+        theta[(size_t)i * ld + j] = th[i];
+    }
+    MF::prep_draw(th, mp, dcv, csv);
+#pragma unroll
+    for (int i = 0; i < MF::NDC; i++) dc[(size_t)i * ld + j] = dcv[i];
+#pragma unroll
+    for (int i = 0; i < R; i++) cs[(size_t)i * ld + j] = csv[i];
+    double off = 0.0;
+    if (trafo == KST_TRAFO_IDENTITY) {
+        if (crit == KST_CRIT_D) {
+#pragma unroll
+            for (int i = 0; i < R; i++) off += log(csv[i] * csv[i]);
+            off *= pw[j];
+        } else {
+#pragma unroll
+            for (int i = 0; i < R; i++) aux[(size_t)i * ld + j] = 1.0 / (csv[i] * csv[i]);
+        }
+    } else {
+        for (int a = 0; a < t; a++)
+#pragma unroll
+            for (int i = 0; i < R; i++)
+                aux[(size_t)(a * R + i) * ld + j] = dt[j * (int64_t)(t * R) + a + i * t] / csv[i];
+    }
+    woff[j] = off;
+}
+
+// ------------------------------------------------------------------------------------------
+// shared-memory particle tile
+// ------------------------------------------------------------------------------------------
+template <class MF>
+struct KstTile {
+    static constexpr int RW = 1 + MF::NPC;  // doubles per row: omega, pc...
+    // layout (doubles): rows[P][rows_max][RW] | sumw[P] | wsum[P][NT/32] ; then ints nact[P]
+    __device__ static double *rows(double *s) { return s; }
+    __device__ static double *sumw(double *s, int rows_max) { return s + (size_t)KST_TILE_P * rows_max * RW; }
+    __device__ static double *wsum(double *s, int rows_max) { return sumw(s, rows_max) + KST_TILE_P; }
+    __device__ static int *nact(double *s, int rows_max) { return (int *)(wsum(s, rows_max) + KST_TILE_P * (KST_NT / 32)); }
+    __host__ static size_t bytes(int rows_max)
+    {
+        return sizeof(double) * ((size_t)KST_TILE_P * rows_max * RW + KST_TILE_P + KST_TILE_P * (KST_NT / 32)) +
+               sizeof(int) * KST_TILE_P;
+    }
+};
+
+// One thread per particle of the tile: map design points to rows (map_to_covariate! +
+// update_model_vcov!, src/design-common.jl:51-61, src/model-nonlinear-regression.jl:39-49),
+// hoist covariate-only transcendentals, drop trivial rows.
+template <class MF>
+__device__ __forceinline__ void kst_build_tile(double *smem, const double *__restrict__ pts,
+                                               const double *__restrict__ w, int p0, int S, int K,
+                                               const KstModelParams &mp)
+{
+    const int rows_max = K * mp.m;
+    if (threadIdx.x < KST_TILE_P) {
+        const int p = p0 + threadIdx.x;
+        double *rows = KstTile<MF>::rows(smem) + (size_t)threadIdx.x * rows_max * KstTile<MF>::RW;
+        int na = 0;
+        double sw = 0.0;
+        if (p < S) {
+            for (int k = 0; k < K; k++) {
+                const double *z = pts + ((size_t)p * K + k) * mp.d;
+                const double wk = w[(size_t)p * K + k];
+                for (int i = 0; i < mp.m; i++) {
+                    double pc[MF::NPC], varfac;
+                    const bool trivial = MF::prep_row(z, i, mp, pc, varfac);
+                    const double om = wk * varfac;
+                    sw += om;
+                    if (!trivial) {
+                        rows[na * KstTile<MF>::RW] = om;
+#pragma unroll
+                        for (int c = 0; c < MF::NPC; c++) rows[na * KstTile<MF>::RW + 1 + c] = pc[c];
+                        na++;
+                    }
+                }
+            }
+        }
+        KstTile<MF>::sumw(smem, rows_max)[threadIdx.x] = sw;
+        KstTile<MF>::nact(smem, rows_max)[threadIdx.x] = na;
+    }
+    __syncthreads();
+}
+
+template <class MF>
+__device__ __forceinline__ void kst_fisher(double *M, const double *__restrict__ rows, int na, double sw,
+                                           const double *dcv)
+{
+    constexpr int R = MF::R, RW = 1 + MF::NPC;
+#pragma unroll
+    for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
+#pragma unroll 2
+    for (int i = 0; i < na; i++) {
+        double g[R];
+        MF::row(rows + i * RW + 1, dcv, g);
+        kst_accum<R, MF::CONST_COL>(M, rows[i * RW], g);
+    }
+    constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
+    if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = sw;
+}
+
+// ------------------------------------------------------------------------------------------
+// the hot kernel
+// ------------------------------------------------------------------------------------------
+template <class MF, int CRIT, int T>
+__global__ void __launch_bounds__(KST_NT, 2) k_objective(const KstObjParams prm)
+{
+    constexpr int R = MF::R;
+    extern __shared__ double smem[];
+    const int rows_max = prm.K * prm.mp.m;
+    const int p0 = blockIdx.y * KST_TILE_P;
+    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int np = min(KST_TILE_P, prm.S - p0);
+    double *wsum = KstTile<MF>::wsum(smem, rows_max);
+    const int64_t stride = (int64_t)gridDim.x * KST_NT;
+
+    for (int p = 0; p < np; p++) {
+        const double *rows = KstTile<MF>::rows(smem) + (size_t)p * rows_max * KstTile<MF>::RW;
+        const int na = KstTile<MF>::nact(smem, rows_max)[p];
+        const double sw = KstTile<MF>::sumw(smem, rows_max)[p];
+        double acc = 0.0;
+        for (int64_t j = (int64_t)blockIdx.x * KST_NT + threadIdx.x; j < prm.N; j += stride) {
+            double dcv[MF::NDC];
+#pragma unroll
+            for (int c = 0; c < MF::NDC; c++) dcv[c] = __ldg(prm.dc + (size_t)c * prm.ld + j);
+            const double pwj = __ldg(prm.pw + j);
+            double M[KstPacked<R>::N];
+            kst_fisher<MF>(M, rows, na, sw, dcv);
+            bool exc;
+            const double val = kst_criterion<R, CRIT, T>(M, prm.aux + j, prm.ld, exc);
+            acc += exc ? -KST_INF : pwj * val;
+        }
+        // fixed-order reduction over the CTA's draws
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+        if (lane == 0) wsum[p * (KST_NT / 32) + warp] = acc;
+    }
+    __syncthreads();
+    if (threadIdx.x < np) {
+        double s = 0.0;
+#pragma unroll
+        for (int wi = 0; wi < KST_NT / 32; wi++) s += wsum[threadIdx.x * (KST_NT / 32) + wi];
+        prm.partials[(size_t)(p0 + threadIdx.x) * gridDim.x + blockIdx.x] = s;
+    }
+}
+
+__global__ void k_obj_finish(const double *__restrict__ partials, int n_blk, double offset,
+                             double *__restrict__ fx, int S)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= S) return;
+    double s = 0.0;
+    for (int b = 0; b < n_blk; b++) s += partials[(size_t)p * n_blk + b];
+    fx[p] = s + offset;
+}
+
+// informationmatrix for one draw (debugging aid of the reference, src/design-common.jl:96-112)
+template <class MF>
+__global__ void k_infomatrix(const double *dc, const double *cs, size_t ld, int64_t j, const double *pts,
+                             const double *w, int K, KstModelParams mp, double *Mout)
+{
+    constexpr int R = MF::R;
+    extern __shared__ double smem[];
+    kst_build_tile<MF>(smem, pts, w, 0, 1, K, mp);
+    if (threadIdx.x != 0) return;
+    const int rows_max = K * mp.m;
+    double dcv[MF::NDC], M[KstPacked<R>::N];
+    for (int c = 0; c < MF::NDC; c++) dcv[c] = dc[(size_t)c * ld + j];
+    kst_fisher<MF>(M, KstTile<MF>::rows(smem), KstTile<MF>::nact(smem, rows_max)[0],
+                   KstTile<MF>::sumw(smem, rows_max)[0], dcv);
+    for (int a = 0; a < R; a++)
+        for (int b = a; b < R; b++) {
+            const double v = M[kst_pidx<R>(a, b)] * cs[(size_t)a * ld + j] * cs[(size_t)b * ld + j];
+            Mout[a + b * R] = v;
+            Mout[b + a * R] = v;
+        }
+}
+
+// Deterministic sum of n doubles: 1024 threads take strided slices, then a fixed tree.
+__global__ void k_sum_fixed(const double *__restrict__ x, int64_t n, double *__restrict__ out)
+{
+    __shared__ double s[1024];
+    double a = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += 1024) a += x[i];
+    s[threadIdx.x] = a;
+    __syncthreads();
+    for (int o = 512; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) s[threadIdx.x] += s[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *out = s[0];
+}
+
+int kst_sum_fixed(kst_problem *h, const double *d_x, int64_t n, double *host_out)
+{
+    double *d_out = nullptr;
+    KST_CUDA(cudaMalloc(&d_out, sizeof(double)));
+    k_sum_fixed<<<1, 1024, 0, h->stream>>>(d_x, n, d_out);
+    KST_CUDA(cudaGetLastError());
+    KST_CUDA(cudaMemcpyAsync(host_out, d_out, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    KST_CUDA(cudaFree(d_out));
+    return KST_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// host-side dispatch
+// ------------------------------------------------------------------------------------------
+
+int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const double *d_dt)
+{
+    double *woff = nullptr;
+    KST_CUDA(cudaMalloc(&woff, sizeof(double) * h->N));
+    const int nt = 256;
+    const unsigned nb = (unsigned)((h->N + nt - 1) / nt);
+    KST_MODEL_SWITCH(h->model_id,
+                     (k_prep_draws<MF><<<nb, nt, 0, h->stream>>>(d_theta_aos, h->pw, d_dt, h->N, h->ld, h->crit,
+                                                                 h->trafo, h->t, h->mp, h->theta, h->dc, h->cs,
+                                                                 h->aux, woff)));
+    KST_CUDA(cudaGetLastError());
+    int rc = kst_sum_fixed(h, woff, h->N, &h->offset);
+    cudaFree(woff);
+    return rc;
+}
+
+int kst_objective_grid(const kst_problem *h, int S, int *n_blk)
+{
+    const int tiles = (S + KST_TILE_P - 1) / KST_TILE_P;
+    const int64_t max_chunks = (h->N + KST_NT - 1) / KST_NT;
+    const int cap = h->sm_count * 2;  // resident CTAs per wave at 2 CTAs/SM
+    // aim for >= 8 waves, then pick the draw split whose last wave is fullest
+    int64_t lo = (8LL * cap + tiles - 1) / tiles;
+    if (lo < 1) lo = 1;
+    int64_t best = lo;
+    double best_waste = 1e30;
+    for (int64_t nb = lo; nb < lo + cap; nb++) {
+        const int64_t tot = nb * tiles;
+        const int64_t waves = (tot + cap - 1) / cap;
+        const double waste = (double)(waves * cap - tot) / (double)tot;
+        if (waste < best_waste - 1e-12) { best_waste = waste; best = nb; }
+    }
+    if (best > max_chunks) best = max_chunks;
+    if (best < 1) best = 1;
+    if (best > 65535) best = 65535;
+    *n_blk = (int)best;
+    return tiles;
+}
+
+template <class MF, int CRIT>
+static int launch_obj_t(kst_problem *h, const KstObjParams &prm, dim3 grid, size_t smem)
+{
+    const int T = h->trafo == KST_TRAFO_IDENTITY ? 0 : h->t;
+#define KST_LAUNCH_T(TV)                                                                        \
+    case TV:                                                                                    \
+        if (TV <= MF::R) {                                                                      \
+            k_objective<MF, CRIT, (TV <= MF::R ? TV : 0)><<<grid, KST_NT, smem, h->stream>>>(prm); \
+            return KST_OK;                                                                      \
+        }                                                                                       \
+        break;
+    switch (T) {
+        KST_LAUNCH_T(0)
+        KST_LAUNCH_T(1)
+        KST_LAUNCH_T(2)
+        KST_LAUNCH_T(3)
+        KST_LAUNCH_T(4)
+        KST_LAUNCH_T(5)
+    }
+#undef KST_LAUNCH_T
+    kst_set_error("unsupported transformation dimension t = %d for r = %d", T, MF::R);
+    return KST_EINVAL;
+}
+
+int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *d_fx)
+{
+    if (S < 1 || K < 1 || K * h->m > KST_MAX_ROWS) {
+        kst_set_error("objective: need S >= 1, K >= 1, K*m <= %d (S=%d K=%d m=%d)", KST_MAX_ROWS, S, K, h->m);
+        return KST_EINVAL;
+    }
+    int n_blk = 1;
+    const int tiles = kst_objective_grid(h, S, &n_blk);
+    int rc = kst_ensure_partials(h, (size_t)S * n_blk);
+    if (rc) return rc;
+    KstObjParams prm;
+    prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.ld = h->ld; prm.N = h->N;
+    prm.pts = d_pts; prm.w = d_w; prm.S = S; prm.K = K; prm.partials = h->partials; prm.mp = h->mp;
+    const dim3 grid(n_blk, tiles);
+    if (h->prof_on) {
+        cudaEvent_t e0, e1;
+        KST_CUDA(cudaEventCreate(&e0));
+        KST_CUDA(cudaEventCreate(&e1));
+        h->prof_events.push_back(e0);
+        h->prof_events.push_back(e1);
+        KST_CUDA(cudaEventRecord(e0, h->stream));
+    }
+    KST_MODEL_SWITCH(h->model_id, {
+        const size_t smem = KstTile<MF>::bytes(K * h->m);
+        rc = h->crit == KST_CRIT_D ? launch_obj_t<MF, 0>(h, prm, grid, smem) : launch_obj_t<MF, 1>(h, prm, grid, smem);
+    });
+    if (rc) return rc;
+    KST_CUDA(cudaGetLastError());
+    if (h->prof_on) KST_CUDA(cudaEventRecord(h->prof_events.back(), h->stream));
+    k_obj_finish<<<(S + 127) / 128, 128, 0, h->stream>>>(h->partials, n_blk, h->offset, d_fx, S);
+    KST_CUDA(cudaGetLastError());
+    return KST_OK;
+}
+
+int kst_launch_infomatrix(kst_problem *h, int K, const double *d_pts, const double *d_w, int64_t draw, double *d_M)
+{
+    if (K < 1 || K * h->m > KST_MAX_ROWS || draw < 0 || draw >= h->N) {
+        kst_set_error("informationmatrix: bad K or draw index");
+        return KST_EINVAL;
+    }
+    KST_MODEL_SWITCH(h->model_id, (k_infomatrix<MF><<<1, 32, KstTile<MF>::bytes(K * h->m), h->stream>>>(
+                                      h->dc, h->cs, h->ld, draw, d_pts, d_w, K, h->mp, d_M)));
+    KST_CUDA(cudaGetLastError());
+    return KST_OK;
+}

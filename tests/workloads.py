@@ -1,0 +1,44 @@
+"""Seeded synthetic inputs for the BASELINE.json configs, shared by tests and bench.py."""
+import numpy as np
+
+
+def emax_prior(n, seed=1):
+    rng = np.random.default_rng(seed)
+    return np.column_stack([rng.normal(1, 0.5, n), rng.normal(10, 2, n), np.exp(rng.normal(np.log(5), 0.3, n))])
+
+
+def sigemax_prior(n, seed=31415):  # docs/src/tutorial.md:190-196
+    rng = np.random.default_rng(seed)
+    return np.array([1, 2, 0.4, 5]) + np.array([0.5, 0.5, 0.05, 0.5]) * rng.standard_normal((n, 4))
+
+
+def tpc_prior(n, seed=3, se_factor=2):  # test/example-compartment.jl:74-82 (draw_from_prior)
+    rng = np.random.default_rng(seed)
+    a = 4.298 + se_factor * 0.5 * (2 * rng.random(n) - 1)
+    e = 0.05884 + se_factor * 0.005 * (2 * rng.random(n) - 1)
+    return np.column_stack([a, e, np.full(n, 21.8)])
+
+
+def ded90_jacobians(theta, rho=90.0):  # docs/src/autodiff.md:257-266 (DED_manual)
+    a = (100 / rho - 1) ** (1 / theta[:, 3])
+    dt = np.zeros((len(theta), 1, 4))
+    dt[:, 0, 2] = 1 / a
+    dt[:, 0, 3] = theta[:, 2] * np.log(100 / rho - 1) / (theta[:, 3] ** 2 * a)
+    return dt
+
+
+def random_swarm(S, K, lb, ub, seed=0, prototype=None):
+    """Particle 0 = equidistant prototype, others uniform points + Exp(1)-normalised weights
+    (the reference's own initialiser, src/designmeasure-abstractpoint.jl:73-107)."""
+    rng = np.random.default_rng(seed)
+    lb, ub = np.atleast_1d(np.asarray(lb, float)), np.atleast_1d(np.asarray(ub, float))
+    d = len(lb)
+    pts = lb + (ub - lb) * rng.random((S, K, d))
+    v = -np.log(1.0 - rng.random((S, K)))
+    w = v / v.sum(axis=1, keepdims=True)
+    if prototype is None:
+        pts[0] = np.linspace(lb, ub, K).reshape(K, d)
+        w[0] = 1.0 / K
+    else:
+        pts[0], w[0] = prototype
+    return pts, w
