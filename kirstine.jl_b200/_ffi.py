@@ -46,6 +46,7 @@ SIGNATURES = {
     "kst_profile_enable": (C.c_int, [_vp, C.c_int]),
     "kst_profile_read": (C.c_int, [_vp, _dp, C.POINTER(C.c_int64)]),
     "kst_fp64_peak_probe": (C.c_int, [C.c_int, _dp]),
+    "kst_math_selftest": (C.c_int, [C.c_int, C.c_int64, _dp, _dp, _dp]),
 }
 
 _lib = None
@@ -250,3 +251,10 @@ def fp64_peak_probe(device=0):
     tf = C.c_double(0)
     check(lib().kst_fp64_peak_probe(device, C.byref(tf)))
     return tf.value
+
+
+def math_selftest(x, device=0):
+    x = f64(x).ravel()
+    e, r = np.empty_like(x), np.empty_like(x)
+    check(lib().kst_math_selftest(device, len(x), ptr(x), ptr(e), ptr(r)))
+    return e, r

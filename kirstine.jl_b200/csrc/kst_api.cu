@@ -608,3 +608,29 @@ extern "C" int kst_fp64_peak_probe(int device_id, double *tflops)
     if (tflops) *tflops = best;
     return KST_OK;
 }
+
+__global__ void k_math_selftest(int64_t n, const double *__restrict__ x, double *__restrict__ e, double *__restrict__ r)
+{
+    __shared__ double s_exptab[KST_EXP_TAB_N];
+    kst_math_init(s_exptab);
+    __syncthreads();
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    e[i] = kst_exp(x[i], s_exptab);
+    r[i] = kst_rcp(x[i]);
+}
+
+extern "C" int kst_math_selftest(int device_id, int64_t n, const double *x, double *exp_out, double *rcp_out)
+{
+    if (n < 1 || !x || !exp_out || !rcp_out) { kst_set_error("math_selftest: bad arguments"); return KST_EINVAL; }
+    KST_CUDA(cudaSetDevice(device_id));
+    double *d = nullptr;
+    KST_CUDA(cudaMalloc(&d, sizeof(double) * 3 * n));
+    KST_CUDA(cudaMemcpy(d, x, sizeof(double) * n, cudaMemcpyHostToDevice));
+    k_math_selftest<<<(unsigned)((n + 255) / 256), 256>>>(n, d, d + n, d + 2 * n);
+    KST_CUDA(cudaGetLastError());
+    KST_CUDA(cudaMemcpy(exp_out, d + n, sizeof(double) * n, cudaMemcpyDeviceToHost));
+    KST_CUDA(cudaMemcpy(rcp_out, d + 2 * n, sizeof(double) * n, cudaMemcpyDeviceToHost));
+    KST_CUDA(cudaFree(d));
+    return KST_OK;
+}

@@ -21,11 +21,11 @@
 
 // rows of one design measure (single thread): map_to_covariate! + update_model_vcov! + compaction
 template <class MF>
-__device__ __forceinline__ int kst_build_rows(double *rows, double &sw, const double *pts, const double *w, int K,
-                                              const KstModelParams &mp)
+__device__ __forceinline__ int kst_build_rows(double *rows, double &sw, int &rank, const double *pts, const double *w,
+                                              int K, const KstModelParams &mp)
 {
     constexpr int RW = 1 + MF::NPC;
-    int na = 0;
+    int na = 0, ntriv = 0;
     sw = 0.0;
     for (int k = 0; k < K; k++) {
         const double *z = pts + (size_t)k * mp.d;
@@ -34,13 +34,17 @@ __device__ __forceinline__ int kst_build_rows(double *rows, double &sw, const do
             const bool trivial = MF::prep_row(z, i, mp, pc, varfac);
             const double om = w[k] * varfac;
             sw += om;
+            if (om == 0.0) continue;  // zero weight: contributes nothing, not even rank
             if (!trivial) {
                 rows[na * RW] = om;
                 for (int c = 0; c < MF::NPC; c++) rows[na * RW + 1 + c] = pc[c];
                 na++;
+            } else {
+                ntriv++;
             }
         }
     }
+    rank = na + ((MF::CONST_COL >= 0 && ntriv > 0) ? 1 : 0);
     return na;
 }
 
@@ -53,13 +57,17 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
                                   double *__restrict__ gtrB, double *__restrict__ wtrB, int *flag)
 {
     constexpr int R = MF::R, RW = 1 + MF::NPC;
-    extern __shared__ double smem[];  // rows[K*m][RW], sw, na
+    extern __shared__ double smem[];  // rows[K*m][RW], sw, (na, rank)
+    __shared__ double s_exptab[KST_EXP_TAB_N];
+    kst_math_init(s_exptab);
     double *rows = smem;
     double *s_sw = smem + (size_t)K * mp.m * RW;
     int *s_na = (int *)(s_sw + 1);
     if (threadIdx.x == 0) {
         double sw;
-        *s_na = kst_build_rows<MF>(rows, sw, pts, w, K, mp);
+        int rank;
+        s_na[0] = kst_build_rows<MF>(rows, sw, rank, pts, w, K, mp);
+        s_na[1] = rank;
         *s_sw = sw;
     }
     __syncthreads();
@@ -73,7 +81,7 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
     const int na = *s_na;
     for (int i = 0; i < na; i++) {
         double g[R];
-        MF::row(rows + i * RW + 1, dcv, g);
+        MF::row(rows + i * RW + 1, dcv, g, s_exptab);
         kst_accum<R, MF::CONST_COL>(M, rows[i * RW], g);
     }
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
@@ -81,6 +89,7 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
 
     double L[R][R], dv[R], dinv[R];
     bool ok = kst_ldlt<R>(M, L, dv, dinv, true);
+    ok = ok && s_na[1] >= R;  // fewer rows than parameters: singular by construction
     // Mt^-1 = Li' diag(dinv) Li with Li = L^-1 (unit lower)
     double Li[R][R];
 #pragma unroll
@@ -232,6 +241,8 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
 {
     constexpr int R = MF::R, RW = 1 + MF::NPC, NP = KstPacked<R>::N, NS = MF::NDC + NP;
     extern __shared__ double smem[];
+    __shared__ double s_exptab[KST_EXP_TAB_N];
+    kst_math_init(s_exptab);  // visible after the first __syncthreads() of the chunk loop
     double *s_draw = smem;                                  // [NS][KST_GD_CHUNK]
     double *s_rows = smem + (size_t)NS * KST_GD_CHUNK;      // [m][RW][KST_GD_NT]
     const int m = mp.m;
@@ -289,7 +300,7 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
                 const double om = s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x];
 #pragma unroll
                 for (int c = 0; c < MF::NPC; c++) pc[c] = s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x];
-                MF::row(pc, dcv, gv);
+                MF::row(pc, dcv, gv, s_exptab);
                 double q = 0.0;
 #pragma unroll
                 for (int a = 0; a < R; a++) {

@@ -11,6 +11,8 @@
 #pragma once
 #include <math.h>
 
+#include "kst_math.cuh"
+
 #define KST_INF (__longlong_as_double(0x7ff0000000000000LL))
 
 template <int R>
@@ -57,7 +59,7 @@ __device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], dou
         for (int k = 0; k < j; k++) dj = fma(-L[j][k], W[j][k], dj);
         dv[j] = dj;
         ok = ok && (dj > 0.0);
-        if (j < R - 1 || need_last_inv) dinv[j] = 1.0 / dj;
+        if (j < R - 1 || need_last_inv) dinv[j] = kst_rcp(dj);  // garbage when dj <= 0, but then ok == false
 #pragma unroll
         for (int i = j + 1; i < R; i++) {
             double v = M[kst_pidx<R>(j, i)];

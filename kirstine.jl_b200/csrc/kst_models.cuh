@@ -20,6 +20,8 @@
 #pragma once
 #include <math.h>
 
+#include "kst_math.cuh"
+
 struct KstModelParams {
     double v[4];
     int m;   // unit length
@@ -46,9 +48,9 @@ struct KstEmax {
         varfac = 1.0;
         return z[0] == 0.0;
     }
-    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g)
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g, const double *)
     {
-        const double rho = 1.0 / (pc[0] + dc[0]);
+        const double rho = kst_rcp(pc[0] + dc[0]);
         const double a = pc[0] * rho;
         g[0] = 1.0;
         g[1] = a;
@@ -57,19 +59,20 @@ struct KstEmax {
 };
 
 // sigmoid Emax: docs/src/tutorial.md:127-142.
-//   A = x^h/(x^h+ed50^h) = 1/(1+e),  e = exp(-h (log x - log ed50)),  A B = emax e/(1+e)^2
-//   row = [1, A, -A B h/ed50, A B log(x/ed50)],  dose == 0 -> [1, 0, 0, 0]
+//   A = x^h/(x^h+ed50^h) = 1/(1+e),  e = exp(q),  q = h (log ed50 - log x),  A B = emax e/(1+e)^2
+//   row = [1, A, -A B h/ed50, A B log(x/ed50)] = diag(1, 1, -emax h/ed50, -emax/h) [1, A, u, u q]
+//   dose == 0 -> [1, 0, 0, 0] (trivial row)
 struct KstSigEmax {
     static constexpr int R = 4, NDC = 2, NPC = 1, CONST_COL = 0, D_MIN = 1;
     __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
     {
         const double isig = 1.0 / fabs(mp.v[0]);  // v[0] = sigma
-        dc[0] = log(th[2]);
-        dc[1] = th[3];
+        dc[0] = th[3];
+        dc[1] = th[3] * log(th[2]);
         cs[0] = isig;
         cs[1] = isig;
         cs[2] = -th[1] * th[3] / th[2] * isig;
-        cs[3] = th[1] * isig;
+        cs[3] = -th[1] / th[3] * isig;
     }
     __device__ static bool prep_row(const double *z, int, const KstModelParams &, double *pc, double &varfac)
     {
@@ -77,17 +80,17 @@ struct KstSigEmax {
         varfac = 1.0;
         return z[0] == 0.0;
     }
-    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g)
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g, const double *tab)
     {
-        const double L = pc[0] - dc[0];
-        // clamp keeps e finite so that u = e/(1+e)^2 never becomes Inf*0
-        const double e = exp(fmin(-dc[1] * L, 700.0));
-        const double rr = 1.0 / (1.0 + e);
+        const double q = fma(-dc[0], pc[0], dc[1]);
+        // |q| is clamped at 700 so that e stays finite and u = e/(1+e)^2 never becomes Inf*0
+        const double e = kst_exp_clamped(q, tab);
+        const double rr = kst_rcp(1.0 + e);
         const double u = e * rr * rr;
         g[0] = 1.0;
         g[1] = rr;
         g[2] = u;
-        g[3] = u * L;
+        g[3] = u * q;
     }
 };
 
@@ -112,11 +115,11 @@ struct KstTpc {
         varfac = 1.0;
         return z[0] == 0.0;
     }
-    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g)
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g, const double *tab)
     {
         const double t = pc[0];
-        const double A = exp(-dc[0] * t);
-        const double E = exp(-dc[1] * t);
+        const double A = kst_exp(-dc[0] * t, tab);
+        const double E = kst_exp(-dc[1] * t, tab);
         g[0] = A * t;
         g[1] = E * t;
         g[2] = E - A;

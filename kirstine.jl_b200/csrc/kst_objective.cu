@@ -72,15 +72,17 @@ __global__ void k_prep_draws(const double *__restrict__ theta_aos, const double 
 template <class MF>
 struct KstTile {
     static constexpr int RW = 1 + MF::NPC;  // doubles per row: omega, pc...
-    // layout (doubles): rows[P][rows_max][RW] | sumw[P] | wsum[P][NT/32] ; then ints nact[P]
+    // layout (doubles): rows[P][rows_max][RW] | sumw[P] | wsum[P][NT/32] ; then ints nact[P], rank[P]
     __device__ static double *rows(double *s) { return s; }
     __device__ static double *sumw(double *s, int rows_max) { return s + (size_t)KST_TILE_P * rows_max * RW; }
     __device__ static double *wsum(double *s, int rows_max) { return sumw(s, rows_max) + KST_TILE_P; }
     __device__ static int *nact(double *s, int rows_max) { return (int *)(wsum(s, rows_max) + KST_TILE_P * (KST_NT / 32)); }
+    // upper bound on rank(Mt): below R the design is singular whatever the rounding does
+    __device__ static int *rank(double *s, int rows_max) { return nact(s, rows_max) + KST_TILE_P; }
     __host__ static size_t bytes(int rows_max)
     {
         return sizeof(double) * ((size_t)KST_TILE_P * rows_max * RW + KST_TILE_P + KST_TILE_P * (KST_NT / 32)) +
-               sizeof(int) * KST_TILE_P;
+               sizeof(int) * 2 * KST_TILE_P;
     }
 };
 
@@ -96,7 +98,7 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
     if (threadIdx.x < KST_TILE_P) {
         const int p = p0 + threadIdx.x;
         double *rows = KstTile<MF>::rows(smem) + (size_t)threadIdx.x * rows_max * KstTile<MF>::RW;
-        int na = 0;
+        int na = 0, ntriv = 0;
         double sw = 0.0;
         if (p < S) {
             for (int k = 0; k < K; k++) {
@@ -107,24 +109,28 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
                     const bool trivial = MF::prep_row(z, i, mp, pc, varfac);
                     const double om = wk * varfac;
                     sw += om;
+                    if (om == 0.0) continue;  // zero weight: contributes nothing, not even rank
                     if (!trivial) {
                         rows[na * KstTile<MF>::RW] = om;
 #pragma unroll
                         for (int c = 0; c < MF::NPC; c++) rows[na * KstTile<MF>::RW + 1 + c] = pc[c];
                         na++;
+                    } else {
+                        ntriv++;
                     }
                 }
             }
         }
         KstTile<MF>::sumw(smem, rows_max)[threadIdx.x] = sw;
         KstTile<MF>::nact(smem, rows_max)[threadIdx.x] = na;
+        KstTile<MF>::rank(smem, rows_max)[threadIdx.x] = na + ((MF::CONST_COL >= 0 && ntriv > 0) ? 1 : 0);
     }
     __syncthreads();
 }
 
 template <class MF>
 __device__ __forceinline__ void kst_fisher(double *M, const double *__restrict__ rows, int na, double sw,
-                                           const double *dcv)
+                                           const double *dcv, const double *tab)
 {
     constexpr int R = MF::R, RW = 1 + MF::NPC;
 #pragma unroll
@@ -132,7 +138,7 @@ __device__ __forceinline__ void kst_fisher(double *M, const double *__restrict__
 #pragma unroll 2
     for (int i = 0; i < na; i++) {
         double g[R];
-        MF::row(rows + i * RW + 1, dcv, g);
+        MF::row(rows + i * RW + 1, dcv, g, tab);
         kst_accum<R, MF::CONST_COL>(M, rows[i * RW], g);
     }
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
@@ -147,19 +153,25 @@ __global__ void __launch_bounds__(KST_NT, 2) k_objective(const KstObjParams prm)
 {
     constexpr int R = MF::R;
     extern __shared__ double smem[];
+    __shared__ double s_exptab[KST_EXP_TAB_N];
     const int rows_max = prm.K * prm.mp.m;
     const int p0 = blockIdx.y * KST_TILE_P;
-    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp);
+    kst_math_init(s_exptab);
+    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp);  // ends with __syncthreads()
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int np = min(KST_TILE_P, prm.S - p0);
     double *wsum = KstTile<MF>::wsum(smem, rows_max);
     const int64_t stride = (int64_t)gridDim.x * KST_NT;
 
+#pragma unroll 1
     for (int p = 0; p < np; p++) {
         const double *rows = KstTile<MF>::rows(smem) + (size_t)p * rows_max * KstTile<MF>::RW;
         const int na = KstTile<MF>::nact(smem, rows_max)[p];
         const double sw = KstTile<MF>::sumw(smem, rows_max)[p];
+        // fewer rows than parameters: singular by construction (one-point designs etc.); the reference
+        // reaches the same -Inf through an exactly zero pivot
+        const bool rank_deficient = KstTile<MF>::rank(smem, rows_max)[p] < R;
         double acc = 0.0;
         for (int64_t j = (int64_t)blockIdx.x * KST_NT + threadIdx.x; j < prm.N; j += stride) {
             double dcv[MF::NDC];
@@ -167,9 +179,13 @@ __global__ void __launch_bounds__(KST_NT, 2) k_objective(const KstObjParams prm)
             for (int c = 0; c < MF::NDC; c++) dcv[c] = __ldg(prm.dc + (size_t)c * prm.ld + j);
             const double pwj = __ldg(prm.pw + j);
             double M[KstPacked<R>::N];
-            kst_fisher<MF>(M, rows, na, sw, dcv);
+            kst_fisher<MF>(M, rows, na, sw, dcv, s_exptab);
             bool exc;
-            const double val = kst_criterion<R, CRIT, T>(M, prm.aux + j, prm.ld, exc);
+            double val = kst_criterion<R, CRIT, T>(M, prm.aux + j, prm.ld, exc);
+            if (rank_deficient) {
+                val = -KST_INF;
+                exc = !(CRIT == 0 && T == 0);
+            }
             acc += exc ? -KST_INF : pwj * val;
         }
         // fixed-order reduction over the CTA's draws
@@ -203,13 +219,15 @@ __global__ void k_infomatrix(const double *dc, const double *cs, size_t ld, int6
 {
     constexpr int R = MF::R;
     extern __shared__ double smem[];
+    __shared__ double s_exptab[KST_EXP_TAB_N];
+    kst_math_init(s_exptab);
     kst_build_tile<MF>(smem, pts, w, 0, 1, K, mp);
     if (threadIdx.x != 0) return;
     const int rows_max = K * mp.m;
     double dcv[MF::NDC], M[KstPacked<R>::N];
     for (int c = 0; c < MF::NDC; c++) dcv[c] = dc[(size_t)c * ld + j];
     kst_fisher<MF>(M, KstTile<MF>::rows(smem), KstTile<MF>::nact(smem, rows_max)[0],
-                   KstTile<MF>::sumw(smem, rows_max)[0], dcv);
+                   KstTile<MF>::sumw(smem, rows_max)[0], dcv, s_exptab);
     for (int a = 0; a < R; a++)
         for (int b = a; b < R; b++) {
             const double v = M[kst_pidx<R>(a, b)] * cs[(size_t)a * ld + j] * cs[(size_t)b * ld + j];

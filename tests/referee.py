@@ -1,0 +1,154 @@
+"""Extended-precision referee (x87 80-bit long double, 64-bit mantissa) for objective and
+Gateaux-derivative values.
+
+Used to arbitrate engine-vs-oracle disagreements on ill-conditioned designs: random swarm
+particles often have cond(M) >= 1e8, where the reference's own double arithmetic is only good to
+1e-8 and a 1e-10 engine-vs-oracle comparison is meaningless.  `assert_parity` accepts a value when
+it is within the north-star tolerance of the oracle, or at least as close to the referee as the
+oracle is (up to a small factor).  Test infrastructure only.
+"""
+import numpy as np
+
+LD = np.longdouble
+
+
+def rows(model, mp, z, theta, m=1):
+    """Whitened Jacobian rows of one design point for all draws: (N, m, r) long double."""
+    th = theta.astype(LD)
+    z = LD(z)
+    N = len(th)
+    if model == 1:  # Emax, mp = sigma_squared
+        e0, emax, ec50 = th.T
+        g = np.stack([np.ones(N, LD), z / (z + ec50), -emax * z / (z + ec50) ** 2], axis=1)[:, None, :]
+        return g / np.sqrt(LD(mp[0]))
+    if model == 2:  # sigmoid Emax, mp = sigma
+        e0, emax, ed50, h = th.T
+        if z == 0:
+            g = np.stack([np.ones(N, LD), np.zeros(N, LD), np.zeros(N, LD), np.zeros(N, LD)], axis=1)
+        else:
+            xp, ep = z ** h, ed50 ** h
+            A = xp / (xp + ep)
+            B = ep * emax / (xp + ep)
+            g = np.stack([np.ones(N, LD), A, -A * B * h / ed50, A * B * np.log(z / ed50)], axis=1)
+        return g[:, None, :] / abs(LD(mp[0]))
+    if model in (3, 4):  # TPC (mp = sigma) / VU (mp = sigma_squared), times (i) * z
+        a, e, s = th.T
+        out = []
+        for i in range(m):
+            t = z if model == 3 else LD(i) * z
+            A, E = np.exp(-a * t), np.exp(-e * t)
+            g = np.stack([A * s * t, -E * s * t, E - A], axis=1)
+            var = LD(mp[0]) ** 2 if model == 3 else LD(mp[0]) * (1 + t)
+            out.append(g / np.sqrt(var))
+        return np.stack(out, axis=1)
+    raise KeyError(model)
+
+
+def infomatrix(model, mp, pts, w, theta, m=1):
+    pts = np.asarray(pts, dtype=np.float64).reshape(-1)
+    M = 0
+    for z, wk in zip(pts, np.asarray(w, dtype=np.float64)):
+        g = rows(model, mp, z, theta, m)
+        M = M + LD(wk) * np.einsum("nia,nib->nab", g, g)
+    return M
+
+
+def inv_spd(M):
+    """Batched inverse by Gauss-Jordan (no pivoting; M is SPD) and a flag for non-positive pivots."""
+    M = M.copy()
+    n = M.shape[-1]
+    I = np.broadcast_to(np.eye(n, dtype=LD), M.shape).copy()
+    ok = np.ones(M.shape[0], bool)
+    logdet = np.zeros(M.shape[0], LD)
+    for c in range(n):
+        piv = M[:, c, c].copy()
+        ok &= piv > 0
+        with np.errstate(all="ignore"):
+            logdet += np.log(np.where(piv > 0, piv, 1))
+            M[:, c, :] /= piv[:, None]
+            I[:, c, :] /= piv[:, None]
+            for a in range(n):
+                if a != c:
+                    f = M[:, a, c].copy()
+                    M[:, a, :] -= f[:, None] * M[:, c, :]
+                    I[:, a, :] -= f[:, None] * I[:, c, :]
+    return I, ok, logdet
+
+
+def objective(model, mp, pts, w, theta, pw, crit=0, dt=None, m=1):
+    M = infomatrix(model, mp, pts, w, theta, m)
+    iM, ok, logdet = inv_spd(M)
+    if not ok.all():
+        return -np.inf
+    if dt is None:
+        val = logdet if crit == 0 else -np.trace(iM, axis1=1, axis2=2)
+    else:
+        D = dt.astype(LD)
+        C = np.einsum("nai,nij,nbj->nab", D, iM, D)
+        if crit == 1:
+            val = -np.trace(C, axis1=1, axis2=2)
+        else:
+            _, ok2, ld2 = inv_spd(C)
+            if not ok2.all():
+                return -np.inf
+            val = -ld2
+    return float(np.sum(pw.astype(LD) * val))
+
+
+def gateaux(model, mp, at_pts, at_w, dirs, theta, pw, crit=0, dt=None, m=1):
+    M = infomatrix(model, mp, at_pts, at_w, theta, m)
+    iM, ok, _ = inv_spd(M)
+    assert ok.all()
+    r = M.shape[-1]
+    if dt is None:
+        if crit == 0:
+            A, trB = iM, np.full(len(M), LD(r))
+        else:
+            A, trB = np.einsum("nab,nbc->nac", iM, iM), np.trace(iM, axis1=1, axis2=2)
+    else:
+        D = dt.astype(LD)
+        C = np.einsum("nai,nij,nbj->nab", D, iM, D)
+        if crit == 0:
+            W, okc, _ = inv_spd(C)
+            assert okc.all()
+            A = np.einsum("nij,naj,nab,nbk,nkl->nil", iM, D, W, D, iM)
+            trB = np.full(len(M), LD(D.shape[1]))
+        else:
+            A = np.einsum("nij,naj,nak,nkl->nil", iM, D, D, iM)
+            trB = np.trace(C, axis1=1, axis2=2)
+    out = []
+    for z in np.asarray(dirs, dtype=np.float64).reshape(-1):
+        Md = infomatrix(model, mp, [z], [1.0], theta, m)
+        out.append(float(np.sum(pw.astype(LD) * (np.einsum("nab,nab->n", A, Md) - trB))))
+    return np.array(out)
+
+
+def assert_parity(got, oracle, referee_fn, rtol=1e-10, slack=64.0, scale=None):
+    """got/oracle: arrays.  referee_fn(i) -> extended-precision value of element i (called only where
+    got and oracle disagree beyond rtol).  scale: magnitude for absolute comparison (Gateaux values
+    cross zero), default |oracle| elementwise."""
+    got, oracle = np.asarray(got, float), np.asarray(oracle, float)
+    assert got.shape == oracle.shape
+    sc = np.abs(oracle) if scale is None else np.full(got.shape, float(scale))
+    bad = []
+    for i in range(got.size):
+        g, o = got.flat[i], oracle.flat[i]
+        if np.isnan(o) or np.isinf(o):
+            # the oracle's +-Inf / NaN on numerically singular designs is rounding luck unless the design is
+            # structurally singular; structural cases are asserted separately by the callers
+            continue
+        if abs(g - o) <= rtol * sc.flat[i]:
+            continue
+        ref = referee_fn(i)
+        if not np.isfinite(ref):
+            continue
+        eg, eo = abs(g - ref), abs(o - ref)
+        bar = rtol * max(sc.flat[i], abs(ref))
+        if eg <= bar:
+            continue
+        # the oracle itself is at (or within 10x of) the bar: the design is ill-conditioned for double
+        # arithmetic, so only ask the engine to be of the same quality as the reference arithmetic
+        if eo >= 0.1 * bar and eg <= slack * eo:
+            continue
+        bad.append((i, g, o, ref))
+    assert not bad, "engine further from the extended-precision referee than the oracle: %r" % bad[:5]

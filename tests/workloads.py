@@ -42,3 +42,18 @@ def random_swarm(S, K, lb, ub, seed=0, prototype=None):
     else:
         pts[0], w[0] = prototype
     return pts, w
+
+
+def jittered_swarm(S, K, lb, ub, seed=0, log_lo=None):
+    """Well-separated random designs for parity tests: point k is drawn inside the k-th of K equal
+    cells (of [lb, ub], or of [log_lo, ub] on the log scale), weights are Dirichlet(4,...,4).
+    Random i.i.d. points (random_swarm) are often numerically singular, where even the reference's
+    own arithmetic is rounding noise."""
+    rng = np.random.default_rng(seed)
+    u = (np.arange(K) + 0.15 + 0.7 * rng.random((S, K))) / K
+    if log_lo is None:
+        pts = lb + (ub - lb) * u
+    else:
+        pts = np.exp(np.log(log_lo) + u * (np.log(ub) - np.log(log_lo)))
+    w = rng.dirichlet(np.full(K, 4.0), size=S)
+    return pts.reshape(S, K, 1), w
