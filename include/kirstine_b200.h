@@ -184,9 +184,11 @@ KST_API int kst_pso_get_state(kst_problem *h, double *x_points, double *x_weight
 KST_API int kst_profile_enable(kst_problem *h, int on);
 KST_API int kst_profile_read(kst_problem *h, double *total_ms, int64_t *launches);
 KST_API int kst_fp64_peak_probe(int device_id, double *tflops);
-/* accuracy self-test of the engine's own FP64 exp and reciprocal (csrc/kst_math.cuh): evaluates them on
- * n host-supplied arguments; rcp_out[i] = 1/x[i] is only meaningful for normal, non-zero x[i]. */
-KST_API int kst_math_selftest(int device_id, int64_t n, const double *x, double *exp_out, double *rcp_out);
+/* accuracy self-test of the engine's own FP64 exp, reciprocal and log (csrc/kst_math.cuh) on n host-supplied
+ * arguments: exp_out[i] = exp(x[i]), rcp_out[i] = 1/x[i], log_out[i] = log|x[i]| (the latter two are only
+ * meaningful for normal, non-zero x[i]). */
+KST_API int kst_math_selftest(int device_id, int64_t n, const double *x, double *exp_out, double *rcp_out,
+                              double *log_out);
 
 #ifdef __cplusplus
 }

@@ -9,7 +9,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libkirstine_b200.so")
+# KST_LIB_PATH selects an alternative build of the same library (kernel tuning experiments)
+LIB_PATH = os.environ.get("KST_LIB_PATH") or os.path.join(_HERE, "libkirstine_b200.so")
 
 MODEL_EMAX, MODEL_SIGEMAX, MODEL_TPC, MODEL_VU = 1, 2, 3, 4
 CP_COPY, CP_EQUITIME = 0, 1
@@ -46,7 +47,7 @@ SIGNATURES = {
     "kst_profile_enable": (C.c_int, [_vp, C.c_int]),
     "kst_profile_read": (C.c_int, [_vp, _dp, C.POINTER(C.c_int64)]),
     "kst_fp64_peak_probe": (C.c_int, [C.c_int, _dp]),
-    "kst_math_selftest": (C.c_int, [C.c_int, C.c_int64, _dp, _dp, _dp]),
+    "kst_math_selftest": (C.c_int, [C.c_int, C.c_int64, _dp, _dp, _dp, _dp]),
 }
 
 _lib = None
@@ -255,6 +256,6 @@ def fp64_peak_probe(device=0):
 
 def math_selftest(x, device=0):
     x = f64(x).ravel()
-    e, r = np.empty_like(x), np.empty_like(x)
-    check(lib().kst_math_selftest(device, len(x), ptr(x), ptr(e), ptr(r)))
-    return e, r
+    e, r, l = np.empty_like(x), np.empty_like(x), np.empty_like(x)
+    check(lib().kst_math_selftest(device, len(x), ptr(x), ptr(e), ptr(r), ptr(l)))
+    return e, r, l

@@ -45,6 +45,20 @@ def _compile(src, verbose):
     return src, r.stderr
 
 
+def build_variant(name, defines):
+    """Tuning helper: build lib<name>.so with extra -D flags into its own object directory."""
+    global OBJ, LIB, COMMON
+    saved = (OBJ, LIB, COMMON)
+    try:
+        OBJ = os.path.join(HERE, "build", name)
+        os.makedirs(os.path.join(HERE, "variants"), exist_ok=True)
+        LIB = os.path.join(HERE, "variants", "lib%s.so" % name)
+        COMMON = COMMON + ["-D" + d for d in defines]
+        return build(force=False)
+    finally:
+        OBJ, LIB, COMMON = saved
+
+
 def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
     hdrs = _headers()
@@ -66,4 +80,8 @@ def build(force=False, verbose=False):
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))
+    if "--variant" in sys.argv:
+        i = sys.argv.index("--variant")
+        print(build_variant(sys.argv[i + 1], sys.argv[i + 2:]))
+    else:
+        print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

@@ -609,28 +609,32 @@ extern "C" int kst_fp64_peak_probe(int device_id, double *tflops)
     return KST_OK;
 }
 
-__global__ void k_math_selftest(int64_t n, const double *__restrict__ x, double *__restrict__ e, double *__restrict__ r)
+__global__ void k_math_selftest(int64_t n, const double *__restrict__ x, double *__restrict__ e, double *__restrict__ r,
+                                double *__restrict__ l)
 {
-    __shared__ double s_exptab[KST_EXP_TAB_N];
-    kst_math_init(s_exptab);
+    __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
+    const KstTab tab = kst_math_init(s_mathtab);
     __syncthreads();
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    e[i] = kst_exp(x[i], s_exptab);
+    e[i] = kst_exp(x[i], tab);
     r[i] = kst_rcp(x[i]);
+    l[i] = kst_log(fabs(x[i]), tab);
 }
 
-extern "C" int kst_math_selftest(int device_id, int64_t n, const double *x, double *exp_out, double *rcp_out)
+extern "C" int kst_math_selftest(int device_id, int64_t n, const double *x, double *exp_out, double *rcp_out,
+                                 double *log_out)
 {
-    if (n < 1 || !x || !exp_out || !rcp_out) { kst_set_error("math_selftest: bad arguments"); return KST_EINVAL; }
+    if (n < 1 || !x || !exp_out || !rcp_out || !log_out) { kst_set_error("math_selftest: bad arguments"); return KST_EINVAL; }
     KST_CUDA(cudaSetDevice(device_id));
     double *d = nullptr;
-    KST_CUDA(cudaMalloc(&d, sizeof(double) * 3 * n));
+    KST_CUDA(cudaMalloc(&d, sizeof(double) * 4 * n));
     KST_CUDA(cudaMemcpy(d, x, sizeof(double) * n, cudaMemcpyHostToDevice));
-    k_math_selftest<<<(unsigned)((n + 255) / 256), 256>>>(n, d, d + n, d + 2 * n);
+    k_math_selftest<<<(unsigned)((n + 255) / 256), 256>>>(n, d, d + n, d + 2 * n, d + 3 * n);
     KST_CUDA(cudaGetLastError());
     KST_CUDA(cudaMemcpy(exp_out, d + n, sizeof(double) * n, cudaMemcpyDeviceToHost));
     KST_CUDA(cudaMemcpy(rcp_out, d + 2 * n, sizeof(double) * n, cudaMemcpyDeviceToHost));
+    KST_CUDA(cudaMemcpy(log_out, d + 3 * n, sizeof(double) * n, cudaMemcpyDeviceToHost));
     KST_CUDA(cudaFree(d));
     return KST_OK;
 }

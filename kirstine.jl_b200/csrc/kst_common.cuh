@@ -10,8 +10,15 @@
 #include "../../include/kirstine_b200.h"
 #include "kst_models.cuh"
 
+#ifndef KST_NT
 #define KST_NT 256          // threads per CTA of the evaluation kernels
+#endif
+#ifndef KST_MINB
+#define KST_MINB 3          // minimum resident CTAs per SM the objective kernel is compiled for
+#endif
+#ifndef KST_TILE_P
 #define KST_TILE_P 8        // particles per CTA tile (objective kernel)
+#endif
 #define KST_GD_NT 128       // threads (= directions) per CTA of the Gateaux kernel
 #define KST_GD_CHUNK 64     // draws staged per shared-memory chunk in the Gateaux kernel
 

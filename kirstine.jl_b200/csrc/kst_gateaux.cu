@@ -19,12 +19,18 @@
 #include "kst_common.cuh"
 #include "kst_linalg.cuh"
 
+// doubles per row in shared memory: sqrt(omega), pc...
+template <class MF>
+struct KstRowW {
+    static constexpr int RW = 1 + MF::NPC;
+};
+
 // rows of one design measure (single thread): map_to_covariate! + update_model_vcov! + compaction
 template <class MF>
 __device__ __forceinline__ int kst_build_rows(double *rows, double &sw, int &rank, const double *pts, const double *w,
                                               int K, const KstModelParams &mp)
 {
-    constexpr int RW = 1 + MF::NPC;
+    constexpr int RW = KstRowW<MF>::RW;
     int na = 0, ntriv = 0;
     sw = 0.0;
     for (int k = 0; k < K; k++) {
@@ -36,7 +42,9 @@ __device__ __forceinline__ int kst_build_rows(double *rows, double &sw, int &ran
             sw += om;
             if (om == 0.0) continue;  // zero weight: contributes nothing, not even rank
             if (!trivial) {
-                rows[na * RW] = om;
+                const double sq = sqrt(om);
+                MF::post_row(pc, sq);
+                rows[na * RW] = sq;
                 for (int c = 0; c < MF::NPC; c++) rows[na * RW + 1 + c] = pc[c];
                 na++;
             } else {
@@ -56,10 +64,10 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
                                   const double *__restrict__ w, int K, KstModelParams mp, double *__restrict__ gA,
                                   double *__restrict__ gtrB, double *__restrict__ wtrB, int *flag)
 {
-    constexpr int R = MF::R, RW = 1 + MF::NPC;
-    extern __shared__ double smem[];  // rows[K*m][RW], sw, (na, rank)
-    __shared__ double s_exptab[KST_EXP_TAB_N];
-    kst_math_init(s_exptab);
+    constexpr int R = MF::R, RW = KstRowW<MF>::RW;
+    extern __shared__ __align__(16) double smem[];  // rows[K*m][RW], sw, (na, rank)
+    __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
+    const KstTab tab = kst_math_init(s_mathtab);
     double *rows = smem;
     double *s_sw = smem + (size_t)K * mp.m * RW;
     int *s_na = (int *)(s_sw + 1);
@@ -81,14 +89,14 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
     const int na = *s_na;
     for (int i = 0; i < na; i++) {
         double g[R];
-        MF::row(rows + i * RW + 1, dcv, g, s_exptab);
-        kst_accum<R, MF::CONST_COL>(M, rows[i * RW], g);
+        MF::row(rows + i * RW + 1, dcv, rows[i * RW], g, tab);
+        kst_accum<R, MF::CONST_COL>(M, g);
     }
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
     if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = *s_sw;
 
     double L[R][R], dv[R], dinv[R];
-    bool ok = kst_ldlt<R>(M, L, dv, dinv, true);
+    bool ok = kst_ldlt<R, false>(M, L, dv, dinv, true);
     ok = ok && s_na[1] >= R;  // fewer rows than parameters: singular by construction
     // Mt^-1 = Li' diag(dinv) Li with Li = L^-1 (unit lower)
     double Li[R][R];
@@ -239,28 +247,30 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
                                                             const double *__restrict__ dirs, int64_t G,
                                                             KstModelParams mp, double *__restrict__ partials)
 {
-    constexpr int R = MF::R, RW = 1 + MF::NPC, NP = KstPacked<R>::N, NS = MF::NDC + NP;
-    extern __shared__ double smem[];
-    __shared__ double s_exptab[KST_EXP_TAB_N];
-    kst_math_init(s_exptab);  // visible after the first __syncthreads() of the chunk loop
+    constexpr int R = MF::R, RW = KstRowW<MF>::RW, NP = KstPacked<R>::N, NS = MF::NDC + NP;
+    extern __shared__ __align__(16) double smem[];
+    __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
+    const KstTab tab = kst_math_init(s_mathtab);  // visible after the first __syncthreads() of the chunk loop
     double *s_draw = smem;                                  // [NS][KST_GD_CHUNK]
     double *s_rows = smem + (size_t)NS * KST_GD_CHUNK;      // [m][RW][KST_GD_NT]
     const int m = mp.m;
     const int64_t g = (int64_t)blockIdx.x * KST_GD_NT + threadIdx.x;
     const bool live = g < G;
 
-    // rows of this thread's direction (weight 1); trivial rows get omega = 0 and benign pc
+    // rows of this thread's direction (weight 1); trivial rows get sqrt(omega) = 0 and benign pc
     double sw_triv = 0.0;
     for (int i = 0; i < m; i++) {
         double pc[MF::NPC], varfac = 0.0;
         bool trivial = true;
         if (live) trivial = MF::prep_row(dirs + g * mp.d, i, mp, pc, varfac);
+        double sq = sqrt(varfac);
         if (trivial) {
             sw_triv += varfac;
-            varfac = 0.0;
+            sq = 0.0;
             for (int c = 0; c < MF::NPC; c++) pc[c] = 1.0;
         }
-        s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x] = varfac;
+        MF::post_row(pc, sq);
+        s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x] = sq;
         for (int c = 0; c < MF::NPC; c++) s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x] = pc[c];
     }
 
@@ -297,19 +307,17 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
             for (int c = 0; c < NP; c++) Ap[c] = s_draw[(MF::NDC + c) * KST_GD_CHUNK + jj];
             for (int i = 0; i < m; i++) {
                 double pc[MF::NPC], gv[R];
-                const double om = s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x];
+                const double sq = s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x];
 #pragma unroll
                 for (int c = 0; c < MF::NPC; c++) pc[c] = s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x];
-                MF::row(pc, dcv, gv, s_exptab);
-                double q = 0.0;
+                MF::row(pc, dcv, sq, gv, tab);  // weighted row: gv' A gv = omega * gt' A gt
 #pragma unroll
                 for (int a = 0; a < R; a++) {
                     double s = 0.0;
 #pragma unroll
                     for (int b = a; b < R; b++) s = fma(Ap[kst_pidx<R>(a, b)], gv[b], s);
-                    q = fma(s, gv[a], q);
+                    acc = fma(s, gv[a], acc);
                 }
-                acc = fma(om, q, acc);
             }
             constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
             if (MF::CONST_COL >= 0) acc = fma(sw_triv, Ap[kst_pidx<R>(cc, cc)], acc);
@@ -349,7 +357,7 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
     const int nt = 128;
     const unsigned nb = (unsigned)((h->N + nt - 1) / nt);
     KST_MODEL_SWITCH(h->model_id, {
-        const size_t smem = sizeof(double) * ((size_t)K * h->m * (1 + MF::NPC) + 2);
+        const size_t smem = sizeof(double) * ((size_t)K * h->m * KstRowW<MF>::RW + 2);
         k_gateaux_prepare<MF><<<nb, nt, smem, h->stream>>>(h->dc, h->cs, h->aux, h->pw, h->ld, h->N, h->crit, h->trafo,
                                                            h->t, d_pts, d_w, K, h->mp, h->gA, h->gtrB, wtrB, h->d_flag);
     });
@@ -392,7 +400,7 @@ int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, dou
     if (!h->g_singular) {
         KST_MODEL_SWITCH(h->model_id, {
             constexpr int NS = MF::NDC + KstPacked<MF::R>::N;
-            const size_t smem = sizeof(double) * ((size_t)NS * KST_GD_CHUNK + (size_t)h->m * (1 + MF::NPC) * KST_GD_NT);
+            const size_t smem = sizeof(double) * ((size_t)NS * KST_GD_CHUNK + (size_t)h->m * KstRowW<MF>::RW * KST_GD_NT);
             k_gateaux_eval<MF><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->pw, h->gA, h->ld, h->N, d_dirs, G, h->mp,
                                                                      h->gd_partials);
         });

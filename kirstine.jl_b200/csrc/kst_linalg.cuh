@@ -25,30 +25,27 @@ struct KstPacked {
     static constexpr int N = R * (R + 1) / 2;
 };
 
-// Mt += w * g g'  (upper triangle).  g[CC] is the compile-time constant 1 when CC >= 0; the
-// (CC, CC) entry is not accumulated at all: it is the per-particle sum of row weights.
+// Mt += g g'  (upper triangle) for a weighted row g = sqrt(omega) gt.  When CC >= 0 the (CC, CC)
+// entry is not accumulated at all: it is the per-particle sum of row weights (gt[CC] == 1).
 template <int R, int CC>
-__device__ __forceinline__ void kst_accum(double *M, double w, const double *g)
+__device__ __forceinline__ void kst_accum(double *M, const double *g)
 {
 #pragma unroll
     for (int i = 0; i < R; i++) {
-        const double wg = (i == CC) ? w : w * g[i];
 #pragma unroll
         for (int j = i; j < R; j++) {
             if (i == CC && j == CC) continue;
-            if (j == CC)
-                M[kst_pidx<R>(i, j)] += wg;
-            else
-                M[kst_pidx<R>(i, j)] = fma(wg, g[j], M[kst_pidx<R>(i, j)]);
+            M[kst_pidx<R>(i, j)] = fma(g[i], g[j], M[kst_pidx<R>(i, j)]);
         }
     }
 }
 
 // Mt (packed upper) -> unit lower L (strictly lower part used), pivots dv, 1/dv.
-// Returns false at the first pivot that is not > 0 (also catches NaN).
-template <int R>
+// Returns false at the first pivot that is not > 0 (also catches NaN).  With INV0 the reciprocal of
+// the first pivot is supplied by the caller (per-particle constant when the family has a constant column).
+template <int R, bool INV0 = false>
 __device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], double (&dv)[R],
-                                         double (&dinv)[R], bool need_last_inv)
+                                         double (&dinv)[R], bool need_last_inv, double inv0 = 0.0)
 {
     double W[R][R];  // W[i][j] = L[i][j] * dv[j]
     bool ok = true;
@@ -59,7 +56,8 @@ __device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], dou
         for (int k = 0; k < j; k++) dj = fma(-L[j][k], W[j][k], dj);
         dv[j] = dj;
         ok = ok && (dj > 0.0);
-        if (j < R - 1 || need_last_inv) dinv[j] = kst_rcp(dj);  // garbage when dj <= 0, but then ok == false
+        if (j < R - 1 || need_last_inv)
+            dinv[j] = (INV0 && j == 0) ? inv0 : kst_rcp(dj);  // garbage when dj <= 0, but then ok == false
 #pragma unroll
         for (int i = j + 1; i < R; i++) {
             double v = M[kst_pidx<R>(j, i)];
@@ -75,12 +73,13 @@ __device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], dou
 // log of a product of positive pivots with one log call; falls back to a sum of logs when the
 // product leaves the normal range (never on well-scaled information matrices).
 template <int R>
-__device__ __forceinline__ double kst_log_prod(const double (&dv)[R])
+__device__ __forceinline__ double kst_log_prod(const double (&dv)[R], KstTab tab)
 {
     double prod = dv[0];
 #pragma unroll
     for (int j = 1; j < R; j++) prod *= dv[j];
-    if (prod > 1e-290 && prod < 1e290) return log(prod);
+    // one integer range test on the exponent field: 2^-900 < prod < 2^900
+    if ((unsigned)((__double2hiint(prod) >> 20) - 123) < 1800u) return kst_log(prod, tab);
     double s = 0.0;
 #pragma unroll
     for (int j = 0; j < R; j++) s += log(dv[j]);
@@ -97,16 +96,17 @@ __device__ __forceinline__ double kst_log_prod(const double (&dv)[R])
 // SingularException from potri!, src/criterion-a.jl:39): objective! then returns -Inf no matter
 // the prior weight (src/designproblem.jl:217-223).  Silent failures (log_det!,
 // src/design-common.jl:213-220) just return -Inf, which the caller multiplies by the weight.
-template <int R, int CRIT, int T>
-__device__ __forceinline__ double kst_criterion(const double *M, const double *aux, size_t ld, bool &exc)
+template <int R, int CRIT, int T, bool INV0>
+__device__ __forceinline__ double kst_criterion(const double *M, const double *aux, size_t ld, bool &exc,
+                                                double inv0, KstTab tab)
 {
     double L[R][R], dv[R], dinv[R];
     exc = false;
     if (CRIT == 0 && T == 0) {
-        const bool ok = kst_ldlt<R>(M, L, dv, dinv, false);
-        return ok ? kst_log_prod<R>(dv) : -KST_INF;
+        const bool ok = kst_ldlt<R, INV0>(M, L, dv, dinv, false, inv0);
+        return ok ? kst_log_prod<R>(dv, tab) : -KST_INF;
     }
-    const bool ok = kst_ldlt<R>(M, L, dv, dinv, true);
+    const bool ok = kst_ldlt<R, INV0>(M, L, dv, dinv, true, inv0);
     if (!ok) {
         exc = true;
         return -KST_INF;
@@ -163,6 +163,6 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
             Mi[kst_pidx<TT>(a, b)] = s;
         }
     double L2[TT][TT], dv2[TT], dinv2[TT];
-    const bool ok2 = kst_ldlt<TT>(Mi, L2, dv2, dinv2, false);
-    return ok2 ? -kst_log_prod<TT>(dv2) : -KST_INF;
+    const bool ok2 = kst_ldlt<TT, false>(Mi, L2, dv2, dinv2, false);
+    return ok2 ? -kst_log_prod<TT>(dv2, tab) : -KST_INF;
 }

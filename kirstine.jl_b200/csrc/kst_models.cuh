@@ -17,6 +17,11 @@
 //
 // "Trivial" rows have gt = e_CONST_COL (or 0 when the family has no constant column): they
 // contribute nothing to the per-draw accumulators and are compacted away per particle.
+//
+// row() returns the WEIGHTED reduced row  g = sqrt(omega) * gt  (sw = sqrt(omega) comes from the
+// per-particle prologue), so that Mt += g g' needs no separate weight multiplications; each family
+// folds sw into its cheapest product chain.  post_row() lets a family precompute sw-dependent
+// per-row constants in the prologue.
 #pragma once
 #include <math.h>
 
@@ -32,7 +37,7 @@ struct KstModelParams {
 
 // Emax: test/example-emax.jl:41-47.  row = [1, x/(x+ec50), -emax x/(x+ec50)^2]
 struct KstEmax {
-    static constexpr int R = 3, NDC = 1, NPC = 1, CONST_COL = 0, D_MIN = 1;
+    static constexpr int R = 3, NDC = 1, NPC = 2, CONST_COL = 0;
     __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
     {
         const double isig = 1.0 / sqrt(mp.v[0]);  // v[0] = sigma_squared
@@ -45,16 +50,18 @@ struct KstEmax {
     __device__ static bool prep_row(const double *z, int, const KstModelParams &, double *pc, double &varfac)
     {
         pc[0] = z[0];
+        pc[1] = 0.0;
         varfac = 1.0;
         return z[0] == 0.0;
     }
-    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g, const double *)
+    __device__ static void post_row(double *pc, double sw) { pc[1] = sw * pc[0]; }
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab)
     {
         const double rho = kst_rcp(pc[0] + dc[0]);
-        const double a = pc[0] * rho;
-        g[0] = 1.0;
-        g[1] = a;
-        g[2] = a * rho;
+        const double sa = pc[1] * rho;  // sw x / (x + ec50)
+        g[0] = sw;
+        g[1] = sa;
+        g[2] = sa * rho;
     }
 };
 
@@ -62,8 +69,10 @@ struct KstEmax {
 //   A = x^h/(x^h+ed50^h) = 1/(1+e),  e = exp(q),  q = h (log ed50 - log x),  A B = emax e/(1+e)^2
 //   row = [1, A, -A B h/ed50, A B log(x/ed50)] = diag(1, 1, -emax h/ed50, -emax/h) [1, A, u, u q]
 //   dose == 0 -> [1, 0, 0, 0] (trivial row)
+// |q| beyond 708 saturates inside kst_exp, so e stays finite and u = e/(1+e)^2 never becomes Inf*0;
+// a NaN parameter still reaches the row through q and makes the draw singular like in the reference.
 struct KstSigEmax {
-    static constexpr int R = 4, NDC = 2, NPC = 1, CONST_COL = 0, D_MIN = 1;
+    static constexpr int R = 4, NDC = 2, NPC = 1, CONST_COL = 0;
     __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
     {
         const double isig = 1.0 / fabs(mp.v[0]);  // v[0] = sigma
@@ -80,17 +89,18 @@ struct KstSigEmax {
         varfac = 1.0;
         return z[0] == 0.0;
     }
-    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g, const double *tab)
+    __device__ static void post_row(double *, double) {}
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
         const double q = fma(-dc[0], pc[0], dc[1]);
-        // |q| is clamped at 700 so that e stays finite and u = e/(1+e)^2 never becomes Inf*0
-        const double e = kst_exp_clamped(q, tab);
-        const double rr = kst_rcp(1.0 + e);
-        const double u = e * rr * rr;
-        g[0] = 1.0;
-        g[1] = rr;
-        g[2] = u;
-        g[3] = u * q;
+        const double e = kst_exp(q, tab);
+        const double a = kst_rcp(1.0 + e);
+        const double sa = sw * a;
+        const double su = sa * (e * a);  // sw e / (1+e)^2
+        g[0] = sw;
+        g[1] = sa;
+        g[2] = su;
+        g[3] = su * q;
     }
 };
 
@@ -99,12 +109,12 @@ struct KstSigEmax {
 // VUMod (test/example-vector.jl:9-50) is the same row at times (i-1)*z with unit covariance
 // diag(sigma_squared (1 + t_i)).
 struct KstTpc {
-    static constexpr int R = 3, NDC = 2, NPC = 1, CONST_COL = -1, D_MIN = 1;
+    static constexpr int R = 3, NDC = 2, NPC = 2, CONST_COL = -1;
     __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
     {
         const double isig = 1.0 / fabs(mp.v[0]);  // v[0] = sigma
-        dc[0] = th[0];
-        dc[1] = th[1];
+        dc[0] = -th[0];
+        dc[1] = -th[1];
         cs[0] = th[2] * isig;
         cs[1] = -th[2] * isig;
         cs[2] = isig;
@@ -112,17 +122,18 @@ struct KstTpc {
     __device__ static bool prep_row(const double *z, int, const KstModelParams &, double *pc, double &varfac)
     {
         pc[0] = z[0];
+        pc[1] = 0.0;
         varfac = 1.0;
         return z[0] == 0.0;
     }
-    __device__ __forceinline__ static void row(const double *pc, const double *dc, double *g, const double *tab)
+    __device__ static void post_row(double *pc, double sw) { pc[1] = sw * pc[0]; }
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
-        const double t = pc[0];
-        const double A = kst_exp(-dc[0] * t, tab);
-        const double E = kst_exp(-dc[1] * t, tab);
-        g[0] = A * t;
-        g[1] = E * t;
-        g[2] = E - A;
+        const double A = kst_exp(dc[0] * pc[0], tab);
+        const double E = kst_exp(dc[1] * pc[0], tab);
+        g[0] = pc[1] * A;  // sw t A
+        g[1] = pc[1] * E;
+        g[2] = sw * (E - A);
     }
 };
 
@@ -130,8 +141,8 @@ struct KstVu : KstTpc {
     __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
     {
         const double isig = 1.0 / sqrt(mp.v[0]);  // v[0] = sigma_squared
-        dc[0] = th[0];
-        dc[1] = th[1];
+        dc[0] = -th[0];
+        dc[1] = -th[1];
         cs[0] = th[2] * isig;
         cs[1] = -th[2] * isig;
         cs[2] = isig;
@@ -140,6 +151,7 @@ struct KstVu : KstTpc {
     {
         const double t = (double)i * z[0];
         pc[0] = t;
+        pc[1] = 0.0;
         varfac = 1.0 / (1.0 + t);
         return t == 0.0;
     }

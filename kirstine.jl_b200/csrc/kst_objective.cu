@@ -71,33 +71,36 @@ __global__ void k_prep_draws(const double *__restrict__ theta_aos, const double 
 // ------------------------------------------------------------------------------------------
 template <class MF>
 struct KstTile {
-    static constexpr int RW = 1 + MF::NPC;  // doubles per row: omega, pc...
-    // layout (doubles): rows[P][rows_max][RW] | sumw[P] | wsum[P][NT/32] ; then ints nact[P], rank[P]
+    // doubles per row: sqrt(omega), pc...; padded to an even count so rows can be read as 16-byte vectors
+    static constexpr int RW = (1 + MF::NPC + 1) / 2 * 2;
+    // layout (doubles): rows[P][rows_max][RW] | sumw[P] | isumw[P] | wsum[P][NT/32] ; then ints nact[P], rank[P]
     __device__ static double *rows(double *s) { return s; }
     __device__ static double *sumw(double *s, int rows_max) { return s + (size_t)KST_TILE_P * rows_max * RW; }
-    __device__ static double *wsum(double *s, int rows_max) { return sumw(s, rows_max) + KST_TILE_P; }
+    __device__ static double *isumw(double *s, int rows_max) { return sumw(s, rows_max) + KST_TILE_P; }
+    __device__ static double *wsum(double *s, int rows_max) { return isumw(s, rows_max) + KST_TILE_P; }
     __device__ static int *nact(double *s, int rows_max) { return (int *)(wsum(s, rows_max) + KST_TILE_P * (KST_NT / 32)); }
     // upper bound on rank(Mt): below R the design is singular whatever the rounding does
     __device__ static int *rank(double *s, int rows_max) { return nact(s, rows_max) + KST_TILE_P; }
     __host__ static size_t bytes(int rows_max)
     {
-        return sizeof(double) * ((size_t)KST_TILE_P * rows_max * RW + KST_TILE_P + KST_TILE_P * (KST_NT / 32)) +
+        return sizeof(double) * ((size_t)KST_TILE_P * rows_max * RW + 2 * KST_TILE_P + KST_TILE_P * (KST_NT / 32)) +
                sizeof(int) * 2 * KST_TILE_P;
     }
 };
 
 // One thread per particle of the tile: map design points to rows (map_to_covariate! +
 // update_model_vcov!, src/design-common.jl:51-61, src/model-nonlinear-regression.jl:39-49),
-// hoist covariate-only transcendentals, drop trivial rows.
+// hoist covariate-only transcendentals, drop trivial and zero-weight rows.
 template <class MF>
 __device__ __forceinline__ void kst_build_tile(double *smem, const double *__restrict__ pts,
                                                const double *__restrict__ w, int p0, int S, int K,
                                                const KstModelParams &mp)
 {
     const int rows_max = K * mp.m;
+    constexpr int RW = KstTile<MF>::RW;
     if (threadIdx.x < KST_TILE_P) {
         const int p = p0 + threadIdx.x;
-        double *rows = KstTile<MF>::rows(smem) + (size_t)threadIdx.x * rows_max * KstTile<MF>::RW;
+        double *rows = KstTile<MF>::rows(smem) + (size_t)threadIdx.x * rows_max * RW;
         int na = 0, ntriv = 0;
         double sw = 0.0;
         if (p < S) {
@@ -111,9 +114,11 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
                     sw += om;
                     if (om == 0.0) continue;  // zero weight: contributes nothing, not even rank
                     if (!trivial) {
-                        rows[na * KstTile<MF>::RW] = om;
+                        const double sq = sqrt(om);
+                        MF::post_row(pc, sq);
+                        rows[na * RW] = sq;
 #pragma unroll
-                        for (int c = 0; c < MF::NPC; c++) rows[na * KstTile<MF>::RW + 1 + c] = pc[c];
+                        for (int c = 0; c < MF::NPC; c++) rows[na * RW + 1 + c] = pc[c];
                         na++;
                     } else {
                         ntriv++;
@@ -122,6 +127,7 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
             }
         }
         KstTile<MF>::sumw(smem, rows_max)[threadIdx.x] = sw;
+        KstTile<MF>::isumw(smem, rows_max)[threadIdx.x] = 1.0 / sw;
         KstTile<MF>::nact(smem, rows_max)[threadIdx.x] = na;
         KstTile<MF>::rank(smem, rows_max)[threadIdx.x] = na + ((MF::CONST_COL >= 0 && ntriv > 0) ? 1 : 0);
     }
@@ -130,16 +136,22 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
 
 template <class MF>
 __device__ __forceinline__ void kst_fisher(double *M, const double *__restrict__ rows, int na, double sw,
-                                           const double *dcv, const double *tab)
+                                           const double *dcv, KstTab tab)
 {
-    constexpr int R = MF::R, RW = 1 + MF::NPC;
+    constexpr int R = MF::R, RW = KstTile<MF>::RW;
 #pragma unroll
     for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
 #pragma unroll 2
     for (int i = 0; i < na; i++) {
-        double g[R];
-        MF::row(rows + i * RW + 1, dcv, g, tab);
-        kst_accum<R, MF::CONST_COL>(M, rows[i * RW], g);
+        double rw[RW], g[R];
+#pragma unroll
+        for (int c = 0; c < RW; c += 2) {
+            const double2 v = *reinterpret_cast<const double2 *>(rows + i * RW + c);
+            rw[c] = v.x;
+            rw[c + 1] = v.y;
+        }
+        MF::row(rw + 1, dcv, rw[0], g, tab);
+        kst_accum<R, MF::CONST_COL>(M, g);
     }
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
     if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = sw;
@@ -149,14 +161,14 @@ __device__ __forceinline__ void kst_fisher(double *M, const double *__restrict__
 // the hot kernel
 // ------------------------------------------------------------------------------------------
 template <class MF, int CRIT, int T>
-__global__ void __launch_bounds__(KST_NT, 2) k_objective(const KstObjParams prm)
+__global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjParams prm)
 {
     constexpr int R = MF::R;
-    extern __shared__ double smem[];
-    __shared__ double s_exptab[KST_EXP_TAB_N];
+    extern __shared__ __align__(16) double smem[];
+    __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
     const int rows_max = prm.K * prm.mp.m;
     const int p0 = blockIdx.y * KST_TILE_P;
-    kst_math_init(s_exptab);
+    const KstTab tab = kst_math_init(s_mathtab);
     kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp);  // ends with __syncthreads()
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -169,19 +181,36 @@ __global__ void __launch_bounds__(KST_NT, 2) k_objective(const KstObjParams prm)
         const double *rows = KstTile<MF>::rows(smem) + (size_t)p * rows_max * KstTile<MF>::RW;
         const int na = KstTile<MF>::nact(smem, rows_max)[p];
         const double sw = KstTile<MF>::sumw(smem, rows_max)[p];
+        // 1 / first pivot, hoisted per particle when the first pivot is the constant-column entry
+        constexpr bool INV0 = MF::CONST_COL == 0;
+        const double inv0 = KstTile<MF>::isumw(smem, rows_max)[p];
         // fewer rows than parameters: singular by construction (one-point designs etc.); the reference
         // reaches the same -Inf through an exactly zero pivot
         const bool rank_deficient = KstTile<MF>::rank(smem, rows_max)[p] < R;
         double acc = 0.0;
-        for (int64_t j = (int64_t)blockIdx.x * KST_NT + threadIdx.x; j < prm.N; j += stride) {
+        // software prefetch: the next draw's constants are requested before this draw's rows are evaluated
+        int64_t j = (int64_t)blockIdx.x * KST_NT + threadIdx.x;
+        double dcn[MF::NDC], pwn = 0.0;
+        if (j < prm.N) {
+#pragma unroll
+            for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(prm.dc + (size_t)c * prm.ld + j);
+            pwn = __ldg(prm.pw + j);
+        }
+        for (; j < prm.N; j += stride) {
             double dcv[MF::NDC];
 #pragma unroll
-            for (int c = 0; c < MF::NDC; c++) dcv[c] = __ldg(prm.dc + (size_t)c * prm.ld + j);
-            const double pwj = __ldg(prm.pw + j);
+            for (int c = 0; c < MF::NDC; c++) dcv[c] = dcn[c];
+            const double pwj = pwn;
+            const int64_t jn = j + stride;
+            if (jn < prm.N) {
+#pragma unroll
+                for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(prm.dc + (size_t)c * prm.ld + jn);
+                pwn = __ldg(prm.pw + jn);
+            }
             double M[KstPacked<R>::N];
-            kst_fisher<MF>(M, rows, na, sw, dcv, s_exptab);
+            kst_fisher<MF>(M, rows, na, sw, dcv, tab);
             bool exc;
-            double val = kst_criterion<R, CRIT, T>(M, prm.aux + j, prm.ld, exc);
+            double val = kst_criterion<R, CRIT, T, INV0>(M, prm.aux + j, prm.ld, exc, inv0, tab);
             if (rank_deficient) {
                 val = -KST_INF;
                 exc = !(CRIT == 0 && T == 0);
@@ -218,16 +247,16 @@ __global__ void k_infomatrix(const double *dc, const double *cs, size_t ld, int6
                              const double *w, int K, KstModelParams mp, double *Mout)
 {
     constexpr int R = MF::R;
-    extern __shared__ double smem[];
-    __shared__ double s_exptab[KST_EXP_TAB_N];
-    kst_math_init(s_exptab);
+    extern __shared__ __align__(16) double smem[];
+    __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
+    const KstTab tab = kst_math_init(s_mathtab);
     kst_build_tile<MF>(smem, pts, w, 0, 1, K, mp);
     if (threadIdx.x != 0) return;
     const int rows_max = K * mp.m;
     double dcv[MF::NDC], M[KstPacked<R>::N];
     for (int c = 0; c < MF::NDC; c++) dcv[c] = dc[(size_t)c * ld + j];
     kst_fisher<MF>(M, KstTile<MF>::rows(smem), KstTile<MF>::nact(smem, rows_max)[0],
-                   KstTile<MF>::sumw(smem, rows_max)[0], dcv, s_exptab);
+                   KstTile<MF>::sumw(smem, rows_max)[0], dcv, tab);
     for (int a = 0; a < R; a++)
         for (int b = a; b < R; b++) {
             const double v = M[kst_pidx<R>(a, b)] * cs[(size_t)a * ld + j] * cs[(size_t)b * ld + j];
@@ -287,7 +316,7 @@ int kst_objective_grid(const kst_problem *h, int S, int *n_blk)
 {
     const int tiles = (S + KST_TILE_P - 1) / KST_TILE_P;
     const int64_t max_chunks = (h->N + KST_NT - 1) / KST_NT;
-    const int cap = h->sm_count * 2;  // resident CTAs per wave at 2 CTAs/SM
+    const int cap = h->sm_count * KST_MINB;  // resident CTAs per wave
     // aim for >= 8 waves, then pick the draw split whose last wave is fullest
     int64_t lo = (8LL * cap + tiles - 1) / tiles;
     if (lo < 1) lo = 1;

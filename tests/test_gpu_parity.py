@@ -346,21 +346,32 @@ def test_abi_errors():
 
 
 def test_engine_math_accuracy():
-    """kst_exp / kst_rcp (csrc/kst_math.cuh) against mpmath: <= 1 ulp over the ranges the kernels use."""
+    """kst_exp / kst_rcp / kst_log (csrc/kst_math.cuh) against mpmath over the ranges the kernels use."""
     import mpmath as mp
     mp.mp.prec = 200
     rng = np.random.default_rng(0)
-    x = np.concatenate([rng.uniform(-700, 700, 4000), rng.uniform(-30, 30, 4000), rng.normal(0, 1e-3, 500),
-                        [0.0, -0.0, 707.9, -707.9, 709.5, -745.0, -800.0, 1e-300, np.inf, -np.inf]])
-    e, _ = kb._ffi.math_selftest(x)
+    x = np.concatenate([rng.uniform(-708, 708, 4000), rng.uniform(-30, 30, 4000), rng.normal(0, 1e-3, 500),
+                        [0.0, -0.0, 707.9, -707.9, 720.0, -720.0, 5000.0, -5000.0, np.nan]])
+    e, _, _ = kb._ffi.math_selftest(x)
     worst = 0.0
     for xi, ei in zip(x[:8500:7], e[:8500:7]):
         ref = mp.exp(mp.mpf(float(xi)))
         worst = max(worst, float(abs(mp.mpf(float(ei)) - ref) / ref) / 2.0 ** -52)
     assert worst <= 1.0, worst
-    assert e[-2] == np.inf and e[-1] == 0.0 and e[-4] == 0.0 and e[-10] == 1.0 and e[-9] == 1.0 and e[-3] == 1.0
-    assert e[-6] == pytest.approx(np.exp(709.5), rel=1e-15) and e[-5] == pytest.approx(np.exp(-745.0), rel=0.5)
+    assert e[-9] == 1.0 and e[-8] == 1.0
+    assert e[-7] == pytest.approx(np.exp(707.9), rel=1e-15) and e[-6] == pytest.approx(np.exp(-707.9), rel=1e-15)
+    # beyond |x| = 708 the result saturates at a finite, normal value; NaN stays NaN
+    assert np.isfinite(e[-5]) and e[-5] > 1e300 and 0 < e[-4] < 1e-300
+    assert np.isfinite(e[-3]) and e[-3] > 1e300 and 0 < e[-2] < 1e-300 and np.isnan(e[-1])
     y = np.concatenate([np.exp(rng.uniform(-600, 600, 4000)), -np.exp(rng.uniform(-5, 5, 100)), 1 + rng.random(1000)])
-    _, r = kb._ffi.math_selftest(y)
-    assert np.max(np.abs(r * y - 1.0)) <= 2.5 * 2.0 ** -53
-    assert np.max(np.abs(r - 1.0 / y) / np.abs(1.0 / y)) <= 2.0 ** -52
+    _, r, l = kb._ffi.math_selftest(y)
+    assert np.max(np.abs(r - 1.0 / y) / np.abs(1.0 / y)) <= 2.0 * 2.0 ** -52
+    worst_abs, worst_rel = 0.0, 0.0
+    for yi, li in zip(y[::9], l[::9]):
+        ref = mp.log(mp.mpf(abs(float(yi))))
+        err = float(abs(mp.mpf(float(li)) - ref))
+        worst_abs = max(worst_abs, err / max(1.0, abs(float(ref))))
+    assert worst_abs <= 3e-16, worst_abs
+    near1 = 1.0 + rng.uniform(-1e-3, 1e-3, 500)
+    _, _, l1 = kb._ffi.math_selftest(near1)
+    assert np.max(np.abs(l1 - np.log(near1))) <= 3e-16
