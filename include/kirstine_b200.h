@@ -135,6 +135,18 @@ KST_API int kst_objective_batch(kst_problem *h, int S, int K, const double *poin
  * stream (kst_stream_synchronize waits). */
 KST_API int kst_objective_batch_device(kst_problem *h, int S, int K, const double *d_points,
                                const double *d_weights, double *d_fx);
+/*
+ * No counterpart in the reference.  The same evaluation as kst_objective_batch_device for callers that
+ * must not allocate device memory while they run (all device memory already given to another pool, or a
+ * loop that cannot take the device-wide synchronisation of cudaMalloc / cudaFree): the per-CTA partial
+ * sums live in a fixed 2 MiB array inside the library image, which every GPU that loads the library
+ * keeps until exit.  At most 4096 particles per call (KST_ELIMIT beyond).  The first call on each GPU
+ * looks up the array's device address and should come before any stream capture.  Calls that overlap
+ * on one GPU race on the shared array: serialise them.  Asynchronous on the handle's stream; sums only
+ * the draws held by this handle (no collective even when a communicator is attached).
+ */
+KST_API int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const double *d_points,
+                                        const double *d_weights, double *d_fx);
 KST_API int kst_stream_synchronize(kst_problem *h);
 /* The handle's cudaStream_t, for callers that enqueue their own work or copies in order. */
 KST_API void *kst_stream(kst_problem *h);

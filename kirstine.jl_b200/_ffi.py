@@ -34,6 +34,7 @@ SIGNATURES = {
     "kst_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
     "kst_objective_batch": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
     "kst_objective_batch_device": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
+    "kst_objective_batch_noalloc": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
     "kst_stream_synchronize": (C.c_int, [_vp]),
     "kst_stream": (_vp, [_vp]),
     "kst_informationmatrix": (C.c_int, [_vp, C.c_int, _dp, _dp, C.c_int64, _dp]),
@@ -167,6 +168,11 @@ class ProblemHandle:
 
     def objective_batch_device(self, S, K, d_points, d_weights, d_fx):
         check(lib().kst_objective_batch_device(self._h, S, K, d_points, d_weights, d_fx))
+
+    def objective_batch_noalloc(self, S, K, d_points, d_weights, d_fx):
+        """Device pointers (integers); evaluates without touching the CUDA allocator (fixed 2 MiB scratch
+        inside the library, at most 4096 particles).  Asynchronous: call synchronize() before reading d_fx."""
+        check(lib().kst_objective_batch_noalloc(self._h, S, K, d_points, d_weights, d_fx))
 
     def synchronize(self):
         check(lib().kst_stream_synchronize(self._h))

@@ -11,6 +11,8 @@
 // matrix, its LDL' factor and everything after live in FP64 registers.  Per particle one
 // fixed-order block reduction; per-CTA partial sums go to scratch [S][n_blk] and are summed in
 // fixed order by k_obj_finish, so results are bit-reproducible run to run.
+#include <mutex>
+
 #include "kst_common.cuh"
 #include "kst_linalg.cuh"
 
@@ -401,6 +403,93 @@ int kst_launch_infomatrix(kst_problem *h, int K, const double *d_pts, const doub
     }
     KST_MODEL_SWITCH(h->model_id, (k_infomatrix<MF><<<1, 32, KstTile<MF>::bytes(K * h->m), h->stream>>>(
                                       h->dc, h->cs, h->ld, draw, d_pts, d_w, K, h->mp, d_M)));
+    KST_CUDA(cudaGetLastError());
+    return KST_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Evaluation without any allocation (no counterpart in the reference)
+// ------------------------------------------------------------------------------------------
+// Who needs this: hosts that must not touch the CUDA allocator while they run.  Typical cases are a
+// process whose device memory was handed in full to another pool up front (a framework's caching
+// allocator, a garbage-collected runtime's CUDA pool) so that a later cudaMalloc can fail, and
+// latency-critical loops that cannot afford the device-wide synchronisation cudaMalloc / cudaFree
+// imply.  The regular entry points grow the per-handle scratch for the per-CTA partial sums with
+// cudaMalloc when a larger swarm arrives; this one keeps that scratch in a fixed array inside the
+// library image instead.
+//
+// Cost and limits: every GPU that loads the library holds KST_NOALLOC_MAX_PARTIALS doubles (2 MiB)
+// until the process exits, used or not.  At most KST_NOALLOC_MAX_SWARM particles per call.  All
+// calls on one GPU share the array, so two calls that overlap on that GPU (different handles or
+// streams) race on it: serialise them.  Nothing in the array has to start at zero: within a call
+// every entry the finishing kernel reads has been written by the evaluation kernel of that same
+// call, so contents left over from the previous call are never observed.
+#define KST_NOALLOC_MAX_PARTIALS 262144
+#define KST_NOALLOC_MAX_SWARM 4096
+#define KST_NOALLOC_MAX_DEVICES 64
+
+static __device__ __align__(256) double kst_noalloc_scratch[KST_NOALLOC_MAX_PARTIALS];
+
+// Inside host code `kst_noalloc_scratch` is only a host-side handle for the symbol, not a device
+// address; the address valid on a given GPU comes from cudaGetSymbolAddress with that GPU current.
+static double *g_noalloc_ptr[KST_NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mutex;
+
+static int kst_noalloc_scratch_ptr(int device, double **out)
+{
+    if (device < 0 || device >= KST_NOALLOC_MAX_DEVICES) {
+        kst_set_error("objective_batch_noalloc: device %d beyond the %d devices this build tracks", device,
+                      KST_NOALLOC_MAX_DEVICES);
+        return KST_ELIMIT;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[device]) {
+        void *ptr = nullptr;
+        KST_CUDA(cudaSetDevice(device));
+        KST_CUDA(cudaGetSymbolAddress(&ptr, kst_noalloc_scratch));
+        g_noalloc_ptr[device] = static_cast<double *>(ptr);
+    }
+    *out = g_noalloc_ptr[device];
+    return KST_OK;
+}
+
+// Same evaluation as kst_objective_batch_device (the same k_objective / k_obj_finish kernels), with the
+// partial sums kept in the static array above.  Calls no cudaMalloc, cudaFree or any other allocating
+// routine.  The first call on each GPU looks the array's device address up (cudaGetSymbolAddress); make
+// that first call before starting any stream capture.  Asynchronous on the handle's stream.  Only the
+// draws held by this handle are summed: no collective is issued even when a communicator is attached.
+extern "C" int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const double *d_points,
+                                           const double *d_weights, double *d_fx)
+{
+    if (!h) { kst_set_error("NULL problem handle"); return KST_EINVAL; }
+    if (!d_points || !d_weights || !d_fx) { kst_set_error("objective_batch_noalloc: NULL buffer"); return KST_EINVAL; }
+    if (S < 1 || K < 1 || K * h->m > KST_MAX_ROWS) {
+        kst_set_error("objective_batch_noalloc: need S >= 1, K >= 1, K*m <= %d (S=%d K=%d m=%d)", KST_MAX_ROWS, S, K, h->m);
+        return KST_EINVAL;
+    }
+    if (S > KST_NOALLOC_MAX_SWARM) {
+        kst_set_error("objective_batch_noalloc: swarm of %d particles exceeds the fixed limit of %d; "
+                      "use kst_objective_batch_device, which allocates its scratch", S, KST_NOALLOC_MAX_SWARM);
+        return KST_ELIMIT;
+    }
+    KST_CUDA(cudaSetDevice(h->device));
+    double *scratch = nullptr;
+    int rc = kst_noalloc_scratch_ptr(h->device, &scratch);
+    if (rc) return rc;
+    int n_blk = 1;
+    const int tiles = kst_objective_grid(h, S, &n_blk);
+    if ((size_t)n_blk * S > KST_NOALLOC_MAX_PARTIALS) n_blk = KST_NOALLOC_MAX_PARTIALS / S;  // >= 64 by the swarm limit
+    KstObjParams prm;
+    prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.ld = h->ld; prm.N = h->N;
+    prm.pts = d_points; prm.w = d_weights; prm.S = S; prm.K = K; prm.partials = scratch; prm.mp = h->mp;
+    const dim3 grid(n_blk, tiles);
+    KST_MODEL_SWITCH(h->model_id, {
+        const size_t smem = KstTile<MF>::bytes(K * h->m);
+        rc = h->crit == KST_CRIT_D ? launch_obj_t<MF, 0>(h, prm, grid, smem) : launch_obj_t<MF, 1>(h, prm, grid, smem);
+    });
+    if (rc) return rc;
+    KST_CUDA(cudaGetLastError());
+    k_obj_finish<<<(S + 127) / 128, 128, 0, h->stream>>>(scratch, n_blk, h->offset, d_fx, S);
     KST_CUDA(cudaGetLastError());
     return KST_OK;
 }
