@@ -14,7 +14,7 @@
 #define KST_NT 256          // threads per CTA of the evaluation kernels
 #endif
 #ifndef KST_MINB
-#define KST_MINB 3          // minimum resident CTAs per SM the objective kernel is compiled for
+#define KST_MINB 2          // minimum resident CTAs per SM the objective kernel is compiled for
 #endif
 #ifndef KST_TILE_P
 #define KST_TILE_P 8        // particles per CTA tile (objective kernel)

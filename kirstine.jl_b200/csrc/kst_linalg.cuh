@@ -40,10 +40,24 @@ __device__ __forceinline__ void kst_accum(double *M, const double *g)
     }
 }
 
+// Mt = g g' for the first row of a particle (saves zeroing the accumulators).
+template <int R, int CC>
+__device__ __forceinline__ void kst_accum_init(double *M, const double *g)
+{
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+#pragma unroll
+        for (int j = i; j < R; j++) {
+            if (i == CC && j == CC) continue;
+            M[kst_pidx<R>(i, j)] = g[i] * g[j];
+        }
+    }
+}
+
 // Mt (packed upper) -> unit lower L (strictly lower part used), pivots dv, 1/dv.
 // Returns false at the first pivot that is not > 0 (also catches NaN).  With INV0 the reciprocal of
 // the first pivot is supplied by the caller (per-particle constant when the family has a constant column).
-template <int R, bool INV0 = false>
+template <int R, bool INV0 = false, bool CHECK = true>
 __device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], double (&dv)[R],
                                          double (&dinv)[R], bool need_last_inv, double inv0 = 0.0)
 {
@@ -55,7 +69,7 @@ __device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], dou
 #pragma unroll
         for (int k = 0; k < j; k++) dj = fma(-L[j][k], W[j][k], dj);
         dv[j] = dj;
-        ok = ok && (dj > 0.0);
+        if (CHECK) ok = ok && (dj > 0.0);
         if (j < R - 1 || need_last_inv)
             dinv[j] = (INV0 && j == 0) ? inv0 : kst_rcp(dj);  // garbage when dj <= 0, but then ok == false
 #pragma unroll
@@ -70,19 +84,30 @@ __device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], dou
     return ok;
 }
 
-// log of a product of positive pivots with one log call; falls back to a sum of logs when the
-// product leaves the normal range (never on well-scaled information matrices).
-template <int R>
-__device__ __forceinline__ double kst_log_prod(const double (&dv)[R], KstTab tab)
+// log det from the pivots with one log call and NO floating-point compares: the pivots' sign bits are
+// OR-ed into the high word of their product and a single unsigned test on the exponent field accepts
+// "all pivots positive and 2^-900 < product < 2^900".  Everything else (a non-positive or NaN pivot, an
+// out-of-range product) takes the slow path, which applies the reference's rule pivot by pivot:
+// any pivot that is not > 0 gives -Inf (log_det!, src/design-common.jl:213-220).
+// SKIP0: dv[0] is a per-particle constant already known to be positive.
+template <int R, bool SKIP0>
+__device__ __forceinline__ double kst_log_det(const double (&dv)[R], KstTab tab)
 {
     double prod = dv[0];
+    int signs = SKIP0 ? 0 : __double2hiint(dv[0]);
 #pragma unroll
-    for (int j = 1; j < R; j++) prod *= dv[j];
-    // one integer range test on the exponent field: 2^-900 < prod < 2^900
-    if ((unsigned)((__double2hiint(prod) >> 20) - 123) < 1800u) return kst_log(prod, tab);
+    for (int j = 1; j < R; j++) {
+        prod *= dv[j];
+        signs |= __double2hiint(dv[j]);
+    }
+    const unsigned key = ((unsigned)signs & 0x80000000u) | (unsigned)__double2hiint(prod);
+    if (((key >> 20) - 123u) < 1800u) return kst_log(prod, tab);
     double s = 0.0;
 #pragma unroll
-    for (int j = 0; j < R; j++) s += log(dv[j]);
+    for (int j = 0; j < R; j++) {
+        if (!(dv[j] > 0.0)) return -KST_INF;
+        s += log(dv[j]);
+    }
     return s;
 }
 
@@ -103,8 +128,8 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
     double L[R][R], dv[R], dinv[R];
     exc = false;
     if (CRIT == 0 && T == 0) {
-        const bool ok = kst_ldlt<R, INV0>(M, L, dv, dinv, false, inv0);
-        return ok ? kst_log_prod<R>(dv, tab) : -KST_INF;
+        kst_ldlt<R, INV0, false>(M, L, dv, dinv, false, inv0);
+        return kst_log_det<R, INV0>(dv, tab);
     }
     const bool ok = kst_ldlt<R, INV0>(M, L, dv, dinv, true, inv0);
     if (!ok) {
@@ -163,6 +188,6 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
             Mi[kst_pidx<TT>(a, b)] = s;
         }
     double L2[TT][TT], dv2[TT], dinv2[TT];
-    const bool ok2 = kst_ldlt<TT, false>(Mi, L2, dv2, dinv2, false);
-    return ok2 ? -kst_log_prod<TT>(dv2, tab) : -KST_INF;
+    kst_ldlt<TT, false, false>(Mi, L2, dv2, dinv2, false);
+    return -kst_log_det<TT, false>(dv2, tab);
 }

@@ -13,6 +13,10 @@
 // fixed order by k_obj_finish, so results are bit-reproducible run to run.
 #include <mutex>
 
+#ifndef KST_PEEL
+#define KST_PEEL 0
+#endif
+
 #include "kst_common.cuh"
 #include "kst_linalg.cuh"
 
@@ -128,31 +132,60 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
                 }
             }
         }
+        int rank = na + ((MF::CONST_COL >= 0 && ntriv > 0) ? 1 : 0);
+        // the hoisted first pivot must be a positive, finite number; otherwise the design is singular
+        // (or its weights are NaN) and every draw takes the rank-deficient path
+        if (MF::CONST_COL >= 0 && !(sw > 0.0 && sw < KST_INF)) rank = 0;
+        if (na == 0) {
+            // the evaluation loop always runs the first row: give it a weightless, harmless one
+            double pc[MF::NPC], vf;
+            const double one = 1.0;
+            MF::prep_row(&one, 1, mp, pc, vf);
+            MF::post_row(pc, 0.0);
+            rows[0] = 0.0;
+#pragma unroll
+            for (int c = 0; c < MF::NPC; c++) rows[1 + c] = pc[c];
+            na = 1;
+        }
         KstTile<MF>::sumw(smem, rows_max)[threadIdx.x] = sw;
         KstTile<MF>::isumw(smem, rows_max)[threadIdx.x] = 1.0 / sw;
         KstTile<MF>::nact(smem, rows_max)[threadIdx.x] = na;
-        KstTile<MF>::rank(smem, rows_max)[threadIdx.x] = na + ((MF::CONST_COL >= 0 && ntriv > 0) ? 1 : 0);
+        KstTile<MF>::rank(smem, rows_max)[threadIdx.x] = rank;
     }
     __syncthreads();
 }
 
+// one row record (RW doubles at a 32-bit shared-space address) -> weighted row g
 template <class MF>
-__device__ __forceinline__ void kst_fisher(double *M, const double *__restrict__ rows, int na, double sw,
-                                           const double *dcv, KstTab tab)
+__device__ __forceinline__ void kst_row_at(unsigned addr, const double *dcv, double *g, KstTab tab)
+{
+    constexpr int RW = KstTile<MF>::RW;
+    double rw[RW];
+#pragma unroll
+    for (int c = 0; c < RW; c += 2)
+        asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rw[c]), "=d"(rw[c + 1]) : "r"(addr + 8u * c));
+    MF::row(rw + 1, dcv, rw[0], g, tab);
+}
+
+// Mt = sum over the particle's live rows (at least one) of g g'; rows_addr is a shared-space address
+template <class MF>
+__device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na, double sw, const double *dcv,
+                                           KstTab tab)
 {
     constexpr int R = MF::R, RW = KstTile<MF>::RW;
+    double g[R];
+#if KST_PEEL
+    kst_row_at<MF>(rows_addr, dcv, g, tab);
+    kst_accum_init<R, MF::CONST_COL>(M, g);
+#pragma unroll 2
+    for (int i = 1; i < na; i++) {
+#else
 #pragma unroll
     for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
 #pragma unroll 2
     for (int i = 0; i < na; i++) {
-        double rw[RW], g[R];
-#pragma unroll
-        for (int c = 0; c < RW; c += 2) {
-            const double2 v = *reinterpret_cast<const double2 *>(rows + i * RW + c);
-            rw[c] = v.x;
-            rw[c + 1] = v.y;
-        }
-        MF::row(rw + 1, dcv, rw[0], g, tab);
+#endif
+        kst_row_at<MF>(rows_addr + (unsigned)(i * RW * 8), dcv, g, tab);
         kst_accum<R, MF::CONST_COL>(M, g);
     }
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
@@ -176,48 +209,53 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int np = min(KST_TILE_P, prm.S - p0);
     double *wsum = KstTile<MF>::wsum(smem, rows_max);
-    const int64_t stride = (int64_t)gridDim.x * KST_NT;
+    // 32-bit draw indices (the launcher guarantees N + stride < 2^31) and 32-bit shared-space addresses:
+    // the loop bookkeeping is a handful of integer instructions
+    const int n = (int)prm.N, stride = (int)gridDim.x * KST_NT, j0 = (int)blockIdx.x * KST_NT + (int)threadIdx.x;
+    const unsigned rows_base = (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem));
+    const double *__restrict__ pw = prm.pw;
+    const double *__restrict__ dc = prm.dc;
+    const unsigned ld = (unsigned)prm.ld;
 
 #pragma unroll 1
     for (int p = 0; p < np; p++) {
-        const double *rows = KstTile<MF>::rows(smem) + (size_t)p * rows_max * KstTile<MF>::RW;
+        const unsigned rows_addr = rows_base + (unsigned)(p * rows_max * KstTile<MF>::RW * 8);
         const int na = KstTile<MF>::nact(smem, rows_max)[p];
         const double sw = KstTile<MF>::sumw(smem, rows_max)[p];
         // 1 / first pivot, hoisted per particle when the first pivot is the constant-column entry
         constexpr bool INV0 = MF::CONST_COL == 0;
         const double inv0 = KstTile<MF>::isumw(smem, rows_max)[p];
-        // fewer rows than parameters: singular by construction (one-point designs etc.); the reference
-        // reaches the same -Inf through an exactly zero pivot
-        const bool rank_deficient = KstTile<MF>::rank(smem, rows_max)[p] < R;
         double acc = 0.0;
-        // software prefetch: the next draw's constants are requested before this draw's rows are evaluated
-        int64_t j = (int64_t)blockIdx.x * KST_NT + threadIdx.x;
-        double dcn[MF::NDC], pwn = 0.0;
-        if (j < prm.N) {
+        if (KstTile<MF>::rank(smem, rows_max)[p] < R) {
+            // fewer live rows than parameters: singular by construction (one-point designs etc.).  The
+            // reference reaches the same -Inf through an exactly zero pivot: weighted by the prior weight
+            // for log_det! (0 * -Inf = NaN, as there), unweighted where it throws.
+            for (int j = j0; j < n; j += stride) acc += (CRIT == 0 && T == 0) ? pw[j] * -KST_INF : -KST_INF;
+        } else {
+            // software prefetch: the next draw's constants are requested before this draw's rows are evaluated
+            double dcn[MF::NDC], pwn = 0.0;
+            if (j0 < n) {
 #pragma unroll
-            for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(prm.dc + (size_t)c * prm.ld + j);
-            pwn = __ldg(prm.pw + j);
-        }
-        for (; j < prm.N; j += stride) {
-            double dcv[MF::NDC];
-#pragma unroll
-            for (int c = 0; c < MF::NDC; c++) dcv[c] = dcn[c];
-            const double pwj = pwn;
-            const int64_t jn = j + stride;
-            if (jn < prm.N) {
-#pragma unroll
-                for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(prm.dc + (size_t)c * prm.ld + jn);
-                pwn = __ldg(prm.pw + jn);
+                for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)j0));
+                pwn = __ldg(pw + j0);
             }
-            double M[KstPacked<R>::N];
-            kst_fisher<MF>(M, rows, na, sw, dcv, tab);
-            bool exc;
-            double val = kst_criterion<R, CRIT, T, INV0>(M, prm.aux + j, prm.ld, exc, inv0, tab);
-            if (rank_deficient) {
-                val = -KST_INF;
-                exc = !(CRIT == 0 && T == 0);
+            for (int j = j0; j < n; j += stride) {
+                double dcv[MF::NDC];
+#pragma unroll
+                for (int c = 0; c < MF::NDC; c++) dcv[c] = dcn[c];
+                const double pwj = pwn;
+                const int jn = j + stride;
+                if (jn < n) {
+#pragma unroll
+                    for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
+                    pwn = __ldg(pw + jn);
+                }
+                double M[KstPacked<R>::N];
+                kst_fisher<MF>(M, rows_addr, na, sw, dcv, tab);
+                bool exc;
+                const double val = kst_criterion<R, CRIT, T, INV0>(M, prm.aux + j, prm.ld, exc, inv0, tab);
+                acc += exc ? -KST_INF : pwj * val;
             }
-            acc += exc ? -KST_INF : pwj * val;
         }
         // fixed-order reduction over the CTA's draws
 #pragma unroll
@@ -257,7 +295,7 @@ __global__ void k_infomatrix(const double *dc, const double *cs, size_t ld, int6
     const int rows_max = K * mp.m;
     double dcv[MF::NDC], M[KstPacked<R>::N];
     for (int c = 0; c < MF::NDC; c++) dcv[c] = dc[(size_t)c * ld + j];
-    kst_fisher<MF>(M, KstTile<MF>::rows(smem), KstTile<MF>::nact(smem, rows_max)[0],
+    kst_fisher<MF>(M, (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem)), KstTile<MF>::nact(smem, rows_max)[0],
                    KstTile<MF>::sumw(smem, rows_max)[0], dcv, tab);
     for (int a = 0; a < R; a++)
         for (int b = a; b < R; b++) {
@@ -366,6 +404,10 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
     if (S < 1 || K < 1 || K * h->m > KST_MAX_ROWS) {
         kst_set_error("objective: need S >= 1, K >= 1, K*m <= %d (S=%d K=%d m=%d)", KST_MAX_ROWS, S, K, h->m);
         return KST_EINVAL;
+    }
+    if (h->N > (1LL << 29)) {  // 32-bit element indices into the [NDC][ld] arrays inside the kernel
+        kst_set_error("objective: at most 2^29 draws per GPU (shard the prior sample over more GPUs)");
+        return KST_ELIMIT;
     }
     int n_blk = 1;
     const int tiles = kst_objective_grid(h, S, &n_blk);
