@@ -13,9 +13,6 @@
 // fixed order by k_obj_finish, so results are bit-reproducible run to run.
 #include <mutex>
 
-#ifndef KST_PEEL
-#define KST_PEEL 0
-#endif
 
 #include "kst_common.cuh"
 #include "kst_linalg.cuh"
@@ -173,20 +170,24 @@ __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na
                                            KstTab tab)
 {
     constexpr int R = MF::R, RW = KstTile<MF>::RW;
-    double g[R];
-#if KST_PEEL
-    kst_row_at<MF>(rows_addr, dcv, g, tab);
-    kst_accum_init<R, MF::CONST_COL>(M, g);
-#pragma unroll 2
-    for (int i = 1; i < na; i++) {
-#else
 #pragma unroll
     for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
-#pragma unroll 2
-    for (int i = 0; i < na; i++) {
-#endif
-        kst_row_at<MF>(rows_addr + (unsigned)(i * RW * 8), dcv, g, tab);
+    // odd row first, then pairs: two independent rows per iteration give the scheduler two exp / reciprocal
+    // chains to interleave, and there is no remainder code after the loop
+    int i = 0;
+    if (na & 1) {
+        double g[R];
+        kst_row_at<MF>(rows_addr, dcv, g, tab);
         kst_accum<R, MF::CONST_COL>(M, g);
+        i = 1;
+    }
+#pragma unroll 1
+    for (; i < na; i += 2) {
+        double g0[R], g1[R];
+        kst_row_at<MF>(rows_addr + (unsigned)(i * RW * 8), dcv, g0, tab);
+        kst_row_at<MF>(rows_addr + (unsigned)((i + 1) * RW * 8), dcv, g1, tab);
+        kst_accum<R, MF::CONST_COL>(M, g0);
+        kst_accum<R, MF::CONST_COL>(M, g1);
     }
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
     if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = sw;
@@ -203,7 +204,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
     __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
     const int rows_max = prm.K * prm.mp.m;
     const int p0 = blockIdx.y * KST_TILE_P;
-    const KstTab tab = kst_math_init(s_mathtab);
+    KstTab tab = kst_math_init(s_mathtab);
     kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp);  // ends with __syncthreads()
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -212,7 +213,10 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
     // 32-bit draw indices (the launcher guarantees N + stride < 2^31) and 32-bit shared-space addresses:
     // the loop bookkeeping is a handful of integer instructions
     const int n = (int)prm.N, stride = (int)gridDim.x * KST_NT, j0 = (int)blockIdx.x * KST_NT + (int)threadIdx.x;
-    const unsigned rows_base = (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem));
+    unsigned rows_base = (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem));
+    // make both shared-space bases opaque: otherwise the compiler rebuilds them from SR_CgaCtaId (a
+    // variable-latency S2R/S2UR + LEA) in front of every use instead of keeping them in a register
+    asm volatile("" : "+r"(tab), "+r"(rows_base));
     const double *__restrict__ pw = prm.pw;
     const double *__restrict__ dc = prm.dc;
     const unsigned ld = (unsigned)prm.ld;
