@@ -50,17 +50,31 @@ extern "C" {
  *   KST_MODEL_SIGEMAX  docs/src/tutorial.md:107-142      params {sigma},          theta = (e0, emax, ed50, h)
  *   KST_MODEL_TPC      test/example-compartment.jl:10-21 params {sigma},          theta = (a, e, s)
  *   KST_MODEL_VU       test/example-vector.jl:9-41       params {sigma_squared},  theta = (a, e, s), unit length m
+ *   KST_MODEL_DTR      test/example-dtr.jl:4-47, docs/src/dtr.md:87-129  params {sigma}, theta = (a, e, e0, emax, ec50),
+ *                      unit length m, design points (dose[, time or delta-t])
  * Unregistered model types must keep using stock Kirstine. */
 #define KST_MODEL_EMAX 1
 #define KST_MODEL_SIGEMAX 2
 #define KST_MODEL_TPC 3
 #define KST_MODEL_VU 4
+#define KST_MODEL_DTR 5
 
 /* covariate parameterizations = map_to_covariate! (src/user.jl:68):
  *   KST_CP_COPY      CopyDose / CopyTime / JustCopy: covariate = design point (src/user.jl:185-216)
- *   KST_CP_EQUITIME  EquiTime (test/example-vector.jl:45-50): time_i = (i-1) * z[1], i = 1..m */
+ *   KST_CP_EQUITIME  EquiTime (test/example-vector.jl:45-50): time_i = (i-1) * z[1], i = 1..m
+ * for KST_MODEL_DTR (docs/src/dtr.md; z = design point, cp_params in brackets):
+ *   KST_CP_DTR_COPYBOTH        CopyBoth :197-203          dose = z[1], time_1 = z[2]              (d = 2, m = 1)
+ *   KST_CP_DTR_FIXEDDOSE       FixedDose :331-339         dose = [dose], time_1 = z[1]            (d = 1, m = 1)
+ *   KST_CP_DTR_FIXEDTIMES      FixedTimes :401-409        dose = z[1], time = [time_1..time_m]    (d = 1)
+ *   KST_CP_DTR_EQUIDISTANT     EquidistantTimes :484-495  dose = z[1], time_i = (i-1) z[2]        (d = 2)
+ *   KST_CP_DTR_LOGEQUIDISTANT  LogEquidistantTimes :663-681 dose = z[1], time = 0, z[2], b z[2], ... [b] (d = 2, m >= 2) */
 #define KST_CP_COPY 0
 #define KST_CP_EQUITIME 1
+#define KST_CP_DTR_COPYBOTH 2
+#define KST_CP_DTR_FIXEDDOSE 3
+#define KST_CP_DTR_FIXEDTIMES 4
+#define KST_CP_DTR_EQUIDISTANT 5
+#define KST_CP_DTR_LOGEQUIDISTANT 6
 
 #define KST_CRIT_D 0 /* DCriterion, src/criterion-d.jl:29 */
 #define KST_CRIT_A 1 /* ACriterion, src/criterion-a.jl:29 */
@@ -92,6 +106,7 @@ KST_API int kst_device_count(int *count);
  * (src/transformation.jl:71-92): the caller evaluates DeltaMethod's Jacobian on the host for
  * every draw (arbitrary user closure) and passes the result.
  *
+ *  cp_params  parameters of the covariate parameterization (may be NULL when it has none)
  *  theta    N*r doubles, array-of-structs exactly like Julia's Vector{P} of isbits parameter
  *           structs (PriorSample.p, src/priorknowledge.jl:11-38); transposed to SoA on upload
  *  prior_w  N prior weights (PriorSample.weight)
@@ -104,6 +119,7 @@ KST_API int kst_device_count(int *count);
  * kst_comm_init.
  */
 KST_API int kst_problem_create(int model_id, const double *model_params, int n_model_params, int cp_id,
+                       const double *cp_params, int n_cp_params,
                        int criterion_id, int trafo_id, int r, int t, int m, int d, int64_t N,
                        const double *theta, const double *prior_w, const double *dt_jm,
                        const double *lb, const double *ub, int device_id, kst_problem **out);

@@ -74,9 +74,9 @@ function handle(dp::DesignProblem{<:Any,<:Any,<:RegisteredModel}; device = 0)
         mp = model_params(model(dp))
         out = Ref{Ptr{Cvoid}}(C_NULL)
         check(ccall((:kst_problem_create, LIB), Cint,
-            (Cint, Ptr{Cdouble}, Cint, Cint, Cint, Cint, Cint, Cint, Cint, Cint, Int64,
+            (Cint, Ptr{Cdouble}, Cint, Cint, Ptr{Cdouble}, Cint, Cint, Cint, Cint, Cint, Cint, Cint, Int64,
              Ptr{Cdouble}, Ptr{Cdouble}, Ptr{Cdouble}, Ptr{Cdouble}, Ptr{Cdouble}, Cint, Ref{Ptr{Cvoid}}),
-            model_id(model(dp)), mp, length(mp), cp_id(model(dp)), crit_id(criterion(dp)), isdelta ? 1 : 0,
+            model_id(model(dp)), mp, length(mp), cp_id(model(dp)), C_NULL, 0, crit_id(criterion(dp)), isdelta ? 1 : 0,
             r, t, Kirstine.unit_length(model(dp)), length(lb), N, theta, pk.weight,
             isdelta ? dt : C_NULL, lb, ub, device, out))
         h = Handle(out[])

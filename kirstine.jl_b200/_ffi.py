@@ -12,8 +12,9 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # KST_LIB_PATH selects an alternative build of the same library (kernel tuning experiments)
 LIB_PATH = os.environ.get("KST_LIB_PATH") or os.path.join(_HERE, "libkirstine_b200.so")
 
-MODEL_EMAX, MODEL_SIGEMAX, MODEL_TPC, MODEL_VU = 1, 2, 3, 4
+MODEL_EMAX, MODEL_SIGEMAX, MODEL_TPC, MODEL_VU, MODEL_DTR = 1, 2, 3, 4, 5
 CP_COPY, CP_EQUITIME = 0, 1
+CP_DTR_COPYBOTH, CP_DTR_FIXEDDOSE, CP_DTR_FIXEDTIMES, CP_DTR_EQUIDISTANT, CP_DTR_LOGEQUIDISTANT = 2, 3, 4, 5, 6
 CRIT_D, CRIT_A = 0, 1
 TRAFO_IDENTITY, TRAFO_DELTA = 0, 1
 PSO_MODE_OBJECTIVE, PSO_MODE_GATEAUX = 0, 1
@@ -27,8 +28,8 @@ SIGNATURES = {
     "kst_last_error": (C.c_char_p, []),
     "kst_version": (C.c_int, []),
     "kst_device_count": (C.c_int, [_ip]),
-    "kst_problem_create": (C.c_int, [C.c_int, _dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
-                                     C.c_int, C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_int, C.POINTER(_vp)]),
+    "kst_problem_create": (C.c_int, [C.c_int, _dp, C.c_int, C.c_int, _dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                     C.c_int, C.c_int, C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_int, C.POINTER(_vp)]),
     "kst_problem_destroy": (C.c_int, [_vp]),
     "kst_comm_unique_id": (C.c_int, [_vp]),
     "kst_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
@@ -106,7 +107,7 @@ class ProblemHandle:
     """
 
     def __init__(self, model_id, model_params, theta, prior_weights, crit, dt, lb, ub, m=1, cp_id=CP_COPY,
-                 device=0):
+                 device=0, cp_params=()):
         theta = f64(theta)
         if theta.ndim != 2:
             raise ValueError("theta must be (N, r)")
@@ -123,8 +124,10 @@ class ProblemHandle:
             self.trafo, self.t = TRAFO_DELTA, dt.shape[1]
             dtc = f64(np.transpose(dt, (0, 2, 1)))  # per draw column-major t x r
         mp = f64(model_params).ravel()
+        cpp = f64(cp_params).ravel() if len(cp_params) else None
         h = _vp()
-        check(lib().kst_problem_create(model_id, ptr(mp), len(mp), cp_id, crit, self.trafo, self.r, self.t, self.m,
+        check(lib().kst_problem_create(model_id, ptr(mp), len(mp), cp_id, ptr(cpp), 0 if cpp is None else len(cpp), crit,
+                                       self.trafo, self.r, self.t, self.m,
                                        self.d, self.N, ptr(theta), ptr(pw), ptr(dtc), ptr(lb), ptr(ub), device,
                                        C.byref(h)))
         self._h = h

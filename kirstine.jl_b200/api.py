@@ -27,6 +27,7 @@ EmaxPar = namedtuple("EmaxPar", "e0 emax ec50")                    # test/exampl
 SigEmaxParameter = namedtuple("SigEmaxParameter", "e0 emax ed50 h")  # docs/src/tutorial.md:116
 TPCParameter = namedtuple("TPCParameter", "a e s")                  # test/example-compartment.jl:12
 VUParameter = namedtuple("VUParameter", "a e s")                    # test/example-vector.jl:30
+DTRParameter = namedtuple("DTRParameter", "a e e0 emax ec50")       # test/example-dtr.jl:22
 
 
 def dimension(p):
@@ -86,12 +87,30 @@ class VUMod(Model):
         return [self.sigma_squared]
 
 
+class DTRMod(Model):
+    """test/example-dtr.jl:4-7, docs/src/dtr.md:87-90: dose-time-response, m measurements per unit."""
+    model_id, parameter_type = _ffi.MODEL_DTR, DTRParameter
+
+    def __init__(self, sigma, m):
+        self.sigma, self.m = float(sigma), int(m)
+
+    def _params(self):
+        return [self.sigma]
+
+
 def unit_length(m):
     return m.m
 
 
 class CovariateParameterization:
     cp_id = _ffi.CP_COPY
+
+    def _params(self):
+        return []
+
+    def simplify_unique(self, d, dr, m, **uargs):
+        """Generic catch-all of the reference (src/designmeasure.jl:412-424)."""
+        return simplify_unique(d, dr, m, self, **uargs)
 
 
 class JustCopy(CovariateParameterization):
@@ -111,6 +130,63 @@ class CopyTime(CovariateParameterization):  # test/example-compartment.jl:16
 
 class EquiTime(CovariateParameterization):  # test/example-vector.jl:43
     cp_id = _ffi.CP_EQUITIME
+
+
+class CopyBoth(CovariateParameterization):
+    """docs/src/dtr.md:197-203: dose = z[0], time = z[1]; with its simplify_unique (:229-247)."""
+    cp_id = _ffi.CP_DTR_COPYBOTH
+
+    def simplify_unique(self, d, dr, m, minposdose=0, minpostime=0):
+        res = d.copy()
+        if tuple(dr.lowerbound) == (0.0, 0.0):
+            drop = (res.points[:, 0] < minposdose) | (res.points[:, 1] < minpostime)
+            res.points[drop] = 0.0
+        return res
+
+
+class FixedDose(CovariateParameterization):  # docs/src/dtr.md:331-339
+    cp_id = _ffi.CP_DTR_FIXEDDOSE
+
+    def __init__(self, dose):
+        self.dose = float(dose)
+
+    def _params(self):
+        return [self.dose]
+
+
+class FixedTimes(CovariateParameterization):  # docs/src/dtr.md:401-409
+    cp_id = _ffi.CP_DTR_FIXEDTIMES
+
+    def __init__(self, time):
+        self.time = [float(t) for t in time]
+
+    def _params(self):
+        return self.time
+
+
+class EquidistantTimes(CovariateParameterization):
+    """docs/src/dtr.md:484-495 with its simplify_unique (:498-523)."""
+    cp_id = _ffi.CP_DTR_EQUIDISTANT
+
+    def simplify_unique(self, d, dr, m, minposdose=0, minposdelta=0):
+        res = d.copy()
+        if dr.lowerbound[0] == 0:
+            drop = res.points[:, 0] <= minposdose
+            if dr.lowerbound[1] == 0:
+                drop |= res.points[:, 1] <= minposdelta
+            res.points[drop, 0] = 0.0
+            res.points[drop, 1] = dr.upperbound[1]
+        return res
+
+
+class LogEquidistantTimes(EquidistantTimes):  # docs/src/dtr.md:663-681 (same canonical representative)
+    cp_id = _ffi.CP_DTR_LOGEQUIDISTANT
+
+    def __init__(self, b):
+        self.b = float(b)
+
+    def _params(self):
+        return [self.b]
 
 
 # ------------------------------------------------------------------------------------------------
@@ -225,7 +301,7 @@ class DesignProblem:
             dt = trafo_constants(self.trafo, self.pk)
             h = _ffi.ProblemHandle(self.m.model_id, self.m._params(), self.pk.theta, self.pk.weight, self.dc.crit_id,
                                    dt, self.dr.lowerbound, self.dr.upperbound, m=self.m.m, cp_id=self.cp.cp_id,
-                                   device=self.device)
+                                   device=self.device, cp_params=self.cp._params())
             if self.comm is not None:
                 h.comm_init(*self.comm)
             self._handle_cache = h
@@ -310,7 +386,8 @@ def informationmatrix(d, m, cp, p, na):
     p = np.asarray(p, dtype=np.float64).reshape(1, -1)
     lo = np.minimum(d.points.min(axis=0), 0.0) - 1.0
     hi = d.points.max(axis=0) + 1.0
-    h = _ffi.ProblemHandle(m.model_id, m._params(), p, [1.0], _ffi.CRIT_D, None, lo, hi, m=m.m, cp_id=cp.cp_id)
+    h = _ffi.ProblemHandle(m.model_id, m._params(), p, [1.0], _ffi.CRIT_D, None, lo, hi, m=m.m, cp_id=cp.cp_id,
+                           cp_params=cp._params())
     try:
         return h.informationmatrix(d.points, d.weights, 0)
     finally:
@@ -319,7 +396,7 @@ def informationmatrix(d, m, cp, p, na):
 
 def simplify(d, dp, maxweight=0, maxdist=0, **uargs):
     """src/designproblem.jl:185-190."""
-    d = simplify_unique(d, dp.dr, dp.m, dp.cp, **uargs)
+    d = dp.cp.simplify_unique(d, dp.dr, dp.m, **uargs)
     d = simplify_merge(d, dp.dr, maxdist)
     d = simplify_drop(d, maxweight)
     return d

@@ -133,6 +133,7 @@ static int model_dims(int model_id, int *r, int *ndc)
     case KST_MODEL_SIGEMAX: *r = KstSigEmax::R; *ndc = KstSigEmax::NDC; return 0;
     case KST_MODEL_TPC: *r = KstTpc::R; *ndc = KstTpc::NDC; return 0;
     case KST_MODEL_VU: *r = KstVu::R; *ndc = KstVu::NDC; return 0;
+    case KST_MODEL_DTR: *r = KstDtr::R; *ndc = KstDtr::NDC; return 0;
     }
     return -1;
 }
@@ -155,7 +156,7 @@ extern "C" int kst_problem_destroy(kst_problem *h)
 }
 
 extern "C" int kst_problem_create(int model_id, const double *model_params, int n_model_params, int cp_id,
-                                  int criterion_id, int trafo_id, int r, int t, int m, int d, int64_t N,
+                                  const double *cp_params, int n_cp_params, int criterion_id, int trafo_id, int r, int t, int m, int d, int64_t N,
                                   const double *theta, const double *prior_w, const double *dt_jm, const double *lb,
                                   const double *ub, int device_id, kst_problem **out)
 {
@@ -172,13 +173,30 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
         // more rows than columns makes every information matrix singular (src/transformation.jl:86-88)
         if (t < 1 || t > r) { kst_set_error("DeltaMethod needs 1 <= t <= r, got t = %d", t); return KST_EINVAL; }
     } else { kst_set_error("unknown transformation %d", trafo_id); return KST_EINVAL; }
-    const bool vector_unit = model_id == KST_MODEL_VU;
-    if (m < 1 || m > KST_MAX_UNIT || (!vector_unit && m != 1)) { kst_set_error("bad unit length m = %d for model %d", m, model_id); return KST_EINVAL; }
-    if ((vector_unit && cp_id != KST_CP_EQUITIME) || (!vector_unit && cp_id != KST_CP_COPY)) {
-        kst_set_error("covariate parameterization %d not registered for model %d", cp_id, model_id);
+    // which (model, covariate parameterization, unit length, region dimension) combinations are registered
+    int want_d = 1, want_ncp = 0;
+    bool ok_m = m == 1, ok_cp = cp_id == KST_CP_COPY;
+    if (model_id == KST_MODEL_VU) {
+        ok_m = m >= 1 && m <= KST_MAX_UNIT;
+        ok_cp = cp_id == KST_CP_EQUITIME;
+    } else if (model_id == KST_MODEL_DTR) {
+        ok_m = m >= 1 && m <= KST_MAX_UNIT;
+        switch (cp_id) {
+        case KST_CP_DTR_COPYBOTH: ok_cp = true; want_d = 2; ok_m = m == 1; break;
+        case KST_CP_DTR_FIXEDDOSE: ok_cp = true; want_ncp = 1; ok_m = m == 1; break;
+        case KST_CP_DTR_FIXEDTIMES: ok_cp = true; want_ncp = m; break;
+        case KST_CP_DTR_EQUIDISTANT: ok_cp = true; want_d = 2; break;
+        case KST_CP_DTR_LOGEQUIDISTANT: ok_cp = true; want_d = 2; want_ncp = 1; ok_m = ok_m && m >= 2; break;
+        default: ok_cp = false;
+        }
+    }
+    if (!ok_cp) { kst_set_error("covariate parameterization %d not registered for model %d", cp_id, model_id); return KST_EINVAL; }
+    if (!ok_m) { kst_set_error("bad unit length m = %d for model %d with covariate parameterization %d", m, model_id, cp_id); return KST_EINVAL; }
+    if (d != want_d) { kst_set_error("design-region dimension d = %d, model %d with covariate parameterization %d needs %d", d, model_id, cp_id, want_d); return KST_EINVAL; }
+    if (want_ncp > 0 && (!cp_params || n_cp_params != want_ncp)) {
+        kst_set_error("covariate parameterization %d needs %d parameter(s), got %d", cp_id, want_ncp, cp_params ? n_cp_params : 0);
         return KST_EINVAL;
     }
-    if (d < 1 || d > KST_MAX_D || d != 1) { kst_set_error("design-region dimension d = %d not supported by model %d", d, model_id); return KST_EINVAL; }
     if (N < 1 || !theta || !prior_w || !lb || !ub) { kst_set_error("problem_create: empty prior sample or NULL buffer"); return KST_EINVAL; }
     if (n_model_params < 1 || !model_params) { kst_set_error("problem_create: model_params missing"); return KST_EINVAL; }
     for (int j = 0; j < d; j++)
@@ -200,6 +218,7 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
     h->r = r; h->t = t; h->m = m; h->d = d; h->N = N;
     h->ld = ((size_t)N + 31) / 32 * 32;
     for (int i = 0; i < 4; i++) h->mp.v[i] = i < n_model_params ? model_params[i] : 0.0;
+    for (int i = 0; i < 16; i++) h->mp.cpv[i] = (cp_params && i < n_cp_params) ? cp_params[i] : 0.0;
     h->mp.m = m; h->mp.cp = cp_id; h->mp.d = d;
     for (int j = 0; j < d; j++) { h->lb[j] = lb[j]; h->ub[j] = ub[j]; }
     h->n_aux = trafo_id == KST_TRAFO_DELTA ? t * r : (criterion_id == KST_CRIT_A ? r : 0);

@@ -40,6 +40,7 @@ void kst_set_error(const char *fmt, ...);
     case KST_MODEL_SIGEMAX: { using MF = KstSigEmax; __VA_ARGS__; } break; \
     case KST_MODEL_TPC: { using MF = KstTpc; __VA_ARGS__; } break;       \
     case KST_MODEL_VU: { using MF = KstVu; __VA_ARGS__; } break;         \
+    case KST_MODEL_DTR: { using MF = KstDtr; __VA_ARGS__; } break;       \
     default: kst_set_error("unregistered model id %d", id); return KST_EINVAL; \
     }
 

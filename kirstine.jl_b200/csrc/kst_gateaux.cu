@@ -257,8 +257,11 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
     const int64_t g = (int64_t)blockIdx.x * KST_GD_NT + threadIdx.x;
     const bool live = g < G;
 
-    // rows of this thread's direction (weight 1); trivial rows get sqrt(omega) = 0 and benign pc
+    // rows of this thread's direction (weight 1); trivial rows get sqrt(omega) = 0 and benign pc.
+    // live_mask: bit i is set when row i is live for at least one direction of the CTA; rows that are
+    // trivial for the whole CTA (time 0 of every vector unit) are skipped outright in the draw loop.
     double sw_triv = 0.0;
+    unsigned live_mask = 0;
     for (int i = 0; i < m; i++) {
         double pc[MF::NPC], varfac = 0.0;
         bool trivial = true;
@@ -272,6 +275,7 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
         MF::post_row(pc, sq);
         s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x] = sq;
         for (int c = 0; c < MF::NPC; c++) s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x] = pc[c];
+        if (__syncthreads_or(sq != 0.0)) live_mask |= 1u << i;
     }
 
     // this CTA's draw range
@@ -306,6 +310,7 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
 #pragma unroll
             for (int c = 0; c < NP; c++) Ap[c] = s_draw[(MF::NDC + c) * KST_GD_CHUNK + jj];
             for (int i = 0; i < m; i++) {
+                if (!((live_mask >> i) & 1u)) continue;  // uniform over the CTA
                 double pc[MF::NPC], gv[R];
                 const double sq = s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x];
 #pragma unroll
@@ -401,6 +406,8 @@ int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, dou
         KST_MODEL_SWITCH(h->model_id, {
             constexpr int NS = MF::NDC + KstPacked<MF::R>::N;
             const size_t smem = sizeof(double) * ((size_t)NS * KST_GD_CHUNK + (size_t)h->m * KstRowW<MF>::RW * KST_GD_NT);
+            if (smem > 48 * 1024)  // vector units with many rows: opt in to a large dynamic shared-memory window
+                KST_CUDA(cudaFuncSetAttribute(k_gateaux_eval<MF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             k_gateaux_eval<MF><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->pw, h->gA, h->ld, h->N, d_dirs, G, h->mp,
                                                                      h->gd_partials);
         });

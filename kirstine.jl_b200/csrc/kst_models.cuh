@@ -26,9 +26,11 @@
 #include <math.h>
 
 #include "kst_math.cuh"
+#include "../../include/kirstine_b200.h"
 
 struct KstModelParams {
-    double v[4];
+    double v[4];    // model parameters (sigma or sigma_squared)
+    double cpv[16]; // parameters of the covariate parameterization (fixed dose, fixed times, log base)
     int m;   // unit length
     int cp;  // covariate parameterization id
     int d;   // design-region dimension
@@ -154,5 +156,74 @@ struct KstVu : KstTpc {
         pc[1] = 0.0;
         varfac = 1.0 / (1.0 + t);
         return t == 0.0;
+    }
+};
+
+// dose-time-response model: test/example-dtr.jl:27-47, docs/src/dtr.md:87-129.  theta = (a, e, e0, emax, ec50)
+//   A = exp(-a t), B = exp(-e t), C = B - A, rd = e - a, den = dose C a - rd ec50, w = 1/den
+//   row = [-dose ec50 emax (A t a rd + e C) w^2, dose a ec50 emax (B t rd + C) w^2, 1, dose a C w, dose a emax C rd w^2]
+//       = diag(-ec50 emax, a ec50 emax, 1, a, a emax rd) [dose (A t a rd + e C) w^2, dose (B t rd + C) w^2, 1, dose C w, dose C w^2]
+// dose == 0 or t == 0 -> [0, 0, 1, 0, 0] (trivial row).
+// Covariate parameterizations (docs/src/dtr.md): CopyBoth :197-203, FixedDose :331-339, FixedTimes :401-409,
+// EquidistantTimes :484-495, LogEquidistantTimes :663-681.
+struct KstDtr {
+    static constexpr int R = 5, NDC = 7, NPC = 3, CONST_COL = 2;
+    __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
+    {
+        const double isig = 1.0 / fabs(mp.v[0]);  // v[0] = sigma
+        const double a = th[0], e = th[1], emax = th[3], ec50 = th[4], rd = e - a;
+        dc[0] = -a;
+        dc[1] = -e;
+        dc[2] = a;
+        dc[3] = rd;
+        dc[4] = a * rd;
+        dc[5] = e;
+        dc[6] = -rd * ec50;
+        cs[0] = -ec50 * emax * isig;
+        cs[1] = a * ec50 * emax * isig;
+        cs[2] = isig;
+        cs[3] = a * isig;
+        cs[4] = a * emax * rd * isig;
+    }
+    __device__ static void covariate(const double *z, int i, const KstModelParams &mp, double &dose, double &t)
+    {
+        switch (mp.cp) {
+        case KST_CP_DTR_FIXEDDOSE: dose = mp.cpv[0]; t = i == 0 ? z[0] : 0.0; break;
+        case KST_CP_DTR_FIXEDTIMES: dose = z[0]; t = mp.cpv[i]; break;
+        case KST_CP_DTR_EQUIDISTANT: dose = z[0]; t = (double)i * z[1]; break;
+        case KST_CP_DTR_LOGEQUIDISTANT: {
+            dose = z[0];
+            t = i == 0 ? 0.0 : z[1];
+            for (int j = 2; j <= i; j++) t = mp.cpv[0] * t;  // time[j] = b * time[j-1], same rounding as the reference
+            break;
+        }
+        default: dose = z[0]; t = i == 0 ? z[1] : 0.0;  // CopyBoth
+        }
+    }
+    __device__ static bool prep_row(const double *z, int i, const KstModelParams &mp, double *pc, double &varfac)
+    {
+        double dose, t;
+        covariate(z, i, mp, dose, t);
+        pc[0] = t;
+        pc[1] = dose;
+        pc[2] = 0.0;
+        varfac = 1.0;
+        return dose == 0.0 || t == 0.0;
+    }
+    __device__ static void post_row(double *pc, double sw) { pc[2] = sw * pc[1]; }
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
+    {
+        const double t = pc[0];
+        const double A = kst_exp(dc[0] * t, tab);
+        const double B = kst_exp(dc[1] * t, tab);
+        const double C = B - A;
+        const double w = kst_rcp(fma(pc[1] * C, dc[2], dc[6]));  // 1 / (dose C a - rd ec50)
+        const double sdw = pc[2] * w;                             // sw dose w
+        const double sdw2 = sdw * w;
+        g[0] = sdw2 * fma(A * t, dc[4], dc[5] * C);
+        g[1] = sdw2 * fma(B * t, dc[3], C);
+        g[2] = sw;
+        g[3] = sdw * C;
+        g[4] = sdw2 * C;
     }
 };

@@ -14,7 +14,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "libkirstine_oracle.so")
 
 EMAX, SIGEMAX, TPC, VU, DTR = 1, 2, 3, 4, 5
-CP_COPY, CP_EQUITIME, CP_DTR_EQUIDISTANT = 0, 1, 2
+CP_COPY, CP_EQUITIME = 0, 1
+CP_DTR_COPYBOTH, CP_DTR_FIXEDDOSE, CP_DTR_FIXEDTIMES, CP_DTR_EQUIDISTANT, CP_DTR_LOGEQUIDISTANT = 2, 3, 4, 5, 6
 CRIT_D, CRIT_A = 0, 1
 TRAFO_IDENTITY, TRAFO_DELTA = 0, 1
 
@@ -42,7 +43,7 @@ def lib():
         build()
         L = C.CDLL(_LIB_PATH)
         L.ko_create.restype = C.c_void_p
-        L.ko_create.argtypes = [C.c_int, _dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+        L.ko_create.argtypes = [C.c_int, _dp, C.c_int, C.c_int, _dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                 C.c_int, C.c_int, C.c_long, _dp, _dp, _dp]
         L.ko_destroy.argtypes = [C.c_void_p]
         L.ko_objective.restype = C.c_double
@@ -100,7 +101,7 @@ class Problem:
     """
 
     def __init__(self, model_id, model_params, theta, prior_weights=None, crit=CRIT_D,
-                 dt=None, m=1, d=1, cp_id=CP_COPY):
+                 dt=None, m=1, d=1, cp_id=CP_COPY, cp_params=()):
         theta = _f64(theta)
         self.N, self.r = theta.shape
         self.m, self.d = int(m), int(d)
@@ -115,9 +116,11 @@ class Problem:
             # per draw column-major t x r, like Julia's Matrix{Float64}
             dtc = _f64(np.transpose(dt, (0, 2, 1)).reshape(self.N, -1))
         mp = _f64(model_params)
+        cpp = _f64(cp_params) if len(cp_params) else None
         self.crit = crit
         self.model_id = model_id
-        self._h = lib().ko_create(model_id, _d(mp), len(mp), cp_id, crit, self.trafo, self.r, self.t,
+        self._h = lib().ko_create(model_id, _d(mp), len(mp), cp_id, _d(cpp), 0 if cpp is None else len(cpp), crit,
+                                  self.trafo, self.r, self.t,
                                   self.m, self.d, self.N, _d(theta), _d(pw), _d(dtc))
         if not self._h:
             raise ValueError("oracle: dimensions out of range")

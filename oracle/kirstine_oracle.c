@@ -35,7 +35,8 @@
 #define KO_MAXD 4
 
 enum { KO_EMAX = 1, KO_SIGEMAX = 2, KO_TPC = 3, KO_VU = 4, KO_DTR = 5 };
-enum { KO_CP_COPY = 0, KO_CP_EQUITIME = 1, KO_CP_DTR_EQUIDISTANT = 2 };
+enum { KO_CP_COPY = 0, KO_CP_EQUITIME = 1, KO_CP_DTR_COPYBOTH = 2, KO_CP_DTR_FIXEDDOSE = 3,
+       KO_CP_DTR_FIXEDTIMES = 4, KO_CP_DTR_EQUIDISTANT = 5, KO_CP_DTR_LOGEQUIDISTANT = 6 };
 enum { KO_CRIT_D = 0, KO_CRIT_A = 1 };
 enum { KO_TRAFO_IDENTITY = 0, KO_TRAFO_DELTA = 1 };
 
@@ -44,6 +45,7 @@ typedef struct {
     int r, t, m, d;
     long N;
     double mp[4];
+    double cpp[KO_MAXM]; /* parameters of the covariate parameterization */
     double *theta; /* N x r, AoS (one parameter struct after the other) */
     double *pw;    /* N prior weights */
     double *dt;    /* N x (t x r col-major), NULL for identity */
@@ -66,11 +68,30 @@ static void ko_covariate(const ko_problem *p, const double *z, double *c)
     case KO_VU:
         for (int j = 0; j < p->m; j++) c[j] = (double)j * z[0];
         break;
-    case KO_DTR:
-        c[0] = z[0];
-        if (p->cp_id == KO_CP_DTR_EQUIDISTANT) {
+    case KO_DTR: /* docs/src/dtr.md: CopyBoth :197-203, FixedDose :331-339, FixedTimes :401-409,
+                    EquidistantTimes :484-495, LogEquidistantTimes :663-681 */
+        switch (p->cp_id) {
+        case KO_CP_DTR_FIXEDDOSE:
+            c[0] = p->cpp[0];
+            for (int j = 0; j < p->m; j++) c[1 + j] = 0.0;
+            c[1] = z[0];
+            break;
+        case KO_CP_DTR_FIXEDTIMES:
+            c[0] = z[0];
+            for (int j = 0; j < p->m; j++) c[1 + j] = p->cpp[j];
+            break;
+        case KO_CP_DTR_EQUIDISTANT:
+            c[0] = z[0];
             for (int j = 0; j < p->m; j++) c[1 + j] = (double)j * z[1];
-        } else {
+            break;
+        case KO_CP_DTR_LOGEQUIDISTANT:
+            c[0] = z[0];
+            c[1] = 0.0;
+            if (p->m > 1) c[2] = z[1];
+            for (int j = 2; j < p->m; j++) c[1 + j] = p->cpp[0] * c[j];
+            break;
+        default: /* CopyBoth */
+            c[0] = z[0];
             for (int j = 0; j < p->m; j++) c[1 + j] = 0.0;
             c[1] = z[1];
         }
@@ -610,8 +631,8 @@ void ko_gateaux_batch(const ko_problem *p, long G, const double *dirs, const dou
 /* problem handle                                                             */
 /* ------------------------------------------------------------------------- */
 
-ko_problem *ko_create(int model_id, const double *mp, int nmp, int cp_id, int crit, int trafo,
-                      int r, int t, int m, int d, long N, const double *theta,
+ko_problem *ko_create(int model_id, const double *mp, int nmp, int cp_id, const double *cpp, int ncpp,
+                      int crit, int trafo, int r, int t, int m, int d, long N, const double *theta,
                       const double *pw, const double *dt)
 {
     if (r > KO_MAXR || t > KO_MAXR || m > KO_MAXM || d > KO_MAXD) return NULL;
@@ -619,6 +640,7 @@ ko_problem *ko_create(int model_id, const double *mp, int nmp, int cp_id, int cr
     p->model_id = model_id; p->cp_id = cp_id; p->crit = crit; p->trafo = trafo;
     p->r = r; p->t = t; p->m = m; p->d = d; p->N = N;
     for (int i = 0; i < nmp && i < 4; i++) p->mp[i] = mp[i];
+    for (int i = 0; i < ncpp && i < KO_MAXM; i++) p->cpp[i] = cpp[i];
     p->theta = (double *)malloc(sizeof(double) * N * r);
     memcpy(p->theta, theta, sizeof(double) * N * r);
     p->pw = (double *)malloc(sizeof(double) * N);

@@ -12,11 +12,43 @@ import numpy as np
 LD = np.longdouble
 
 
-def rows(model, mp, z, theta, m=1):
+def dtr_covariate(cp, cpp, z, m):
+    """(dose, [time_1..time_m]) of the DTR covariate parameterizations (docs/src/dtr.md)."""
+    z = np.atleast_1d(np.asarray(z, dtype=np.float64))
+    if cp == 3:
+        return cpp[0], [z[0]] + [0.0] * (m - 1)
+    if cp == 4:
+        return z[0], list(cpp[:m])
+    if cp == 5:
+        return z[0], [float(j) * z[1] for j in range(m)]
+    if cp == 6:
+        t = [0.0, z[1]]
+        for _ in range(2, m):
+            t.append(cpp[0] * t[-1])
+        return z[0], t[:m]
+    return z[0], [z[1]] + [0.0] * (m - 1)
+
+
+def rows(model, mp, z, theta, m=1, cov=None):
     """Whitened Jacobian rows of one design point for all draws: (N, m, r) long double."""
     th = theta.astype(LD)
-    z = LD(z)
     N = len(th)
+    if model == 5:  # DTR, mp = sigma; cov = (cp_id, cp_params)
+        dose, times = dtr_covariate(cov[0], cov[1], z, m)
+        a, e, e0, emax, ec50 = th.T
+        dose = LD(dose)
+        out = []
+        for t in times:
+            t = LD(t)
+            A, B = np.exp(-a * t), np.exp(-e * t)
+            C, rd = B - A, e - a
+            den = dose * C * a - rd * ec50
+            g = np.stack([-dose * ec50 * emax * (A * t * a * rd + e * C) / den ** 2,
+                          dose * a * ec50 * emax * (B * t * rd + C) / den ** 2, np.ones(N, LD), dose * a * C / den,
+                          dose * a * emax * C * rd / den ** 2], axis=1)
+            out.append(g / abs(LD(mp[0])))
+        return np.stack(out, axis=1)
+    z = LD(np.atleast_1d(z)[0])
     if model == 1:  # Emax, mp = sigma_squared
         e0, emax, ec50 = th.T
         g = np.stack([np.ones(N, LD), z / (z + ec50), -emax * z / (z + ec50) ** 2], axis=1)[:, None, :]
@@ -44,11 +76,12 @@ def rows(model, mp, z, theta, m=1):
     raise KeyError(model)
 
 
-def infomatrix(model, mp, pts, w, theta, m=1):
-    pts = np.asarray(pts, dtype=np.float64).reshape(-1)
+def infomatrix(model, mp, pts, w, theta, m=1, cov=None):
+    w = np.asarray(w, dtype=np.float64).ravel()
+    pts = np.asarray(pts, dtype=np.float64).reshape(len(w), -1)
     M = 0
-    for z, wk in zip(pts, np.asarray(w, dtype=np.float64)):
-        g = rows(model, mp, z, theta, m)
+    for z, wk in zip(pts, w):
+        g = rows(model, mp, z, theta, m, cov)
         M = M + LD(wk) * np.einsum("nia,nib->nab", g, g)
     return M
 
@@ -75,8 +108,8 @@ def inv_spd(M):
     return I, ok, logdet
 
 
-def objective(model, mp, pts, w, theta, pw, crit=0, dt=None, m=1):
-    M = infomatrix(model, mp, pts, w, theta, m)
+def objective(model, mp, pts, w, theta, pw, crit=0, dt=None, m=1, cov=None):
+    M = infomatrix(model, mp, pts, w, theta, m, cov)
     iM, ok, logdet = inv_spd(M)
     if not ok.all():
         return -np.inf
@@ -95,8 +128,8 @@ def objective(model, mp, pts, w, theta, pw, crit=0, dt=None, m=1):
     return float(np.sum(pw.astype(LD) * val))
 
 
-def gateaux(model, mp, at_pts, at_w, dirs, theta, pw, crit=0, dt=None, m=1):
-    M = infomatrix(model, mp, at_pts, at_w, theta, m)
+def gateaux(model, mp, at_pts, at_w, dirs, theta, pw, crit=0, dt=None, m=1, cov=None):
+    M = infomatrix(model, mp, at_pts, at_w, theta, m, cov)
     iM, ok, _ = inv_spd(M)
     assert ok.all()
     r = M.shape[-1]
@@ -117,8 +150,9 @@ def gateaux(model, mp, at_pts, at_w, dirs, theta, pw, crit=0, dt=None, m=1):
             A = np.einsum("nij,naj,nak,nkl->nil", iM, D, D, iM)
             trB = np.trace(C, axis1=1, axis2=2)
     out = []
-    for z in np.asarray(dirs, dtype=np.float64).reshape(-1):
-        Md = infomatrix(model, mp, [z], [1.0], theta, m)
+    d = np.asarray(at_pts, dtype=np.float64).reshape(len(np.ravel(at_w)), -1).shape[1]
+    for z in np.asarray(dirs, dtype=np.float64).reshape(-1, d):
+        Md = infomatrix(model, mp, [z], [1.0], theta, m, cov)
         out.append(float(np.sum(pw.astype(LD) * (np.einsum("nab,nab->n", A, Md) - trB))))
     return np.array(out)
 

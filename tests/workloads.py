@@ -57,3 +57,25 @@ def jittered_swarm(S, K, lb, ub, seed=0, log_lo=None):
         pts = np.exp(np.log(log_lo) + u * (np.log(ub) - np.log(log_lo)))
     w = rng.dirichlet(np.full(K, 4.0), size=S)
     return pts.reshape(S, K, 1), w
+
+
+def dtr_prior(n, seed=4711):  # docs/src/dtr.md:133-147 (draw_from_prior)
+    rng = np.random.default_rng(seed)
+    return np.column_stack([0.5 + 0.10 * rng.standard_normal(n), 0.1 + 0.02 * rng.standard_normal(n),
+                            1.0 + 0.25 * rng.standard_normal(n), 2.0 + 0.50 * rng.standard_normal(n),
+                            np.exp(2.3 + 0.6 * rng.standard_normal(n))])
+
+
+def jittered_swarm_nd(S, K, lb, ub, seed=0):
+    """Well-separated random designs in a d-dimensional box: coordinate c of point k lies in the
+    ((k * (c + 1)) mod K)-th of K equal cells, so no two points share a cell in any coordinate."""
+    rng = np.random.default_rng(seed)
+    lb, ub = np.asarray(lb, float), np.asarray(ub, float)
+    d = len(lb)
+    pts = np.empty((S, K, d))
+    for c in range(d):
+        cell = (np.arange(K) * (c + 1) + c) % K
+        u = (cell + 0.15 + 0.7 * rng.random((S, K))) / K
+        pts[:, :, c] = lb[c] + (ub[c] - lb[c]) * u
+    w = rng.dirichlet(np.full(K, 4.0), size=S)
+    return pts, w
