@@ -4,8 +4,8 @@
 // instruction every two cycles per SM sub-partition) and, almost as tightly, by instruction issue.
 // libdevice's exp costs 15 FP64 instructions plus ~25 issue slots of 64-bit immediates (UMOV pairs)
 // and slow-path branches; its division adds a denormal/overflow fix-up call.  The versions below
-//   kst_exp : 32-entry 2^(j/32) table in shared memory + degree-6 Taylor polynomial on
-//             |r| <= ln2/64 (truncation error 3.5e-18)                     -> 11 FP64 instructions
+//   kst_exp : 64-entry 2^(j/64) table in shared memory + degree-5 polynomial on
+//             |r| <= ln2/128 (truncation error 4.4e-18)                    -> 10 FP64 instructions
 //   kst_log : 64-entry (c_i ~ 1/m_i, -log c_i) table + degree-7 log1p polynomial on
 //             |r| <= 2^-7 (truncation error 1.7e-18)                       -> 12 FP64 instructions
 //   kst_rcp : MUFU.RCP64H seed + one cubic step (e + e^2)                  ->  3 FP64 instructions
@@ -18,22 +18,33 @@
 #pragma once
 #include <math.h>
 
-__constant__ double kst_exp2_tab_c[32] = {
-    0x1.0000000000000p+0, 0x1.059b0d3158574p+0, 0x1.0b5586cf9890fp+0, 0x1.11301d0125b51p+0,
-    0x1.172b83c7d517bp+0, 0x1.1d4873168b9aap+0, 0x1.2387a6e756238p+0, 0x1.29e9df51fdee1p+0,
-    0x1.306fe0a31b715p+0, 0x1.371a7373aa9cbp+0, 0x1.3dea64c123422p+0, 0x1.44e086061892dp+0,
-    0x1.4bfdad5362a27p+0, 0x1.5342b569d4f82p+0, 0x1.5ab07dd485429p+0, 0x1.6247eb03a5585p+0,
-    0x1.6a09e667f3bcdp+0, 0x1.71f75e8ec5f74p+0, 0x1.7a11473eb0187p+0, 0x1.82589994cce13p+0,
-    0x1.8ace5422aa0dbp+0, 0x1.93737b0cdc5e5p+0, 0x1.9c49182a3f090p+0, 0x1.a5503b23e255dp+0,
-    0x1.ae89f995ad3adp+0, 0x1.b7f76f2fb5e47p+0, 0x1.c199bdd85529cp+0, 0x1.cb720dcef9069p+0,
-    0x1.d5818dcfba487p+0, 0x1.dfc97337b9b5fp+0, 0x1.ea4afa2a490dap+0, 0x1.f50765b6e4540p+0};
+__constant__ double kst_exp2_tab_c[64] = {  // 2^(j/64), correctly rounded
+    0x1.0000000000000p+0, 0x1.02c9a3e778061p+0, 0x1.059b0d3158574p+0, 0x1.0874518759bc8p+0,
+    0x1.0b5586cf9890fp+0, 0x1.0e3ec32d3d1a2p+0, 0x1.11301d0125b51p+0, 0x1.1429aaea92de0p+0,
+    0x1.172b83c7d517bp+0, 0x1.1a35beb6fcb75p+0, 0x1.1d4873168b9aap+0, 0x1.2063b88628cd6p+0,
+    0x1.2387a6e756238p+0, 0x1.26b4565e27cddp+0, 0x1.29e9df51fdee1p+0, 0x1.2d285a6e4030bp+0,
+    0x1.306fe0a31b715p+0, 0x1.33c08b26416ffp+0, 0x1.371a7373aa9cbp+0, 0x1.3a7db34e59ff7p+0,
+    0x1.3dea64c123422p+0, 0x1.4160a21f72e2ap+0, 0x1.44e086061892dp+0, 0x1.486a2b5c13cd0p+0,
+    0x1.4bfdad5362a27p+0, 0x1.4f9b2769d2ca7p+0, 0x1.5342b569d4f82p+0, 0x1.56f4736b527dap+0,
+    0x1.5ab07dd485429p+0, 0x1.5e76f15ad2148p+0, 0x1.6247eb03a5585p+0, 0x1.6623882552225p+0,
+    0x1.6a09e667f3bcdp+0, 0x1.6dfb23c651a2fp+0, 0x1.71f75e8ec5f74p+0, 0x1.75feb564267c9p+0,
+    0x1.7a11473eb0187p+0, 0x1.7e2f336cf4e62p+0, 0x1.82589994cce13p+0, 0x1.868d99b4492edp+0,
+    0x1.8ace5422aa0dbp+0, 0x1.8f1ae99157736p+0, 0x1.93737b0cdc5e5p+0, 0x1.97d829fde4e50p+0,
+    0x1.9c49182a3f090p+0, 0x1.a0c667b5de565p+0, 0x1.a5503b23e255dp+0, 0x1.a9e6b5579fdbfp+0,
+    0x1.ae89f995ad3adp+0, 0x1.b33a2b84f15fbp+0, 0x1.b7f76f2fb5e47p+0, 0x1.bcc1e904bc1d2p+0,
+    0x1.c199bdd85529cp+0, 0x1.c67f12e57d14bp+0, 0x1.cb720dcef9069p+0, 0x1.d072d4a07897cp+0,
+    0x1.d5818dcfba487p+0, 0x1.da9e603db3285p+0, 0x1.dfc97337b9b5fp+0, 0x1.e502ee78b3ff6p+0,
+    0x1.ea4afa2a490dap+0, 0x1.efa1bee615a27p+0, 0x1.f50765b6e4540p+0, 0x1.fa7c1819e90d8p+0};
 
-// 0: 32/ln2   1: 1.5*2^52   2: -ln2/32 (high 38 bits)   3: -ln2/32 (low)   4..8: 1/6!, 1/5!, 1/4!, 1/3!, 1/2!
-__constant__ double kst_mc[9] = {0x1.71547652b82fep+5, 6755399441055744.0, -0x1.62e42fefa0000p-6,
-                                 -0x1.cf79abc9e3b3ap-45, 0x1.6c16c16c16c17p-10, 0x1.1111111111111p-7,
-                                 0x1.5555555555555p-5, 0x1.5555555555555p-3, 0.5};
+// 0: 64/ln2   1: 1.5*2^52   2: -ln2/64 (high 38 bits)   3: -ln2/64 (low)
+// 4..7: c5, c4, c3, c2 of exp(r) ~ 1 + r + r^2 (c2 + c3 r + c4 r^2 + c5 r^3) on |r| <= ln2/128
+// (interpolation at Chebyshev nodes; truncation error 4.4e-18 relative)
+__constant__ double kst_mc[8] = {0x1.71547652b82fep+6, 6755399441055744.0, -0x1.62e42fefa0000p-7,
+                                 -0x1.cf79abc9e3b3ap-46, 0x1.11111d8fbe766p-7, 0x1.55556b3304ec0p-5,
+                                 0x1.5555555555255p-3, 0x1.ffffffffff57fp-2};
 
-#define KST_EXP_TAB_N 32
+#define KST_EXP_TAB_N 64
+#define KST_EXP_TAB_SHIFT 6
 #define KST_LOG_TAB_N 64
 
 // (c_i, -log c_i), c_i = 1/(1 + (i + 0.5)/64) rounded to 13 bits, so that r = m c_i - 1 has |r| <= 2^-7
@@ -117,13 +128,12 @@ __device__ __forceinline__ double kst_exp(double x, KstTab tab)
     double p = fma(kst_mc[4], r, kst_mc[5]);
     p = fma(p, r, kst_mc[6]);
     p = fma(p, r, kst_mc[7]);
-    p = fma(p, r, kst_mc[8]);
     const double r2 = r * r;
     p = fma(r2, p, r);
     double T;
-    asm("ld.shared.f64 %0, [%1];" : "=d"(T) : "r"(tab + (unsigned)((n & (KST_EXP_TAB_N - 1)) << 3)));
+    asm("ld.shared.f64 %0, [%1];" : "=d"(T) : "r"(tab + (((unsigned)n & (KST_EXP_TAB_N - 1u)) << 3)));
     const double y = fma(T, p, T);
-    const int k = min(max(n >> 5, -1021), 1022);
+    const int k = min(max(n >> KST_EXP_TAB_SHIFT, -1021), 1022);
     return __hiloint2double(__double2hiint(y) + (k << 20), __double2loint(y));
 }
 
