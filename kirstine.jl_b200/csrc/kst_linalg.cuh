@@ -111,6 +111,35 @@ __device__ __forceinline__ double kst_log_det(const double (&dv)[R], KstTab tab)
     return s;
 }
 
+#ifndef KST_DET_CLOSED
+#define KST_DET_CLOSED 1
+#endif
+
+// log det of a 4 x 4 matrix whose first pivot M00 (and its reciprocal) are per-particle constants:
+// Schur complement of M00 (3 x 3), then its determinant by cofactors along the last row, which yields the
+// leading minors m1 = S00, m2 = S00 S11 - S01^2, m3 = det S on the way.  No reciprocal, 19 FP64 instructions.
+// Positive definite <=> m1, m2, m3 > 0; their sign bits are OR-ed into the range test like in kst_log_det.
+__device__ __forceinline__ double kst_log_det4_inv0(const double *M, double inv0, KstTab tab)
+{
+    const double t1 = M[kst_pidx<4>(0, 1)] * inv0, t2 = M[kst_pidx<4>(0, 2)] * inv0, t3 = M[kst_pidx<4>(0, 3)] * inv0;
+    const double s00 = fma(-t1, M[kst_pidx<4>(0, 1)], M[kst_pidx<4>(1, 1)]);
+    const double s01 = fma(-t1, M[kst_pidx<4>(0, 2)], M[kst_pidx<4>(1, 2)]);
+    const double s02 = fma(-t1, M[kst_pidx<4>(0, 3)], M[kst_pidx<4>(1, 3)]);
+    const double s11 = fma(-t2, M[kst_pidx<4>(0, 2)], M[kst_pidx<4>(2, 2)]);
+    const double s12 = fma(-t2, M[kst_pidx<4>(0, 3)], M[kst_pidx<4>(2, 3)]);
+    const double s22 = fma(-t3, M[kst_pidx<4>(0, 3)], M[kst_pidx<4>(3, 3)]);
+    const double m2 = fma(s00, s11, -(s01 * s01));
+    const double c12 = fma(s00, s12, -(s01 * s02));
+    const double c02 = fma(s01, s12, -(s11 * s02));
+    const double m3 = fma(s22, m2, fma(s02, c02, -(s12 * c12)));
+    const double prod = M[kst_pidx<4>(0, 0)] * m3;
+    const int signs = __double2hiint(s00) | __double2hiint(m2) | __double2hiint(m3);
+    const unsigned key = ((unsigned)signs & 0x80000000u) | (unsigned)__double2hiint(prod);
+    if (((key >> 20) - 123u) < 1800u) return kst_log(prod, tab);
+    if (!(s00 > 0.0) || !(m2 > 0.0) || !(m3 > 0.0)) return -KST_INF;
+    return log(M[kst_pidx<4>(0, 0)]) + log(m3);
+}
+
 // Per-(particle, draw) criterion value from the accumulated Mt.
 //
 // CRIT 0 = D, 1 = A.  T = 0: Identity; T >= 1: DeltaMethod with codomain dimension T.
@@ -128,6 +157,9 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
     double L[R][R], dv[R], dinv[R];
     exc = false;
     if (CRIT == 0 && T == 0) {
+#if KST_DET_CLOSED
+        if (R == 4 && INV0) return kst_log_det4_inv0(M, inv0, tab);
+#endif
         kst_ldlt<R, INV0, false>(M, L, dv, dinv, false, inv0);
         return kst_log_det<R, INV0>(dv, tab);
     }

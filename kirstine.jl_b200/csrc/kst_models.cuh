@@ -25,6 +25,10 @@
 #pragma once
 #include <math.h>
 
+#ifndef KST_SU_FMA
+#define KST_SU_FMA 1
+#endif
+
 #include "kst_math.cuh"
 #include "../../include/kirstine_b200.h"
 
@@ -98,7 +102,11 @@ struct KstSigEmax {
         const double e = kst_exp(q, tab);
         const double a = kst_rcp(1.0 + e);
         const double sa = sw * a;
+#if KST_SU_FMA
+        const double su = fma(-sa, a, sa);  // sw a (1 - a) = sw e / (1+e)^2, one instruction
+#else
         const double su = sa * (e * a);  // sw e / (1+e)^2
+#endif
         g[0] = sw;
         g[1] = sa;
         g[2] = su;
