@@ -140,6 +140,39 @@ __device__ __forceinline__ double kst_log_det4_inv0(const double *M, double inv0
     return log(M[kst_pidx<4>(0, 0)]) + log(m3);
 }
 
+// 3 x 3 analogue.  INV0: first pivot and its reciprocal are per-particle constants (constant column);
+// otherwise the plain cofactor expansion along the last row with m1 = M00, m2 = M00 M11 - M01^2.
+template <bool INV0>
+__device__ __forceinline__ double kst_log_det3(const double *M, double inv0, KstTab tab)
+{
+    double m1, m2, m3, lead;
+    if (INV0) {
+        const double t1 = M[kst_pidx<3>(0, 1)] * inv0, t2 = M[kst_pidx<3>(0, 2)] * inv0;
+        const double s00 = fma(-t1, M[kst_pidx<3>(0, 1)], M[kst_pidx<3>(1, 1)]);
+        const double s01 = fma(-t1, M[kst_pidx<3>(0, 2)], M[kst_pidx<3>(1, 2)]);
+        const double s11 = fma(-t2, M[kst_pidx<3>(0, 2)], M[kst_pidx<3>(2, 2)]);
+        m1 = s00;
+        m2 = fma(s00, s11, -(s01 * s01));
+        m3 = m2;
+        lead = M[kst_pidx<3>(0, 0)];
+    } else {
+        const double a = M[kst_pidx<3>(0, 0)], b = M[kst_pidx<3>(0, 1)], c = M[kst_pidx<3>(0, 2)];
+        const double d = M[kst_pidx<3>(1, 1)], e = M[kst_pidx<3>(1, 2)], f = M[kst_pidx<3>(2, 2)];
+        m1 = a;
+        m2 = fma(a, d, -(b * b));
+        const double c12 = fma(a, e, -(b * c));
+        const double c02 = fma(b, e, -(d * c));
+        m3 = fma(f, m2, fma(c, c02, -(e * c12)));
+        lead = 1.0;
+    }
+    const double prod = INV0 ? lead * m3 : m3;
+    const int signs = __double2hiint(m1) | __double2hiint(m2) | __double2hiint(m3);
+    const unsigned key = ((unsigned)signs & 0x80000000u) | (unsigned)__double2hiint(prod);
+    if (((key >> 20) - 123u) < 1800u) return kst_log(prod, tab);
+    if (!(m1 > 0.0) || !(m2 > 0.0) || !(m3 > 0.0)) return -KST_INF;
+    return INV0 ? log(lead) + log(m3) : log(m3);
+}
+
 // Per-(particle, draw) criterion value from the accumulated Mt.
 //
 // CRIT 0 = D, 1 = A.  T = 0: Identity; T >= 1: DeltaMethod with codomain dimension T.
@@ -159,6 +192,7 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
     if (CRIT == 0 && T == 0) {
 #if KST_DET_CLOSED
         if (R == 4 && INV0) return kst_log_det4_inv0(M, inv0, tab);
+        if (R == 3) return kst_log_det3<INV0>(M, inv0, tab);
 #endif
         kst_ldlt<R, INV0, false>(M, L, dv, dinv, false, inv0);
         return kst_log_det<R, INV0>(dv, tab);
