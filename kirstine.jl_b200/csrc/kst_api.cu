@@ -222,6 +222,9 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
     h->mp.m = m; h->mp.cp = cp_id; h->mp.d = d;
     for (int j = 0; j < d; j++) { h->lb[j] = lb[j]; h->ub[j] = ub[j]; }
     h->n_aux = trafo_id == KST_TRAFO_DELTA ? t * r : (criterion_id == KST_CRIT_A ? r : 0);
+    h->uniform_w = prior_w[0] > 0.0 && prior_w[0] < 1e300;
+    for (int64_t j = 1; j < N && h->uniform_w; j++) h->uniform_w = prior_w[j] == prior_w[0];
+    h->w_uniform = prior_w[0];
 
     int rc = KST_OK;
     double *d_theta_aos = nullptr, *d_dt = nullptr;

@@ -78,6 +78,8 @@ struct kst_problem {
     double *aux = nullptr;     // A/Identity: r (1/cs^2); DeltaMethod: t*r (DT/cs); else unused
     int n_aux = 0;
     double offset = 0.0;       // sum_j pw_j * 2 sum_i log|cs_ij|  (D / Identity), else 0
+    int uniform_w = 0;         // all prior weights of this handle are the same positive finite number ...
+    double w_uniform = 0.0;    // ... namely this one
 
     // scratch for the objective kernel: partial sums [S][n_blk]
     double *partials = nullptr;

@@ -84,93 +84,69 @@ __device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], dou
     return ok;
 }
 
-// log det from the pivots with one log call and NO floating-point compares: the pivots' sign bits are
-// OR-ed into the high word of their product and a single unsigned test on the exponent field accepts
-// "all pivots positive and 2^-900 < product < 2^900".  Everything else (a non-positive or NaN pivot, an
-// out-of-range product) takes the slow path, which applies the reference's rule pivot by pivot:
-// any pivot that is not > 0 gives -Inf (log_det!, src/design-common.jl:213-220).
-// SKIP0: dv[0] is a per-particle constant already known to be positive.
-template <int R, bool SKIP0>
-__device__ __forceinline__ double kst_log_det(const double (&dv)[R], KstTab tab)
+// Determinant of Mt as ONE product plus the OR of the high words of its leading minors (or pivots), without
+// any reciprocal where a closed form is cheap:
+//   r = 4, first pivot a per-particle constant: Schur complement of M00 (3 x 3), then its determinant by
+//          cofactors along the last row, which yields m1 = S00, m2 = S00 S11 - S01^2, m3 = det S (19 FP64);
+//   r = 3: the same one level down, or the plain cofactor expansion when there is no constant column;
+//   otherwise: LDL' pivots.
+// Positive definite <=> all leading minors (equivalently all pivots) > 0 <=> sign bit of `signs` clear and
+// prod > 0; this is the reference's "potrf! succeeded and every U[i,i] > 0" (src/design-common.jl:213-220).
+template <int R, bool INV0>
+__device__ __forceinline__ void kst_det_signs(const double *M, double inv0, double &prod, int &signs)
 {
-    double prod = dv[0];
-    int signs = SKIP0 ? 0 : __double2hiint(dv[0]);
-#pragma unroll
-    for (int j = 1; j < R; j++) {
-        prod *= dv[j];
-        signs |= __double2hiint(dv[j]);
-    }
-    const unsigned key = ((unsigned)signs & 0x80000000u) | (unsigned)__double2hiint(prod);
-    if (((key >> 20) - 123u) < 1800u) return kst_log(prod, tab);
-    double s = 0.0;
-#pragma unroll
-    for (int j = 0; j < R; j++) {
-        if (!(dv[j] > 0.0)) return -KST_INF;
-        s += log(dv[j]);
-    }
-    return s;
-}
-
-#ifndef KST_DET_CLOSED
-#define KST_DET_CLOSED 1
-#endif
-
-// log det of a 4 x 4 matrix whose first pivot M00 (and its reciprocal) are per-particle constants:
-// Schur complement of M00 (3 x 3), then its determinant by cofactors along the last row, which yields the
-// leading minors m1 = S00, m2 = S00 S11 - S01^2, m3 = det S on the way.  No reciprocal, 19 FP64 instructions.
-// Positive definite <=> m1, m2, m3 > 0; their sign bits are OR-ed into the range test like in kst_log_det.
-__device__ __forceinline__ double kst_log_det4_inv0(const double *M, double inv0, KstTab tab)
-{
-    const double t1 = M[kst_pidx<4>(0, 1)] * inv0, t2 = M[kst_pidx<4>(0, 2)] * inv0, t3 = M[kst_pidx<4>(0, 3)] * inv0;
-    const double s00 = fma(-t1, M[kst_pidx<4>(0, 1)], M[kst_pidx<4>(1, 1)]);
-    const double s01 = fma(-t1, M[kst_pidx<4>(0, 2)], M[kst_pidx<4>(1, 2)]);
-    const double s02 = fma(-t1, M[kst_pidx<4>(0, 3)], M[kst_pidx<4>(1, 3)]);
-    const double s11 = fma(-t2, M[kst_pidx<4>(0, 2)], M[kst_pidx<4>(2, 2)]);
-    const double s12 = fma(-t2, M[kst_pidx<4>(0, 3)], M[kst_pidx<4>(2, 3)]);
-    const double s22 = fma(-t3, M[kst_pidx<4>(0, 3)], M[kst_pidx<4>(3, 3)]);
-    const double m2 = fma(s00, s11, -(s01 * s01));
-    const double c12 = fma(s00, s12, -(s01 * s02));
-    const double c02 = fma(s01, s12, -(s11 * s02));
-    const double m3 = fma(s22, m2, fma(s02, c02, -(s12 * c12)));
-    const double prod = M[kst_pidx<4>(0, 0)] * m3;
-    const int signs = __double2hiint(s00) | __double2hiint(m2) | __double2hiint(m3);
-    const unsigned key = ((unsigned)signs & 0x80000000u) | (unsigned)__double2hiint(prod);
-    if (((key >> 20) - 123u) < 1800u) return kst_log(prod, tab);
-    if (!(s00 > 0.0) || !(m2 > 0.0) || !(m3 > 0.0)) return -KST_INF;
-    return log(M[kst_pidx<4>(0, 0)]) + log(m3);
-}
-
-// 3 x 3 analogue.  INV0: first pivot and its reciprocal are per-particle constants (constant column);
-// otherwise the plain cofactor expansion along the last row with m1 = M00, m2 = M00 M11 - M01^2.
-template <bool INV0>
-__device__ __forceinline__ double kst_log_det3(const double *M, double inv0, KstTab tab)
-{
-    double m1, m2, m3, lead;
-    if (INV0) {
-        const double t1 = M[kst_pidx<3>(0, 1)] * inv0, t2 = M[kst_pidx<3>(0, 2)] * inv0;
-        const double s00 = fma(-t1, M[kst_pidx<3>(0, 1)], M[kst_pidx<3>(1, 1)]);
-        const double s01 = fma(-t1, M[kst_pidx<3>(0, 2)], M[kst_pidx<3>(1, 2)]);
-        const double s11 = fma(-t2, M[kst_pidx<3>(0, 2)], M[kst_pidx<3>(2, 2)]);
-        m1 = s00;
-        m2 = fma(s00, s11, -(s01 * s01));
-        m3 = m2;
-        lead = M[kst_pidx<3>(0, 0)];
-    } else {
-        const double a = M[kst_pidx<3>(0, 0)], b = M[kst_pidx<3>(0, 1)], c = M[kst_pidx<3>(0, 2)];
-        const double d = M[kst_pidx<3>(1, 1)], e = M[kst_pidx<3>(1, 2)], f = M[kst_pidx<3>(2, 2)];
-        m1 = a;
-        m2 = fma(a, d, -(b * b));
+    if (R == 4 && INV0) {
+        const double t1 = M[kst_pidx<R>(0, 1)] * inv0, t2 = M[kst_pidx<R>(0, 2)] * inv0, t3 = M[kst_pidx<R>(0, 3)] * inv0;
+        const double s00 = fma(-t1, M[kst_pidx<R>(0, 1)], M[kst_pidx<R>(1, 1)]);
+        const double s01 = fma(-t1, M[kst_pidx<R>(0, 2)], M[kst_pidx<R>(1, 2)]);
+        const double s02 = fma(-t1, M[kst_pidx<R>(0, 3)], M[kst_pidx<R>(1, 3)]);
+        const double s11 = fma(-t2, M[kst_pidx<R>(0, 2)], M[kst_pidx<R>(2, 2)]);
+        const double s12 = fma(-t2, M[kst_pidx<R>(0, 3)], M[kst_pidx<R>(2, 3)]);
+        const double s22 = fma(-t3, M[kst_pidx<R>(0, 3)], M[kst_pidx<R>(3, 3)]);
+        const double m2 = fma(s00, s11, -(s01 * s01));
+        const double c12 = fma(s00, s12, -(s01 * s02));
+        const double c02 = fma(s01, s12, -(s11 * s02));
+        const double m3 = fma(s22, m2, fma(s02, c02, -(s12 * c12)));
+        prod = M[kst_pidx<R>(0, 0)] * m3;
+        signs = __double2hiint(s00) | __double2hiint(m2) | __double2hiint(m3);
+    } else if (R == 3 && INV0) {
+        const double t1 = M[kst_pidx<R>(0, 1)] * inv0, t2 = M[kst_pidx<R>(0, 2)] * inv0;
+        const double s00 = fma(-t1, M[kst_pidx<R>(0, 1)], M[kst_pidx<R>(1, 1)]);
+        const double s01 = fma(-t1, M[kst_pidx<R>(0, 2)], M[kst_pidx<R>(1, 2)]);
+        const double s11 = fma(-t2, M[kst_pidx<R>(0, 2)], M[kst_pidx<R>(2, 2)]);
+        const double m2 = fma(s00, s11, -(s01 * s01));
+        prod = M[kst_pidx<R>(0, 0)] * m2;
+        signs = __double2hiint(s00) | __double2hiint(m2);
+    } else if (R == 3) {
+        const double a = M[kst_pidx<R>(0, 0)], b = M[kst_pidx<R>(0, 1)], c = M[kst_pidx<R>(0, 2)];
+        const double d = M[kst_pidx<R>(1, 1)], e = M[kst_pidx<R>(1, 2)], f = M[kst_pidx<R>(2, 2)];
+        const double m2 = fma(a, d, -(b * b));
         const double c12 = fma(a, e, -(b * c));
         const double c02 = fma(b, e, -(d * c));
-        m3 = fma(f, m2, fma(c, c02, -(e * c12)));
-        lead = 1.0;
+        prod = fma(f, m2, fma(c, c02, -(e * c12)));
+        signs = __double2hiint(a) | __double2hiint(m2) | __double2hiint(prod);
+    } else {
+        double L[R][R], dv[R], dinv[R];
+        kst_ldlt<R, INV0, false>(M, L, dv, dinv, false, inv0);
+        prod = dv[0];
+        signs = INV0 ? 0 : __double2hiint(dv[0]);
+#pragma unroll
+        for (int j = 1; j < R; j++) {
+            prod *= dv[j];
+            signs |= __double2hiint(dv[j]);
+        }
     }
-    const double prod = INV0 ? lead * m3 : m3;
-    const int signs = __double2hiint(m1) | __double2hiint(m2) | __double2hiint(m3);
+}
+
+// log det from (prod, signs) with one log call and NO floating-point compares: the sign bit of `signs` is
+// OR-ed into the high word of the product and a single unsigned test on the exponent field accepts
+// "positive definite and 2^-900 < det < 2^900".  Everything else takes the slow path: -Inf unless the
+// matrix is positive definite (log_det!, src/design-common.jl:213-220).
+__device__ __forceinline__ double kst_log_checked(double prod, int signs, KstTab tab)
+{
     const unsigned key = ((unsigned)signs & 0x80000000u) | (unsigned)__double2hiint(prod);
     if (((key >> 20) - 123u) < 1800u) return kst_log(prod, tab);
-    if (!(m1 > 0.0) || !(m2 > 0.0) || !(m3 > 0.0)) return -KST_INF;
-    return INV0 ? log(lead) + log(m3) : log(m3);
+    return (signs >= 0 && prod > 0.0) ? log(prod) : -KST_INF;
 }
 
 // Per-(particle, draw) criterion value from the accumulated Mt.
@@ -190,12 +166,10 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
     double L[R][R], dv[R], dinv[R];
     exc = false;
     if (CRIT == 0 && T == 0) {
-#if KST_DET_CLOSED
-        if (R == 4 && INV0) return kst_log_det4_inv0(M, inv0, tab);
-        if (R == 3) return kst_log_det3<INV0>(M, inv0, tab);
-#endif
-        kst_ldlt<R, INV0, false>(M, L, dv, dinv, false, inv0);
-        return kst_log_det<R, INV0>(dv, tab);
+        double prod;
+        int signs;
+        kst_det_signs<R, INV0>(M, inv0, prod, signs);
+        return kst_log_checked(prod, signs, tab);
     }
     const bool ok = kst_ldlt<R, INV0>(M, L, dv, dinv, true, inv0);
     if (!ok) {
@@ -253,7 +227,8 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
             for (int k = 0; k < R; k++) s = fma(Y[a][k] * dinv[k], Y[b][k], s);
             Mi[kst_pidx<TT>(a, b)] = s;
         }
-    double L2[TT][TT], dv2[TT], dinv2[TT];
-    kst_ldlt<TT, false, false>(Mi, L2, dv2, dinv2, false);
-    return -kst_log_det<TT, false>(dv2, tab);
+    double prod2;
+    int signs2;
+    kst_det_signs<TT, false>(Mi, 0.0, prod2, signs2);
+    return -kst_log_checked(prod2, signs2, tab);
 }

@@ -25,6 +25,7 @@ struct KstObjParams {
     int S, K;
     double *partials;       // [S][n_blk]
     KstModelParams mp;
+    double w_uniform;       // the common prior weight when all weights are equal (UNI kernels), else unused
 };
 
 // ------------------------------------------------------------------------------------------
@@ -196,7 +197,11 @@ __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na
 // ------------------------------------------------------------------------------------------
 // the hot kernel
 // ------------------------------------------------------------------------------------------
-template <class MF, int CRIT, int T>
+// UNI (D criterion, Identity, all prior weights equal): sum_j w log det_j = w log prod_j det_j, so the thread
+// multiplies determinants and takes one log per flush instead of one per draw.  The running product is kept
+// inside (2^-600, 2^600); a draw whose determinant would leave that range or is not positive definite flushes
+// the product and is evaluated on its own by the regular path.
+template <class MF, int CRIT, int T, bool UNI>
 __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjParams prm)
 {
     constexpr int R = MF::R;
@@ -236,6 +241,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
             // for log_det! (0 * -Inf = NaN, as there), unweighted where it throws.
             for (int j = j0; j < n; j += stride) acc += (CRIT == 0 && T == 0) ? pw[j] * -KST_INF : -KST_INF;
         } else {
+            double run = 1.0;  // UNI: running product of determinants
             // software prefetch: the next draw's constants are requested before this draw's rows are evaluated
             double dcn[MF::NDC], pwn = 0.0;
             if (j0 < n) {
@@ -256,10 +262,25 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
                 }
                 double M[KstPacked<R>::N];
                 kst_fisher<MF>(M, rows_addr, na, sw, dcv, tab);
-                bool exc;
-                const double val = kst_criterion<R, CRIT, T, INV0>(M, prm.aux + j, prm.ld, exc, inv0, tab);
-                acc += exc ? -KST_INF : pwj * val;
+                if (UNI) {
+                    double det;
+                    int signs;
+                    kst_det_signs<R, INV0>(M, inv0, det, signs);
+                    const double pn = run * det;
+                    const unsigned key = ((unsigned)signs & 0x80000000u) | (unsigned)__double2hiint(pn);
+                    if (((key >> 20) - 423u) < 1200u) {
+                        run = pn;
+                    } else {
+                        acc += kst_log(run, tab) + kst_log_checked(det, signs, tab);
+                        run = 1.0;
+                    }
+                } else {
+                    bool exc;
+                    const double val = kst_criterion<R, CRIT, T, INV0>(M, prm.aux + j, prm.ld, exc, inv0, tab);
+                    acc += exc ? -KST_INF : pwj * val;
+                }
             }
+            if (UNI) acc = prm.w_uniform * (acc + kst_log(run, tab));
         }
         // fixed-order reduction over the CTA's draws
 #pragma unroll
@@ -386,10 +407,14 @@ static int launch_obj_t(kst_problem *h, const KstObjParams &prm, dim3 grid, size
 #define KST_LAUNCH_T(TV)                                                                        \
     case TV:                                                                                    \
         if (TV <= MF::R) {                                                                      \
-            k_objective<MF, CRIT, (TV <= MF::R ? TV : 0)><<<grid, KST_NT, smem, h->stream>>>(prm); \
+            k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false><<<grid, KST_NT, smem, h->stream>>>(prm); \
             return KST_OK;                                                                      \
         }                                                                                       \
         break;
+    if (CRIT == 0 && T == 0 && h->uniform_w) {
+        k_objective<MF, 0, 0, true><<<grid, KST_NT, smem, h->stream>>>(prm);
+        return KST_OK;
+    }
     switch (T) {
         KST_LAUNCH_T(0)
         KST_LAUNCH_T(1)
@@ -419,7 +444,7 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
     if (rc) return rc;
     KstObjParams prm;
     prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.ld = h->ld; prm.N = h->N;
-    prm.pts = d_pts; prm.w = d_w; prm.S = S; prm.K = K; prm.partials = h->partials; prm.mp = h->mp;
+    prm.pts = d_pts; prm.w = d_w; prm.S = S; prm.K = K; prm.partials = h->partials; prm.mp = h->mp; prm.w_uniform = h->w_uniform;
     const dim3 grid(n_blk, tiles);
     if (h->prof_on) {
         cudaEvent_t e0, e1;
@@ -527,7 +552,7 @@ extern "C" int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const d
     if ((size_t)n_blk * S > KST_NOALLOC_MAX_PARTIALS) n_blk = KST_NOALLOC_MAX_PARTIALS / S;  // >= 64 by the swarm limit
     KstObjParams prm;
     prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.ld = h->ld; prm.N = h->N;
-    prm.pts = d_points; prm.w = d_weights; prm.S = S; prm.K = K; prm.partials = scratch; prm.mp = h->mp;
+    prm.pts = d_points; prm.w = d_weights; prm.S = S; prm.K = K; prm.partials = scratch; prm.mp = h->mp; prm.w_uniform = h->w_uniform;
     const dim3 grid(n_blk, tiles);
     KST_MODEL_SWITCH(h->model_id, {
         const size_t smem = KstTile<MF>::bytes(K * h->m);
