@@ -39,9 +39,10 @@ __constant__ double kst_exp2_tab_c[64] = {  // 2^(j/64), correctly rounded
 // 0: 64/ln2   1: 1.5*2^52   2: -ln2/64 (high 38 bits)   3: -ln2/64 (low)
 // 4..7: c5, c4, c3, c2 of exp(r) ~ 1 + r + r^2 (c2 + c3 r + c4 r^2 + c5 r^3) on |r| <= ln2/128
 // (interpolation at Chebyshev nodes; truncation error 4.4e-18 relative)
-__constant__ double kst_mc[8] = {0x1.71547652b82fep+6, 6755399441055744.0, -0x1.62e42fefa0000p-7,
+// 8: -ln2/64 rounded to double (one-step reduction)
+__constant__ double kst_mc[9] = {0x1.71547652b82fep+6, 6755399441055744.0, -0x1.62e42fefa0000p-7,
                                  -0x1.cf79abc9e3b3ap-46, 0x1.11111d8fbe766p-7, 0x1.55556b3304ec0p-5,
-                                 0x1.5555555555255p-3, 0x1.ffffffffff57fp-2};
+                                 0x1.5555555555255p-3, 0x1.ffffffffff57fp-2, -0x1.62e42fefa39efp-7};
 
 #define KST_EXP_TAB_N 64
 #define KST_EXP_TAB_SHIFT 6
@@ -118,13 +119,22 @@ __device__ __forceinline__ double kst_rcp(double x)
 // exp(x).  Exact contract: full accuracy for |x| <= 708; beyond that the result saturates near the
 // largest / smallest normal double instead of overflowing to Inf or flushing to 0 (integer clamp of the
 // binary exponent, no FP64 compare); |x| above ~4e7 and non-finite x give NaN.
+// RED = 2: two-step Cody-Waite reduction, result within 1 ulp of exp(x).  RED = 1: one step with ln2/64
+// rounded to double, which adds at most |x| 2^-53 relative error -- no more than the rounding an argument
+// that is itself a product (h log x, a t, ...) already carries; the model functors use this form.
+template <int RED = 2>
 __device__ __forceinline__ double kst_exp(double x, KstTab tab)
 {
     const double t = fma(x, kst_mc[0], kst_mc[1]);
     const int n = __double2loint(t);
     const double nd = t - kst_mc[1];
-    double r = fma(nd, kst_mc[2], x);
-    r = fma(nd, kst_mc[3], r);
+    double r;
+    if (RED == 2) {
+        r = fma(nd, kst_mc[2], x);
+        r = fma(nd, kst_mc[3], r);
+    } else {
+        r = fma(nd, kst_mc[8], x);
+    }
     double p = fma(kst_mc[4], r, kst_mc[5]);
     p = fma(p, r, kst_mc[6]);
     p = fma(p, r, kst_mc[7]);

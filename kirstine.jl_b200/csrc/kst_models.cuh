@@ -28,6 +28,9 @@
 #ifndef KST_SU_FMA
 #define KST_SU_FMA 1
 #endif
+#ifndef KST_EXP_RED
+#define KST_EXP_RED 1
+#endif
 
 #include "kst_math.cuh"
 #include "../../include/kirstine_b200.h"
@@ -99,7 +102,7 @@ struct KstSigEmax {
     __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
         const double q = fma(-dc[0], pc[0], dc[1]);
-        const double e = kst_exp(q, tab);
+        const double e = kst_exp<KST_EXP_RED>(q, tab);
         const double a = kst_rcp(1.0 + e);
         const double sa = sw * a;
 #if KST_SU_FMA
@@ -139,8 +142,8 @@ struct KstTpc {
     __device__ static void post_row(double *pc, double sw) { pc[1] = sw * pc[0]; }
     __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
-        const double A = kst_exp(dc[0] * pc[0], tab);
-        const double E = kst_exp(dc[1] * pc[0], tab);
+        const double A = kst_exp<KST_EXP_RED>(dc[0] * pc[0], tab);
+        const double E = kst_exp<KST_EXP_RED>(dc[1] * pc[0], tab);
         g[0] = pc[1] * A;  // sw t A
         g[1] = pc[1] * E;
         g[2] = sw * (E - A);
@@ -222,8 +225,8 @@ struct KstDtr {
     __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
         const double t = pc[0];
-        const double A = kst_exp(dc[0] * t, tab);
-        const double B = kst_exp(dc[1] * t, tab);
+        const double A = kst_exp<KST_EXP_RED>(dc[0] * t, tab);
+        const double B = kst_exp<KST_EXP_RED>(dc[1] * t, tab);
         const double C = B - A;
         const double w = kst_rcp(fma(pc[1] * C, dc[2], dc[6]));  // 1 / (dose C a - rd ec50)
         const double sdw = pc[2] * w;                             // sw dose w
