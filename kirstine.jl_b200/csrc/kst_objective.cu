@@ -14,6 +14,7 @@
 #include <mutex>
 
 
+
 #include "kst_common.cuh"
 #include "kst_linalg.cuh"
 
@@ -173,8 +174,9 @@ __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na
     constexpr int R = MF::R, RW = KstTile<MF>::RW;
 #pragma unroll
     for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
-    // odd row first, then pairs: two independent rows per iteration give the scheduler two exp / reciprocal
-    // chains to interleave, and there is no remainder code after the loop
+    // odd row first, then a pair, then groups of four (ROWS4 families) or pairs: the FP64 pipe only saturates
+    // with about four independent dependency chains per warp (tools/fp64_probe.cu), which the interleaved
+    // exp / reciprocal chains of independent rows provide; there is no remainder code after the loop
     int i = 0;
     if (na & 1) {
         double g[R];
@@ -182,6 +184,28 @@ __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na
         kst_accum<R, MF::CONST_COL>(M, g);
         i = 1;
     }
+    if (MF::ROWS4) {
+    if (na & 2) {
+        double g0[R], g1[R];
+        kst_row_at<MF>(rows_addr + (unsigned)(i * RW * 8), dcv, g0, tab);
+        kst_row_at<MF>(rows_addr + (unsigned)((i + 1) * RW * 8), dcv, g1, tab);
+        kst_accum<R, MF::CONST_COL>(M, g0);
+        kst_accum<R, MF::CONST_COL>(M, g1);
+        i += 2;
+    }
+#pragma unroll 1
+    for (; i < na; i += 4) {
+        double g0[R], g1[R], g2[R], g3[R];
+        kst_row_at<MF>(rows_addr + (unsigned)(i * RW * 8), dcv, g0, tab);
+        kst_row_at<MF>(rows_addr + (unsigned)((i + 1) * RW * 8), dcv, g1, tab);
+        kst_row_at<MF>(rows_addr + (unsigned)((i + 2) * RW * 8), dcv, g2, tab);
+        kst_row_at<MF>(rows_addr + (unsigned)((i + 3) * RW * 8), dcv, g3, tab);
+        kst_accum<R, MF::CONST_COL>(M, g0);
+        kst_accum<R, MF::CONST_COL>(M, g1);
+        kst_accum<R, MF::CONST_COL>(M, g2);
+        kst_accum<R, MF::CONST_COL>(M, g3);
+    }
+    } else {
 #pragma unroll 1
     for (; i < na; i += 2) {
         double g0[R], g1[R];
@@ -189,6 +213,7 @@ __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na
         kst_row_at<MF>(rows_addr + (unsigned)((i + 1) * RW * 8), dcv, g1, tab);
         kst_accum<R, MF::CONST_COL>(M, g0);
         kst_accum<R, MF::CONST_COL>(M, g1);
+    }
     }
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
     if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = sw;
