@@ -19,6 +19,16 @@
 #include "kst_common.cuh"
 #include "kst_linalg.cuh"
 
+#ifndef KST_GD_UNROLL
+#define KST_GD_UNROLL 4
+#endif
+// draws evaluated side by side per thread in k_gateaux_eval (independent FP64 chains for the scheduler)
+constexpr int kGdUnroll = KST_GD_UNROLL;
+
+#ifndef KST_GD_UNROLL
+#define KST_GD_UNROLL 4
+#endif
+
 // doubles per row in shared memory: sqrt(omega), pc...
 template <class MF>
 struct KstRowW {
@@ -303,6 +313,7 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
             s_draw[e] = v;
         }
         __syncthreads();
+#pragma unroll kGdUnroll
         for (int jj = 0; jj < nj; jj++) {
             double dcv[MF::NDC], Ap[NP];
 #pragma unroll
