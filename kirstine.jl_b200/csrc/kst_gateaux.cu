@@ -251,19 +251,23 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
 }
 
 // One thread per direction; draws staged in shared memory.
-template <class MF>
+// MR > 0: the unit has exactly MR rows and their constants stay in registers; MR = 0: any unit length, row
+// constants in shared memory.  A draw's constants (NDC hoisted constants + packed pw_j At_j) are stored
+// contiguously and read as 16-byte broadcasts.
+template <class MF, int MR>
 __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__restrict__ dc, const double *__restrict__ pw,
                                                             const double *__restrict__ gA, size_t ld, int64_t N,
                                                             const double *__restrict__ dirs, int64_t G,
                                                             KstModelParams mp, double *__restrict__ partials)
 {
-    constexpr int R = MF::R, RW = KstRowW<MF>::RW, NP = KstPacked<R>::N, NS = MF::NDC + NP;
+    constexpr int R = MF::R, RW = KstRowW<MF>::RW, NP = KstPacked<R>::N, NS = MF::NDC + NP, NSP = (NS + 1) / 2 * 2;
+    constexpr int MRR = MR > 0 ? MR : 1;
     extern __shared__ __align__(16) double smem[];
     __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
     const KstTab tab = kst_math_init(s_mathtab);  // visible after the first __syncthreads() of the chunk loop
-    double *s_draw = smem;                                  // [NS][KST_GD_CHUNK]
-    double *s_rows = smem + (size_t)NS * KST_GD_CHUNK;      // [m][RW][KST_GD_NT]
-    const int m = mp.m;
+    double *s_draw = smem;                                  // [KST_GD_CHUNK][NSP]
+    double *s_rows = smem + (size_t)NSP * KST_GD_CHUNK;     // [m][RW][KST_GD_NT]   (MR == 0 only)
+    const int m = MR > 0 ? MR : mp.m;
     const int64_t g = (int64_t)blockIdx.x * KST_GD_NT + threadIdx.x;
     const bool live = g < G;
 
@@ -272,6 +276,13 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
     // trivial for the whole CTA (time 0 of every vector unit) are skipped outright in the draw loop.
     double sw_triv = 0.0;
     unsigned live_mask = 0;
+    double rsq[MRR], rpc[MRR][MF::NPC];
+#pragma unroll
+    for (int i = 0; i < (MR > 0 ? MR : 1); i++) {
+        rsq[i] = 0.0;
+#pragma unroll
+        for (int c = 0; c < MF::NPC; c++) rpc[i][c] = 1.0;
+    }
     for (int i = 0; i < m; i++) {
         double pc[MF::NPC], varfac = 0.0;
         bool trivial = true;
@@ -283,8 +294,18 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
             for (int c = 0; c < MF::NPC; c++) pc[c] = 1.0;
         }
         MF::post_row(pc, sq);
-        s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x] = sq;
-        for (int c = 0; c < MF::NPC; c++) s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x] = pc[c];
+        if (MR > 0) {
+#pragma unroll
+            for (int ii = 0; ii < MRR; ii++)
+                if (ii == i) {
+                    rsq[ii] = sq;
+#pragma unroll
+                    for (int c = 0; c < MF::NPC; c++) rpc[ii][c] = pc[c];
+                }
+        } else {
+            s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x] = sq;
+            for (int c = 0; c < MF::NPC; c++) s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x] = pc[c];
+        }
         if (__syncthreads_or(sq != 0.0)) live_mask |= 1u << i;
     }
 
@@ -295,10 +316,10 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
     for (int64_t jb = j0; jb < j1; jb += KST_GD_CHUNK) {
         const int nj = (int)min((int64_t)KST_GD_CHUNK, j1 - jb);
         __syncthreads();
-        for (int e = threadIdx.x; e < NS * KST_GD_CHUNK; e += KST_GD_NT) {
-            const int c = e / KST_GD_CHUNK, jj = e % KST_GD_CHUNK;
+        for (int e = threadIdx.x; e < NSP * KST_GD_CHUNK; e += KST_GD_NT) {
+            const int c = e / KST_GD_CHUNK, jj = e % KST_GD_CHUNK;  // consecutive threads read consecutive draws
             double v = 0.0;
-            if (jj < nj) {
+            if (jj < nj && c < NS) {
                 const int64_t j = jb + jj;
                 if (c < MF::NDC) {
                     v = dc[(size_t)c * ld + j];
@@ -310,33 +331,58 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
                     v = pw[j] * gA[(size_t)(a * R + b) * ld + j] * (a == b ? 1.0 : 2.0);
                 }
             }
-            s_draw[e] = v;
+            s_draw[jj * NSP + c] = v;
         }
         __syncthreads();
 #pragma unroll kGdUnroll
         for (int jj = 0; jj < nj; jj++) {
-            double dcv[MF::NDC], Ap[NP];
+            double dv[NSP];
 #pragma unroll
-            for (int c = 0; c < MF::NDC; c++) dcv[c] = s_draw[c * KST_GD_CHUNK + jj];
+            for (int c = 0; c < NSP; c += 2) {
+                const double2 v = *reinterpret_cast<const double2 *>(s_draw + jj * NSP + c);
+                dv[c] = v.x;
+                dv[c + 1] = v.y;
+            }
+            const double *dcv = dv, *Ap = dv + MF::NDC;
+            double qsum = 0.0;
 #pragma unroll
-            for (int c = 0; c < NP; c++) Ap[c] = s_draw[(MF::NDC + c) * KST_GD_CHUNK + jj];
-            for (int i = 0; i < m; i++) {
+            for (int i = 0; i < (MR > 0 ? MR : 1); i++) {
+                if (MR == 0) break;
                 if (!((live_mask >> i) & 1u)) continue;  // uniform over the CTA
-                double pc[MF::NPC], gv[R];
-                const double sq = s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x];
-#pragma unroll
-                for (int c = 0; c < MF::NPC; c++) pc[c] = s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x];
-                MF::row(pc, dcv, sq, gv, tab);  // weighted row: gv' A gv = omega * gt' A gt
+                double gv[R];
+                MF::row(rpc[i], dcv, rsq[i], gv, tab);  // weighted row: gv' A gv = omega * gt' A gt
+                double q = 0.0;
 #pragma unroll
                 for (int a = 0; a < R; a++) {
                     double s = 0.0;
 #pragma unroll
                     for (int b = a; b < R; b++) s = fma(Ap[kst_pidx<R>(a, b)], gv[b], s);
-                    acc = fma(s, gv[a], acc);
+                    q = fma(s, gv[a], q);
+                }
+                qsum += q;
+            }
+            if (MR == 0) {
+                for (int i = 0; i < m; i++) {
+                    if (!((live_mask >> i) & 1u)) continue;  // uniform over the CTA
+                    double pc[MF::NPC], gv[R];
+                    const double sq = s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x];
+#pragma unroll
+                    for (int c = 0; c < MF::NPC; c++) pc[c] = s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x];
+                    MF::row(pc, dcv, sq, gv, tab);
+                    double q = 0.0;
+#pragma unroll
+                    for (int a = 0; a < R; a++) {
+                        double s = 0.0;
+#pragma unroll
+                        for (int b = a; b < R; b++) s = fma(Ap[kst_pidx<R>(a, b)], gv[b], s);
+                        q = fma(s, gv[a], q);
+                    }
+                    qsum += q;
                 }
             }
             constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
-            if (MF::CONST_COL >= 0) acc = fma(sw_triv, Ap[kst_pidx<R>(cc, cc)], acc);
+            if (MF::CONST_COL >= 0) qsum = fma(sw_triv, Ap[kst_pidx<R>(cc, cc)], qsum);
+            acc += qsum;
         }
     }
     if (live) partials[g * gridDim.y + blockIdx.y] = acc;
@@ -389,6 +435,32 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
     return KST_OK;
 }
 
+template <class MF, int MR>
+static int launch_gd(kst_problem *h, dim3 grid, int64_t G, const double *d_dirs, size_t smem)
+{
+    if (smem > 48 * 1024)  // vector units with many rows: opt in to a large dynamic shared-memory window
+        KST_CUDA(cudaFuncSetAttribute(k_gateaux_eval<MF, MR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_gateaux_eval<MF, MR><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->pw, h->gA, h->ld, h->N, d_dirs, G, h->mp,
+                                                                 h->gd_partials);
+    return KST_OK;
+}
+
+template <class MF>
+static int launch_gd_model(kst_problem *h, dim3 grid, int64_t G, const double *d_dirs)
+{
+    constexpr int NSP = (MF::NDC + KstPacked<MF::R>::N + 1) / 2 * 2;
+    const bool in_regs = h->m <= 4;
+    const size_t smem =
+        sizeof(double) * ((size_t)NSP * KST_GD_CHUNK + (in_regs ? 0 : (size_t)h->m * KstRowW<MF>::RW * KST_GD_NT));
+    switch (in_regs ? h->m : 0) {
+    case 1: return launch_gd<MF, 1>(h, grid, G, d_dirs, smem);
+    case 2: return launch_gd<MF, 2>(h, grid, G, d_dirs, smem);
+    case 3: return launch_gd<MF, 3>(h, grid, G, d_dirs, smem);
+    case 4: return launch_gd<MF, 4>(h, grid, G, d_dirs, smem);
+    default: return launch_gd<MF, 0>(h, grid, G, d_dirs, smem);
+    }
+}
+
 int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, double *d_out)
 {
     if (!h->g_ready) {
@@ -414,14 +486,9 @@ int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, dou
     }
     const dim3 grid((unsigned)gblocks, (unsigned)n_split);
     if (!h->g_singular) {
-        KST_MODEL_SWITCH(h->model_id, {
-            constexpr int NS = MF::NDC + KstPacked<MF::R>::N;
-            const size_t smem = sizeof(double) * ((size_t)NS * KST_GD_CHUNK + (size_t)h->m * KstRowW<MF>::RW * KST_GD_NT);
-            if (smem > 48 * 1024)  // vector units with many rows: opt in to a large dynamic shared-memory window
-                KST_CUDA(cudaFuncSetAttribute(k_gateaux_eval<MF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            k_gateaux_eval<MF><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->pw, h->gA, h->ld, h->N, d_dirs, G, h->mp,
-                                                                     h->gd_partials);
-        });
+        int rc = KST_OK;
+        KST_MODEL_SWITCH(h->model_id, rc = launch_gd_model<MF>(h, grid, G, d_dirs));
+        if (rc) return rc;
         KST_CUDA(cudaGetLastError());
     }
     k_gd_finish<<<(unsigned)((G + 127) / 128), 128, 0, h->stream>>>(h->gd_partials, (int)n_split, h->g_offset,
