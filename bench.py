@@ -195,6 +195,7 @@ def main():
     assert st == 0
     for _ in range(args.warmup):
         h.pso_run(1)
+    fg_before = h.pso_state()["fg"]
     clock_lines, stop = [], threading.Event()
     sampler = threading.Thread(target=clock_sampler, args=(stop, clock_lines, local), daemon=True)
     if rank == 0:
@@ -202,10 +203,12 @@ def main():
         time.sleep(0.3)
     h.profile_enable(True)
     barrier()
-    ms = timed_steps(lambda: h.pso_run(1), args.steps)
+    ms = timed_steps(lambda: h.pso_run_async(1), args.steps)
     barrier()
     kern_ms, kern_launches = h.profile_read()
     h.profile_enable(False)
+    st_after = h.pso_state()  # device -> host read of the step's result (best objective so far)
+    assert st_after["fg"] >= fg_before and st_after["n_eval"] == S * (1 + args.warmup + args.steps)
     ms = max_over_ranks(ms)
     units_per_step = float(S) * float(n_total)
     value = units_per_step * args.steps / (ms * 1e-3)

@@ -198,7 +198,8 @@ KST_API int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, con
 /*
  * n_iters times tick! (src/pso.jl:127-141).  trace_fx[n_iters], trace_points[n_iters*K*d],
  * trace_weights[n_iters*K] receive maximum/maximizer after each tick (optimize's trace_fx /
- * trace_x, src/optimize.jl:54-57); any of them may be NULL.
+ * trace_x, src/optimize.jl:54-57); any of them may be NULL.  With all three NULL the call only enqueues the
+ * iterations on the handle's stream and returns (kst_stream_synchronize / kst_pso_get_state wait for them).
  */
 KST_API int kst_pso_run(kst_problem *h, int n_iters, double *trace_fx, double *trace_points,
                 double *trace_weights);

@@ -224,6 +224,10 @@ class ProblemHandle:
         self._pso_dims = (S, K)
         return st.value
 
+    def pso_run_async(self, n_iters):
+        """Enqueue n_iters swarm iterations without copying traces back (no host synchronisation)."""
+        check(lib().kst_pso_run(self._h, n_iters, None, None, None))
+
     def pso_run(self, n_iters):
         S, K = self._pso_dims
         tfx = np.empty(n_iters)

@@ -536,7 +536,8 @@ extern "C" int kst_pso_run(kst_problem *h, int n_iters, double *trace_fx, double
         KST_CUDA(cudaMemcpyAsync(trace_points, p.tr_pts, sizeof(double) * n_iters * p.K * h->d, cudaMemcpyDeviceToHost, h->stream));
     if (trace_weights)
         KST_CUDA(cudaMemcpyAsync(trace_weights, p.tr_w, sizeof(double) * n_iters * p.K, cudaMemcpyDeviceToHost, h->stream));
-    KST_CUDA(cudaStreamSynchronize(h->stream));
+    // without trace buffers nothing has to reach the host: the iterations stay queued on the handle's stream
+    if (trace_fx || trace_points || trace_weights) KST_CUDA(cudaStreamSynchronize(h->stream));
     return KST_OK;
 }
 
