@@ -249,9 +249,15 @@ def main():
     kern_avg_ms = kern_ms / max(1, kern_launches)
     achieved_tf = FLOPS_PER_UNIT * units_per_launch / (kern_avg_ms * 1e-3) / 1e12
     alg_bytes = BYTES_PER_DRAW * float(j1 - j0) * (S / 8.0)  # each 8-particle tile streams the shard once
+    traffic = None  # DRAM bytes per launch from the committed ncu capture of this kernel (cannot be measured live)
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get("k_objective_cfg5_dram_bytes_per_launch")
+    except OSError:
+        pass
     roofline = {
         "bound": "fp64", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-        "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": None,
+        "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic,
         "kernel": "k_objective<KstSigEmax,D,Identity>", "kernel_ms": kern_avg_ms, "launches_timed": kern_launches,
         "flops_per_unit": FLOPS_PER_UNIT,
         "peak_source": "DFMA micro-kernel measured in this run (MEASURED_PEAKS.json has no FP64 figure; "

@@ -47,7 +47,7 @@ struct KstModelParams {
 // Emax: test/example-emax.jl:41-47.  row = [1, x/(x+ec50), -emax x/(x+ec50)^2]
 struct KstEmax {
     static constexpr int R = 3, NDC = 1, NPC = 2, CONST_COL = 0;
-    static constexpr bool ROWS4 = true;  // interleave four rows per loop iteration in the objective kernel
+    static constexpr int ROWS = 4;  // rows interleaved per loop iteration in the objective kernel
     __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
     {
         const double isig = 1.0 / sqrt(mp.v[0]);  // v[0] = sigma_squared
@@ -83,7 +83,7 @@ struct KstEmax {
 // a NaN parameter still reaches the row through q and makes the draw singular like in the reference.
 struct KstSigEmax {
     static constexpr int R = 4, NDC = 2, NPC = 1, CONST_COL = 0;
-    static constexpr bool ROWS4 = true;
+    static constexpr int ROWS = 4;
     __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
     {
         const double isig = 1.0 / fabs(mp.v[0]);  // v[0] = sigma
@@ -125,7 +125,7 @@ struct KstSigEmax {
 // diag(sigma_squared (1 + t_i)).
 struct KstTpc {
     static constexpr int R = 3, NDC = 2, NPC = 2, CONST_COL = -1;
-    static constexpr bool ROWS4 = false;  // two exponentials per row: pairs already give four chains
+    static constexpr int ROWS = 2;  // two exponentials per row: pairs already give four chains
     __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
     {
         const double isig = 1.0 / fabs(mp.v[0]);  // v[0] = sigma
@@ -182,7 +182,7 @@ struct KstVu : KstTpc {
 // EquidistantTimes :484-495, LogEquidistantTimes :663-681.
 struct KstDtr {
     static constexpr int R = 5, NDC = 7, NPC = 3, CONST_COL = 2;
-    static constexpr bool ROWS4 = false;
+    static constexpr int ROWS = 2;
     __device__ static void prep_draw(const double *th, const KstModelParams &mp, double *dc, double *cs)
     {
         const double isig = 1.0 / fabs(mp.v[0]);  // v[0] = sigma

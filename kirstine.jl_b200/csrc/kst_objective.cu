@@ -13,6 +13,10 @@
 // fixed order by k_obj_finish, so results are bit-reproducible run to run.
 #include <mutex>
 
+#ifndef KST_ROWS_OVERRIDE
+#define KST_ROWS_OVERRIDE 0  // tuning: force the row interleave factor (1, 2, 4, 8) for every family
+#endif
+
 
 
 #include "kst_common.cuh"
@@ -166,55 +170,37 @@ __device__ __forceinline__ void kst_row_at(unsigned addr, const double *dcv, dou
     MF::row(rw + 1, dcv, rw[0], g, tab);
 }
 
-// Mt = sum over the particle's live rows (at least one) of g g'; rows_addr is a shared-space address
+// NR consecutive rows: all reduced rows first, then all rank-one updates, so that the NR exp / reciprocal
+// chains are independent instruction streams the scheduler can interleave
+template <class MF, int NR>
+__device__ __forceinline__ void kst_rows(double *M, unsigned addr, const double *dcv, KstTab tab)
+{
+    constexpr int R = MF::R, RW = KstTile<MF>::RW;
+    double g[NR][R];
+#pragma unroll
+    for (int k = 0; k < NR; k++) kst_row_at<MF>(addr + (unsigned)(k * RW * 8), dcv, g[k], tab);
+#pragma unroll
+    for (int k = 0; k < NR; k++) kst_accum<R, MF::CONST_COL>(M, g[k]);
+}
+
+// Mt = sum over the particle's live rows (at least one) of g g'; rows_addr is a shared-space address.
+// Remainders first (1, 2, 4 rows by the bits of na), then groups of MF::ROWS rows: the FP64 pipe only
+// saturates with about four independent dependency chains per warp (tools/fp64_probe.cu), which the
+// interleaved rows provide; there is no remainder code after the loop.
 template <class MF>
 __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na, double sw, const double *dcv,
                                            KstTab tab)
 {
-    constexpr int R = MF::R, RW = KstTile<MF>::RW;
+    constexpr int R = MF::R, RW = KstTile<MF>::RW, UN = KST_ROWS_OVERRIDE > 0 ? KST_ROWS_OVERRIDE : MF::ROWS;
 #pragma unroll
     for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
-    // odd row first, then a pair, then groups of four (ROWS4 families) or pairs: the FP64 pipe only saturates
-    // with about four independent dependency chains per warp (tools/fp64_probe.cu), which the interleaved
-    // exp / reciprocal chains of independent rows provide; there is no remainder code after the loop
-    int i = 0;
-    if (na & 1) {
-        double g[R];
-        kst_row_at<MF>(rows_addr, dcv, g, tab);
-        kst_accum<R, MF::CONST_COL>(M, g);
-        i = 1;
-    }
-    if (MF::ROWS4) {
-    if (na & 2) {
-        double g0[R], g1[R];
-        kst_row_at<MF>(rows_addr + (unsigned)(i * RW * 8), dcv, g0, tab);
-        kst_row_at<MF>(rows_addr + (unsigned)((i + 1) * RW * 8), dcv, g1, tab);
-        kst_accum<R, MF::CONST_COL>(M, g0);
-        kst_accum<R, MF::CONST_COL>(M, g1);
-        i += 2;
-    }
+    unsigned addr = rows_addr;
+    int left = na;
+    if (UN > 1 && (left & 1)) { kst_rows<MF, 1>(M, addr, dcv, tab); addr += RW * 8; left -= 1; }
+    if (UN > 2 && (left & 2)) { kst_rows<MF, 2>(M, addr, dcv, tab); addr += 2 * RW * 8; left -= 2; }
+    if (UN > 4 && (left & 4)) { kst_rows<MF, 4>(M, addr, dcv, tab); addr += 4 * RW * 8; left -= 4; }
 #pragma unroll 1
-    for (; i < na; i += 4) {
-        double g0[R], g1[R], g2[R], g3[R];
-        kst_row_at<MF>(rows_addr + (unsigned)(i * RW * 8), dcv, g0, tab);
-        kst_row_at<MF>(rows_addr + (unsigned)((i + 1) * RW * 8), dcv, g1, tab);
-        kst_row_at<MF>(rows_addr + (unsigned)((i + 2) * RW * 8), dcv, g2, tab);
-        kst_row_at<MF>(rows_addr + (unsigned)((i + 3) * RW * 8), dcv, g3, tab);
-        kst_accum<R, MF::CONST_COL>(M, g0);
-        kst_accum<R, MF::CONST_COL>(M, g1);
-        kst_accum<R, MF::CONST_COL>(M, g2);
-        kst_accum<R, MF::CONST_COL>(M, g3);
-    }
-    } else {
-#pragma unroll 1
-    for (; i < na; i += 2) {
-        double g0[R], g1[R];
-        kst_row_at<MF>(rows_addr + (unsigned)(i * RW * 8), dcv, g0, tab);
-        kst_row_at<MF>(rows_addr + (unsigned)((i + 1) * RW * 8), dcv, g1, tab);
-        kst_accum<R, MF::CONST_COL>(M, g0);
-        kst_accum<R, MF::CONST_COL>(M, g1);
-    }
-    }
+    for (; left > 0; left -= UN, addr += UN * RW * 8) kst_rows<MF, UN>(M, addr, dcv, tab);
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
     if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = sw;
 }
