@@ -156,10 +156,19 @@ def main():
     pts, w = wl.random_swarm(S, K, 0.0, 1.0, seed=5)
     h = kb.ProblemHandle(kb._ffi.MODEL_SIGEMAX, [1.0], theta[j0:j1], np.full(j1 - j0, 1.0 / n_total), kb._ffi.CRIT_D,
                          None, [0.0], [1.0], device=local)
+    collective = "none"
     if world > 1:
-        uid = [kb.ProblemHandle.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        h.comm_init(world, rank, uid[0])
+        # the S partial objectives are summed over NVLink peer memory by one fused kernel per evaluation
+        # (kst_comm_peer_*); KST_BENCH_COLLECTIVE=nccl selects the library all-reduce instead
+        collective = os.environ.get("KST_BENCH_COLLECTIVE", "peer")
+        if collective == "peer":
+            handles = [None] * world
+            dist.all_gather_object(handles, h.comm_peer_handle(world, rank))
+            h.comm_peer_open(handles)
+        else:
+            uid = [kb.ProblemHandle.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            h.comm_init(world, rank, uid[0])
     stream = torch.cuda.ExternalStream(h.stream(), device=local)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
@@ -233,6 +242,8 @@ def main():
     if rank == 0:
         stop.set()
         sampler.join(timeout=3)
+    if collective == "peer":
+        assert h.comm_peer_error() == 0, "peer exchange timed out"
     fx_check = pin_fx.numpy().copy()
     assert np.all(np.isfinite(fx_check[:1])), "prototype particle must have a finite objective"
 
@@ -290,9 +301,11 @@ def main():
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "draws_total": n_total, "draws_per_gpu": j1 - j0, "swarm": S, "points": K,
-                   "step": "one PSO iteration: k_pso_move + k_objective + k_obj_finish (+ allreduce) + k_pso_best",
+                   "step": "one PSO iteration: k_pso_move + k_objective + k_obj_finish (+ all-reduce) + k_pso_best",
                    "l2": "flushed between steps (256 MiB write on the same stream, outside the events)",
-                   "parallelism": "prior draws sharded over %d GPU(s), swarm replicated" % world},
+                   "parallelism": "prior draws sharded over %d GPU(s), swarm replicated" % world,
+                   "collective": {"peer": "fused NVLink peer-memory all-reduce kernel (S doubles per step)",
+                                  "nccl": "ncclAllReduce (S doubles per step)", "none": "none"}[collective]},
         "clocks": summarize_clocks(clock_lines),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(pin_pts.numel() * 8 + pin_w.numel() * 8),
                 "d2h_bytes_per_step": int(S * 8), "ms_per_step": e2e_ms / args.steps,

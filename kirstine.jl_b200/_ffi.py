@@ -33,6 +33,9 @@ SIGNATURES = {
     "kst_problem_destroy": (C.c_int, [_vp]),
     "kst_comm_unique_id": (C.c_int, [_vp]),
     "kst_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "kst_comm_peer_handle": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "kst_comm_peer_open": (C.c_int, [_vp, _vp]),
+    "kst_comm_peer_error": (C.c_int, [_vp, _ip]),
     "kst_objective_batch": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
     "kst_objective_batch_device": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
     "kst_objective_batch_noalloc": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
@@ -154,6 +157,22 @@ class ProblemHandle:
     def comm_init(self, nranks, rank, unique_id):
         buf = C.create_string_buffer(unique_id, 128)
         check(lib().kst_comm_init(self._h, nranks, rank, C.cast(buf, _vp)))
+
+    def comm_peer_handle(self, nranks, rank):
+        buf = (C.c_char * 64)()
+        check(lib().kst_comm_peer_handle(self._h, nranks, rank, C.cast(buf, _vp)))
+        return bytes(buf)
+
+    def comm_peer_open(self, handles):
+        """handles: list of the nranks 64-byte IPC handles in rank order."""
+        blob = b"".join(handles)
+        buf = C.create_string_buffer(blob, len(blob))
+        check(lib().kst_comm_peer_open(self._h, C.cast(buf, _vp)))
+
+    def comm_peer_error(self):
+        e = C.c_int(0)
+        check(lib().kst_comm_peer_error(self._h, C.byref(e)))
+        return e.value
 
     # -- objective --------------------------------------------------------------------------
     def objective_batch(self, points, weights):

@@ -21,6 +21,8 @@
 #endif
 #define KST_GD_NT 128       // threads (= directions) per CTA of the Gateaux kernel
 #define KST_GD_CHUNK 64     // draws staged per shared-memory chunk in the Gateaux kernel
+#define KST_PEER_CAP 16384  // doubles per peer-exchange buffer (larger all-reduces go through NCCL)
+#define KST_PEER_MAX 16     // ranks in one peer-exchange group
 
 void kst_set_error(const char *fmt, ...);
 
@@ -101,6 +103,12 @@ struct kst_problem {
     // communicator (optional)
     void *comm = nullptr;
     int nranks = 1, rank = 0;
+    // peer-memory exchange over NVLink (optional, kst_comm_peer_*): each rank owns one exchange block
+    // {double data[2][KST_PEER_CAP]; unsigned long long flag[2]; int error;} that every peer maps through CUDA IPC
+    void *peer_local = nullptr;          // this rank's block (cudaMalloc)
+    void *peer_map[KST_PEER_MAX] = {};   // all ranks' blocks as seen from this GPU (own entry = peer_local)
+    int peer_ready = 0;
+    unsigned long long peer_seq = 0;     // collectives issued so far (identical on every rank)
 
     // profiling of the evaluation kernel
     int prof_on = 0;

@@ -20,7 +20,7 @@ def _free_port():
     return port
 
 
-def _worker(rank, world, port, out_dir):
+def _worker(rank, world, port, out_dir, peer=False):
     sys.path.insert(0, ROOT)
     import torch
     import torch.distributed as dist
@@ -35,9 +35,14 @@ def _worker(rank, world, port, out_dir):
     theta = wl.sigemax_prior(n, seed=5)
     j0, j1 = kb.shard_range(n, rank, world)
     h = kb.ProblemHandle(2, [1.0], theta[j0:j1], np.full(j1 - j0, 1.0 / n), 0, None, [0.0], [1.0], device=rank)
-    uid = [kb.ProblemHandle.comm_unique_id() if rank == 0 else None]
-    dist.broadcast_object_list(uid, src=0)
-    h.comm_init(world, rank, uid[0])
+    if peer:   # NVLink peer-memory exchange instead of NCCL
+        handles = [None] * world
+        dist.all_gather_object(handles, h.comm_peer_handle(world, rank))
+        h.comm_peer_open(handles)
+    else:
+        uid = [kb.ProblemHandle.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        h.comm_init(world, rank, uid[0])
     pts, w = wl.jittered_swarm(40, 8, 0.0, 1.0, seed=5)
     fx = h.objective_batch(pts, w)
     assert h.pso_init(40, 8, pts[0], w[0], seed=11) == 0
@@ -45,11 +50,14 @@ def _worker(rank, world, port, out_dir):
     st = h.pso_state()
     h.gateaux_prepare(pts[0], w[0])
     gd = h.gateaux_eval(np.linspace(0, 1, 33))
+    if peer:
+        assert h.comm_peer_error() == 0
     np.savez(os.path.join(out_dir, "r%d.npz" % rank), fx=fx, tfx=tfx, tp=tp, tw=tw, x=st["x_pts"], xw=st["x_w"], gd=gd)
     dist.destroy_process_group()
 
 
-def test_two_gpu_sharded_run_matches_single_gpu(tmp_path):
+@pytest.mark.parametrize("peer", [False, True], ids=["nccl", "nvlink-peer"])
+def test_two_gpu_sharded_run_matches_single_gpu(tmp_path, peer):
     import torch
     import torch.multiprocessing as mp
 
@@ -57,7 +65,7 @@ def test_two_gpu_sharded_run_matches_single_gpu(tmp_path):
     from tests import workloads as wl
     if kb.device_count() < 2:
         pytest.skip("needs two GPUs")
-    mp.spawn(_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), str(tmp_path), peer), nprocs=2, join=True)
     a, b = np.load(tmp_path / "r0.npz"), np.load(tmp_path / "r1.npz")
     for key in a.files:
         assert np.array_equal(a[key], b[key]), key                       # replicas bit-identical
