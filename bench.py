@@ -162,10 +162,19 @@ def main():
         # (kst_comm_peer_*); KST_BENCH_COLLECTIVE=nccl selects the library all-reduce instead
         collective = os.environ.get("KST_BENCH_COLLECTIVE", "peer")
         if collective == "peer":
-            handles = [None] * world
-            dist.all_gather_object(handles, h.comm_peer_handle(world, rank))
-            h.comm_peer_open(handles)
-        else:
+            ok = 1
+            try:
+                handles = [None] * world
+                dist.all_gather_object(handles, h.comm_peer_handle(world, rank))
+                h.comm_peer_open(handles)
+            except kb.EngineError as exc:  # no peer access between these GPUs: every rank falls back together
+                print("rank %d: peer exchange unavailable (%s), using NCCL" % (rank, exc), file=sys.stderr)
+                ok = 0
+            flag = torch.tensor([ok], device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 0:
+                collective = "nccl"
+        if collective == "nccl":
             uid = [kb.ProblemHandle.comm_unique_id() if rank == 0 else None]
             dist.broadcast_object_list(uid, src=0)
             h.comm_init(world, rank, uid[0])
