@@ -173,6 +173,7 @@ def main():
             flag = torch.tensor([ok], device="cuda")
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
             if int(flag.item()) == 0:
+                h.comm_peer_close()
                 collective = "nccl"
         if collective == "nccl":
             uid = [kb.ProblemHandle.comm_unique_id() if rank == 0 else None]

@@ -148,6 +148,8 @@ KST_API int kst_comm_init(kst_problem *h, int nranks, int rank, const void *id12
 KST_API int kst_comm_peer_handle(kst_problem *h, int nranks, int rank, void *handle64);
 KST_API int kst_comm_peer_open(kst_problem *h, const void *handles);
 KST_API int kst_comm_peer_error(kst_problem *h, int *error);
+/* Unmap the peers' blocks and go back to NCCL (or to single-GPU operation); all ranks must do this together. */
+KST_API int kst_comm_peer_close(kst_problem *h);
 
 /*
  * pso_evaluate_objective! (src/pso.jl:173-179) calling objective! (src/designproblem.jl:192-224)

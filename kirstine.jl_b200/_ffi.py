@@ -36,6 +36,7 @@ SIGNATURES = {
     "kst_comm_peer_handle": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
     "kst_comm_peer_open": (C.c_int, [_vp, _vp]),
     "kst_comm_peer_error": (C.c_int, [_vp, _ip]),
+    "kst_comm_peer_close": (C.c_int, [_vp]),
     "kst_objective_batch": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
     "kst_objective_batch_device": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
     "kst_objective_batch_noalloc": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
@@ -168,6 +169,9 @@ class ProblemHandle:
         blob = b"".join(handles)
         buf = C.create_string_buffer(blob, len(blob))
         check(lib().kst_comm_peer_open(self._h, C.cast(buf, _vp)))
+
+    def comm_peer_close(self):
+        check(lib().kst_comm_peer_close(self._h))
 
     def comm_peer_error(self):
         e = C.c_int(0)

@@ -250,6 +250,19 @@ extern "C" int kst_comm_peer_open(kst_problem *h, const void *handles)
     return KST_OK;
 }
 
+extern "C" int kst_comm_peer_close(kst_problem *h)
+{
+    if (!h) { kst_set_error("NULL problem handle"); return KST_EINVAL; }
+    KST_CUDA(cudaSetDevice(h->device));
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < KST_PEER_MAX; r++) {
+        if (r != h->rank && h->peer_map[r]) cudaIpcCloseMemHandle(h->peer_map[r]);
+        h->peer_map[r] = nullptr;
+    }
+    h->peer_ready = 0;
+    return KST_OK;
+}
+
 extern "C" int kst_comm_peer_error(kst_problem *h, int *error)
 {
     if (!h || !error) { kst_set_error("comm_peer_error: bad arguments"); return KST_EINVAL; }
@@ -282,7 +295,7 @@ extern "C" int kst_problem_destroy(kst_problem *h)
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->comm && g_nccl.comm_destroy) g_nccl.comm_destroy(h->comm);
-    for (int r = 0; r < h->nranks && h->peer_ready; r++)
+    for (int r = 0; r < KST_PEER_MAX; r++)
         if (r != h->rank && h->peer_map[r]) cudaIpcCloseMemHandle(h->peer_map[r]);
     if (h->peer_local) cudaFree(h->peer_local);
     kst_pso_free(h);
