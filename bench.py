@@ -321,7 +321,9 @@ def main():
                 "d2h_bytes_per_step": int(S * 8), "ms_per_step": e2e_ms / args.steps,
                 "wall_ms_per_step": e2e_wall_ms / args.steps,
                 "call": "kst_objective_batch (host buffers, pinned) = one swarm evaluation"},
-        "gpu_launches": int(4 * args.steps),
+        # own kernels per timed step on each rank: move, objective, finish, best (+ the peer all-reduce kernel when
+        # the NVLink path is used; ncclAllReduce is a library kernel and not counted)
+        "gpu_launches": int((4 + (1 if collective == "peer" else 0)) * args.steps),
         "roofline": roofline,
         "cpu_baseline": cpu,
     }
