@@ -58,6 +58,14 @@ extern "C" {
 #define KST_MODEL_TPC 3
 #define KST_MODEL_VU 4
 #define KST_MODEL_DTR 5
+/* Logistic regression, the user-defined Model supertype of docs/src/extend-model.md:59-106 (its own
+ * average_fishermatrix!: M = sum_k w_k p_k (1 - p_k) J_k' J_k with p = expit(predictor), J = predictor Jacobian;
+ * no unit covariance: model_params is ignored, pass one dummy value):
+ *   KST_MODEL_LINLOGREG  docs/src/extend-model.md:123-179  linear predictor on a d-dimensional covariate copied
+ *                        from the design point (CopyVector = KST_CP_COPY), d = 1..3, theta = (beta_0, ..., beta_d)
+ *   KST_MODEL_SINLOGREG  docs/src/extend-model.md:330-355  predictor a sin(2 pi b (t - c)), theta = (a, b, c) */
+#define KST_MODEL_LINLOGREG 6
+#define KST_MODEL_SINLOGREG 7
 
 /* covariate parameterizations = map_to_covariate! (src/user.jl:68):
  *   KST_CP_COPY      CopyDose / CopyTime / JustCopy: covariate = design point (src/user.jl:185-216)
@@ -78,6 +86,7 @@ extern "C" {
 
 #define KST_CRIT_D 0 /* DCriterion, src/criterion-d.jl:29 */
 #define KST_CRIT_A 1 /* ACriterion, src/criterion-a.jl:29 */
+#define KST_CRIT_DEXP 2 /* det^(1/t), the user-extension DexpCriterion of docs/src/extend-criterion.md:100-183 */
 
 #define KST_TRAFO_IDENTITY 0 /* Identity,    src/transformation.jl:11 */
 #define KST_TRAFO_DELTA 1    /* DeltaMethod, src/transformation.jl:59-61 */

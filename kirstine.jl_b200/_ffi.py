@@ -12,10 +12,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # KST_LIB_PATH selects an alternative build of the same library (kernel tuning experiments)
 LIB_PATH = os.environ.get("KST_LIB_PATH") or os.path.join(_HERE, "libkirstine_b200.so")
 
-MODEL_EMAX, MODEL_SIGEMAX, MODEL_TPC, MODEL_VU, MODEL_DTR = 1, 2, 3, 4, 5
+MODEL_EMAX, MODEL_SIGEMAX, MODEL_TPC, MODEL_VU, MODEL_DTR, MODEL_LINLOGREG, MODEL_SINLOGREG = 1, 2, 3, 4, 5, 6, 7
 CP_COPY, CP_EQUITIME = 0, 1
 CP_DTR_COPYBOTH, CP_DTR_FIXEDDOSE, CP_DTR_FIXEDTIMES, CP_DTR_EQUIDISTANT, CP_DTR_LOGEQUIDISTANT = 2, 3, 4, 5, 6
-CRIT_D, CRIT_A = 0, 1
+CRIT_D, CRIT_A, CRIT_DEXP = 0, 1, 2
 TRAFO_IDENTITY, TRAFO_DELTA = 0, 1
 PSO_MODE_OBJECTIVE, PSO_MODE_GATEAUX = 0, 1
 

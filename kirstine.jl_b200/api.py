@@ -28,6 +28,28 @@ SigEmaxParameter = namedtuple("SigEmaxParameter", "e0 emax ed50 h")  # docs/src/
 TPCParameter = namedtuple("TPCParameter", "a e s")                  # test/example-compartment.jl:12
 VUParameter = namedtuple("VUParameter", "a e s")                    # test/example-vector.jl:30
 DTRParameter = namedtuple("DTRParameter", "a e e0 emax ec50")       # test/example-dtr.jl:22
+SLRParameter = namedtuple("SLRParameter", "a b c")                  # docs/src/extend-model.md:342
+
+
+class LLRParameter:
+    """docs/src/extend-model.md:137-142: beta_0 plus a vector beta_rest; dimension = length(beta_rest) + 1."""
+
+    def __init__(self, beta_0, beta_rest):
+        self.beta_0 = float(beta_0)
+        self.beta_rest = np.asarray(beta_rest, dtype=np.float64).ravel()
+
+    def _flat(self):
+        return np.concatenate([[self.beta_0], self.beta_rest])
+
+    @classmethod
+    def _from_flat(cls, row):
+        return cls(row[0], row[1:])
+
+    def __len__(self):
+        return 1 + len(self.beta_rest)
+
+    def __repr__(self):
+        return "LLRParameter(%r, %r)" % (self.beta_0, list(self.beta_rest))
 
 
 def dimension(p):
@@ -98,6 +120,27 @@ class DTRMod(Model):
         return [self.sigma]
 
 
+class LogisticRegression(Model):
+    """The user-defined Model supertype of docs/src/extend-model.md:59-106: unit length 1, no unit covariance,
+    M = sum_k w_k p_k (1 - p_k) J_k' J_k with p = expit(nonlinear predictor), J = predictor Jacobian."""
+
+    def _params(self):
+        return [0.0]   # the C ABI wants at least one model parameter; logistic models ignore it
+
+
+class LinLogReg(LogisticRegression):
+    """docs/src/extend-model.md:123-179: linear predictor on a dim_covariate-dimensional covariate (1..3)."""
+    model_id, parameter_type = _ffi.MODEL_LINLOGREG, LLRParameter
+
+    def __init__(self, dim_covariate):
+        self.dim_covariate = int(dim_covariate)
+
+
+class SinLogReg(LogisticRegression):
+    """docs/src/extend-model.md:330-355: predictor a sin(2 pi b (t - c))."""
+    model_id, parameter_type = _ffi.MODEL_SINLOGREG, SLRParameter
+
+
 def unit_length(m):
     return m.m
 
@@ -121,6 +164,10 @@ class JustCopy(CovariateParameterization):
 
 
 class CopyDose(CovariateParameterization):  # test/example-emax.jl:18
+    pass
+
+
+class CopyVector(CovariateParameterization):  # docs/src/extend-model.md:145-155: covariate x .= design point
     pass
 
 
@@ -200,6 +247,12 @@ class ACriterion:
     crit_id = _ffi.CRIT_A
 
 
+class DexpCriterion:
+    """det(M_T)^(1/t): the alternative D-criterion the reference's docs build as a user extension
+    (docs/src/extend-criterion.md:100-183).  Not linear in log det, so Bayesian optima differ from DCriterion."""
+    crit_id = _ffi.CRIT_DEXP
+
+
 class Identity:
     pass
 
@@ -224,7 +277,10 @@ class PriorSample:
         types = {type(p) for p in parameters} if not isinstance(parameters, np.ndarray) else {np.ndarray}
         if len(types) > 1:
             raise ValueError("parameters must all have the same concrete type")
-        self.ptype = type(parameters[0]) if hasattr(parameters[0], "_fields") else None
+        p0 = parameters[0]
+        self.ptype = type(p0) if hasattr(p0, "_fields") or hasattr(p0, "_flat") else None
+        if hasattr(p0, "_flat"):
+            parameters = [p._flat() for p in parameters]
         self.theta = np.ascontiguousarray(np.asarray(parameters, dtype=np.float64).reshape(len(parameters), -1))
         n = len(self.theta)
         w = np.full(n, 1.0 / n) if weights is None else np.asarray(weights, dtype=np.float64).ravel()
@@ -236,6 +292,8 @@ class PriorSample:
 
     def parameter(self, i):
         row = self.theta[i]
+        if self.ptype is not None and hasattr(self.ptype, "_from_flat"):
+            return self.ptype._from_flat(row)
         return self.ptype(*row) if self.ptype else row
 
 

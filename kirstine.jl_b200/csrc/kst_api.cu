@@ -277,9 +277,13 @@ extern "C" int kst_comm_peer_error(kst_problem *h, int *error)
 // ---------------------------------------------------------------------------------------
 // problem handle
 // ---------------------------------------------------------------------------------------
-static int model_dims(int model_id, int *r, int *ndc)
+static int model_dims(int model_id, int d, int *r, int *ndc)
 {
     switch (model_id) {
+    case KST_MODEL_LINLOGREG:
+        if (d < 1 || d > 3) return -1;
+        *r = d + 1; *ndc = d + 1; return 0;
+    case KST_MODEL_SINLOGREG: *r = KstSinLogReg::R; *ndc = KstSinLogReg::NDC; return 0;
     case KST_MODEL_EMAX: *r = KstEmax::R; *ndc = KstEmax::NDC; return 0;
     case KST_MODEL_SIGEMAX: *r = KstSigEmax::R; *ndc = KstSigEmax::NDC; return 0;
     case KST_MODEL_TPC: *r = KstTpc::R; *ndc = KstTpc::NDC; return 0;
@@ -317,9 +321,13 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
     if (!out) { kst_set_error("problem_create: out is NULL"); return KST_EINVAL; }
     *out = nullptr;
     int mr = 0, ndc = 0;
-    if (model_dims(model_id, &mr, &ndc)) { kst_set_error("unregistered model id %d", model_id); return KST_EINVAL; }
+    if (model_dims(model_id, d, &mr, &ndc)) {
+        if (model_id == KST_MODEL_LINLOGREG) kst_set_error("KST_MODEL_LINLOGREG is registered for covariate dimension 1..3, got d = %d", d);
+        else kst_set_error("unregistered model id %d", model_id);
+        return KST_EINVAL;
+    }
     if (r != mr) { kst_set_error("model %d has parameter dimension %d, got r = %d", model_id, mr, r); return KST_EINVAL; }
-    if (criterion_id != KST_CRIT_D && criterion_id != KST_CRIT_A) { kst_set_error("unknown criterion %d", criterion_id); return KST_EINVAL; }
+    if (criterion_id != KST_CRIT_D && criterion_id != KST_CRIT_A && criterion_id != KST_CRIT_DEXP) { kst_set_error("unknown criterion %d", criterion_id); return KST_EINVAL; }
     if (trafo_id == KST_TRAFO_IDENTITY) {
         if (t != r) { kst_set_error("identity transformation needs t == r"); return KST_EINVAL; }
     } else if (trafo_id == KST_TRAFO_DELTA) {
@@ -330,6 +338,7 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
     // which (model, covariate parameterization, unit length, region dimension) combinations are registered
     int want_d = 1, want_ncp = 0;
     bool ok_m = m == 1, ok_cp = cp_id == KST_CP_COPY;
+    if (model_id == KST_MODEL_LINLOGREG) want_d = d;  // range checked by model_dims
     if (model_id == KST_MODEL_VU) {
         ok_m = m >= 1 && m <= KST_MAX_UNIT;
         ok_cp = cp_id == KST_CP_EQUITIME;
@@ -368,14 +377,15 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
     kst_problem *h = new (std::nothrow) kst_problem();
     if (!h) { kst_set_error("out of host memory"); return KST_ENOMEM; }
     h->device = device_id;
-    h->model_id = model_id; h->crit = criterion_id; h->trafo = trafo_id;
+    h->model_id = model_id == KST_MODEL_LINLOGREG ? KST_FID_LINLOGREG + d : model_id;
+    h->crit = criterion_id; h->trafo = trafo_id;
     h->r = r; h->t = t; h->m = m; h->d = d; h->N = N;
     h->ld = ((size_t)N + 31) / 32 * 32;
     for (int i = 0; i < 4; i++) h->mp.v[i] = i < n_model_params ? model_params[i] : 0.0;
     for (int i = 0; i < 16; i++) h->mp.cpv[i] = (cp_params && i < n_cp_params) ? cp_params[i] : 0.0;
     h->mp.m = m; h->mp.cp = cp_id; h->mp.d = d;
     for (int j = 0; j < d; j++) { h->lb[j] = lb[j]; h->ub[j] = ub[j]; }
-    h->n_aux = trafo_id == KST_TRAFO_DELTA ? t * r : (criterion_id == KST_CRIT_A ? r : 0);
+    h->n_aux = trafo_id == KST_TRAFO_DELTA ? t * r : (criterion_id == KST_CRIT_A ? r : (criterion_id == KST_CRIT_DEXP ? 1 : 0));
     h->uniform_w = prior_w[0] > 0.0 && prior_w[0] < 1e300;
     for (int64_t j = 1; j < N && h->uniform_w; j++) h->uniform_w = prior_w[j] == prior_w[0];
     h->w_uniform = prior_w[0];

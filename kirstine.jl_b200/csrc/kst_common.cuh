@@ -35,6 +35,10 @@ void kst_set_error(const char *fmt, ...);
         }                                                                                   \
     } while (0)
 
+// kst_problem::model_id holds the public model id, except for KST_MODEL_LINLOGREG whose functor depends on the
+// covariate dimension: there it is KST_FID_LINLOGREG + d
+#define KST_FID_LINLOGREG 60
+
 // dispatch on the registered model family; the body sees the functor type as MF
 #define KST_MODEL_SWITCH(id, ...)                                        \
     switch (id) {                                                        \
@@ -43,6 +47,10 @@ void kst_set_error(const char *fmt, ...);
     case KST_MODEL_TPC: { using MF = KstTpc; __VA_ARGS__; } break;       \
     case KST_MODEL_VU: { using MF = KstVu; __VA_ARGS__; } break;         \
     case KST_MODEL_DTR: { using MF = KstDtr; __VA_ARGS__; } break;       \
+    case KST_FID_LINLOGREG + 1: { using MF = KstLinLogReg<1>; __VA_ARGS__; } break; \
+    case KST_FID_LINLOGREG + 2: { using MF = KstLinLogReg<2>; __VA_ARGS__; } break; \
+    case KST_FID_LINLOGREG + 3: { using MF = KstLinLogReg<3>; __VA_ARGS__; } break; \
+    case KST_MODEL_SINLOGREG: { using MF = KstSinLogReg; __VA_ARGS__; } break; \
     default: kst_set_error("unregistered model id %d", id); return KST_EINVAL; \
     }
 

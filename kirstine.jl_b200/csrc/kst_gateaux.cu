@@ -151,12 +151,20 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
     }
     double At[R][R];
     double trB;
-    if (crit == KST_CRIT_D && trafo == KST_TRAFO_IDENTITY) {
+    // Dexp shares the D constants up to a per-draw factor: psi_j / t with psi_j = det(M_T)^(1/t) the draw's
+    // criterion value, and trB = psi_j (docs/src/extend-criterion.md:40-67)
+    double logdet_mt = 0.0;  // log det M_T
+    if (crit != KST_CRIT_A && trafo == KST_TRAFO_IDENTITY) {
 #pragma unroll
         for (int a = 0; a < R; a++)
 #pragma unroll
             for (int b = 0; b < R; b++) At[a][b] = Mi[a][b];
         trB = (double)R;
+#pragma unroll
+        for (int k = 0; k < R; k++) {
+            const double c = cs[(size_t)k * ld + j];
+            logdet_mt += log(dv[k]) + log(c * c);
+        }
     } else {
         // P = DTt Mt^-1 (tt x R), C = P DTt' (tt x tt)
         double P[R][R], C[R][R], W[R][R];
@@ -198,6 +206,7 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
                 if (c < tt) {
                     const double piv = C[c][c];
                     ok = ok && (piv > 0.0);
+                    logdet_mt -= log(piv);  // C = M_T^-1
                     const double ip = 1.0 / piv;
 #pragma unroll
                     for (int b = 0; b < R; b++) { C[c][b] *= ip; W[c][b] *= ip; }
@@ -240,6 +249,15 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
                 for (int a = 0; a < R; a++) s = fma(P[a][i], WP[a][k], s);
                 At[i][k] = s;
             }
+    }
+    if (crit == KST_CRIT_DEXP) {
+        const double psi = exp(logdet_mt / tt);
+        const double f = psi / tt;
+#pragma unroll
+        for (int a = 0; a < R; a++)
+#pragma unroll
+            for (int b = 0; b < R; b++) At[a][b] *= f;
+        trB = psi;
     }
     if (!ok) atomicExch(flag, 1);
 #pragma unroll

@@ -151,9 +151,11 @@ __device__ __forceinline__ double kst_log_checked(double prod, int signs, KstTab
 
 // Per-(particle, draw) criterion value from the accumulated Mt.
 //
-// CRIT 0 = D, 1 = A.  T = 0: Identity; T >= 1: DeltaMethod with codomain dimension T.
+// CRIT 0 = D, 1 = A, 2 = Dexp (det^(1/t), docs/src/extend-criterion.md:114-127).  T = 0: Identity;
+// T >= 1: DeltaMethod with codomain dimension T.
 // aux points at this draw's auxiliary constants with stride `ld` between entries:
 //   A / Identity : R doubles  s_i = 1/cs_i^2                       (tr M^-1 = sum s_i (Mt^-1)_ii)
+//   Dexp / Identity : 1 double  prod_i cs_i^(2/R)                   (det M^(1/R) = det Mt^(1/R) * that)
 //   DeltaMethod  : T*R doubles DTt[a][i] = DT[a][i]/cs_i, a-major   (DT M^-1 DT' = DTt Mt^-1 DTt')
 // exc is set where the reference throws (PosDefException from posv!, src/design-common.jl:197;
 // SingularException from potri!, src/criterion-a.jl:39): objective! then returns -Inf no matter
@@ -165,11 +167,14 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
 {
     double L[R][R], dv[R], dinv[R];
     exc = false;
-    if (CRIT == 0 && T == 0) {
+    if (CRIT != 1 && T == 0) {
         double prod;
         int signs;
         kst_det_signs<R, INV0>(M, inv0, prod, signs);
-        return kst_log_checked(prod, signs, tab);
+        const double ld = kst_log_checked(prod, signs, tab);
+        if (CRIT == 0) return ld;
+        // a draw that is not positive definite contributes exp(-Inf) = 0
+        return ld == -KST_INF ? 0.0 : kst_exp(ld * (1.0 / R), tab) * aux[0];
     }
     const bool ok = kst_ldlt<R, INV0>(M, L, dv, dinv, true, inv0);
     if (!ok) {
@@ -230,5 +235,8 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
     double prod2;
     int signs2;
     kst_det_signs<TT, false>(Mi, 0.0, prod2, signs2);
-    return -kst_log_checked(prod2, signs2, tab);
+    // log det of the *inverse*: the sign flips unless it is -Inf (src/criterion-d.jl:35-37)
+    const double ldi = kst_log_checked(prod2, signs2, tab);
+    if (CRIT == 2) return ldi == -KST_INF ? 0.0 : kst_exp(-ldi * (1.0 / TT), tab);
+    return ldi == -KST_INF ? ldi : -ldi;
 }

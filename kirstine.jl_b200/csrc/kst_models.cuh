@@ -242,3 +242,84 @@ struct KstDtr {
         g[4] = sdw2 * C;
     }
 };
+
+// ------------------------------------------------------------------------------------------
+// logistic regression: the user-defined Model supertype of docs/src/extend-model.md:59-106.
+//   M(zeta, theta) = sum_k w_k p_k (1 - p_k) J_k' J_k,   p_k = expit(eta(c_k, theta)),   J_k = d eta / d theta  (1 x r)
+// As a weighted reduced row: g = sqrt(w_k) sqrt(p (1 - p)) J,  and with h = exp(-eta / 2)
+//   sqrt(p (1 - p)) = h / (1 + h^2)
+// (no square root, no cancellation in 1 - p).  |eta| beyond 1416 saturates inside kst_exp: h stays finite, h^2
+// overflows to Inf, its reciprocal is 0 and the row vanishes, as p (1 - p) does in the reference.
+// There is no unit covariance and no trivial row.
+// ------------------------------------------------------------------------------------------
+
+// linear predictor eta = beta_0 + sum_j beta_j x_j on a C-dimensional covariate copied from the design point
+// (LinLogReg + CopyVector, docs/src/extend-model.md:123-179).  theta = (beta_0, ..., beta_C), J = [1, x_1, ..., x_C].
+template <int C>
+struct KstLinLogReg {
+    static constexpr int R = C + 1, NDC = C + 1, NPC = C, CONST_COL = -1;
+    static constexpr int ROWS = 4;
+    __device__ static void prep_draw(const double *th, const KstModelParams &, double *dc, double *cs)
+    {
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            dc[i] = -0.5 * th[i];
+            cs[i] = 1.0;
+        }
+    }
+    __device__ static bool prep_row(const double *z, int, const KstModelParams &, double *pc, double &varfac)
+    {
+#pragma unroll
+        for (int i = 0; i < C; i++) pc[i] = z[i];
+        varfac = 1.0;
+        return false;
+    }
+    __device__ static void post_row(double *, double) {}
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
+    {
+        double q = dc[0];  // -eta / 2
+#pragma unroll
+        for (int i = 0; i < C; i++) q = fma(dc[1 + i], pc[i], q);
+        const double h = kst_exp<2>(q, tab);
+        const double s = sw * h * kst_rcp(fma(h, h, 1.0));
+        g[0] = s;
+#pragma unroll
+        for (int i = 0; i < C; i++) g[1 + i] = s * pc[i];
+    }
+};
+
+// eta = a sin(2 pi b (t - c)), theta = (a, b, c)  (SinLogReg, docs/src/extend-model.md:330-355)
+//   J = [sin phi, a cos phi 2 pi (t - c), -a cos phi 2 pi b] = diag(1, 2 pi a, -2 pi a b) [sin phi, cos phi (t - c), cos phi]
+struct KstSinLogReg {
+    static constexpr int R = 3, NDC = 3, NPC = 1, CONST_COL = -1;
+    static constexpr int ROWS = 2;
+    __device__ static void prep_draw(const double *th, const KstModelParams &, double *dc, double *cs)
+    {
+        const double twopi = 2 * 3.14159265358979323846;
+        dc[0] = twopi * th[1];
+        dc[1] = th[2];
+        dc[2] = -0.5 * th[0];
+        cs[0] = 1.0;
+        cs[1] = twopi * th[0];
+        cs[2] = -twopi * th[0] * th[1];
+    }
+    __device__ static bool prep_row(const double *z, int, const KstModelParams &, double *pc, double &varfac)
+    {
+        pc[0] = z[0];
+        varfac = 1.0;
+        return false;
+    }
+    __device__ static void post_row(double *, double) {}
+    __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
+    {
+        const double u = pc[0] - dc[1];
+        double sn, cn;
+        sincos(dc[0] * u, &sn, &cn);
+        const double h = kst_exp<2>(dc[2] * sn, tab);
+        const double s = sw * h * kst_rcp(fma(h, h, 1.0));
+        const double sc = s * cn;
+        g[0] = s * sn;
+        g[1] = sc * u;
+        g[2] = sc;
+    }
+};

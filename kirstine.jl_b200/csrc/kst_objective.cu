@@ -62,6 +62,11 @@ __global__ void k_prep_draws(const double *__restrict__ theta_aos, const double 
 #pragma unroll
             for (int i = 0; i < R; i++) off += log(csv[i] * csv[i]);
             off *= pw[j];
+        } else if (crit == KST_CRIT_DEXP) {
+            double lg = 0.0;
+#pragma unroll
+            for (int i = 0; i < R; i++) lg += log(csv[i] * csv[i]);
+            aux[j] = exp(lg / R);
         } else {
 #pragma unroll
             for (int i = 0; i < R; i++) aux[(size_t)i * ld + j] = 1.0 / (csv[i] * csv[i]);
@@ -250,7 +255,9 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
             // fewer live rows than parameters: singular by construction (one-point designs etc.).  The
             // reference reaches the same -Inf through an exactly zero pivot: weighted by the prior weight
             // for log_det! (0 * -Inf = NaN, as there), unweighted where it throws.
-            for (int j = j0; j < n; j += stride) acc += (CRIT == 0 && T == 0) ? pw[j] * -KST_INF : -KST_INF;
+            // (Dexp: exp(-Inf / t) = 0 for such a draw.)
+            for (int j = j0; j < n; j += stride)
+                acc += T != 0 ? -KST_INF : (CRIT == 0 ? pw[j] * -KST_INF : (CRIT == 2 ? pw[j] * 0.0 : -KST_INF));
         } else {
             double run = 1.0;  // UNI: running product of determinants
             // software prefetch: the next draw's constants are requested before this draw's rows are evaluated
@@ -467,7 +474,9 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
     }
     KST_MODEL_SWITCH(h->model_id, {
         const size_t smem = KstTile<MF>::bytes(K * h->m);
-        rc = h->crit == KST_CRIT_D ? launch_obj_t<MF, 0>(h, prm, grid, smem) : launch_obj_t<MF, 1>(h, prm, grid, smem);
+        rc = h->crit == KST_CRIT_D   ? launch_obj_t<MF, 0>(h, prm, grid, smem)
+             : h->crit == KST_CRIT_A ? launch_obj_t<MF, 1>(h, prm, grid, smem)
+                                     : launch_obj_t<MF, 2>(h, prm, grid, smem);
     });
     if (rc) return rc;
     KST_CUDA(cudaGetLastError());
@@ -567,7 +576,9 @@ extern "C" int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const d
     const dim3 grid(n_blk, tiles);
     KST_MODEL_SWITCH(h->model_id, {
         const size_t smem = KstTile<MF>::bytes(K * h->m);
-        rc = h->crit == KST_CRIT_D ? launch_obj_t<MF, 0>(h, prm, grid, smem) : launch_obj_t<MF, 1>(h, prm, grid, smem);
+        rc = h->crit == KST_CRIT_D   ? launch_obj_t<MF, 0>(h, prm, grid, smem)
+             : h->crit == KST_CRIT_A ? launch_obj_t<MF, 1>(h, prm, grid, smem)
+                                     : launch_obj_t<MF, 2>(h, prm, grid, smem);
     });
     if (rc) return rc;
     KST_CUDA(cudaGetLastError());

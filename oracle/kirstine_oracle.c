@@ -34,10 +34,10 @@
 #define KO_MAXC (KO_MAXM + 2)
 #define KO_MAXD 4
 
-enum { KO_EMAX = 1, KO_SIGEMAX = 2, KO_TPC = 3, KO_VU = 4, KO_DTR = 5 };
+enum { KO_EMAX = 1, KO_SIGEMAX = 2, KO_TPC = 3, KO_VU = 4, KO_DTR = 5, KO_LINLOGREG = 6, KO_SINLOGREG = 7 };
 enum { KO_CP_COPY = 0, KO_CP_EQUITIME = 1, KO_CP_DTR_COPYBOTH = 2, KO_CP_DTR_FIXEDDOSE = 3,
        KO_CP_DTR_FIXEDTIMES = 4, KO_CP_DTR_EQUIDISTANT = 5, KO_CP_DTR_LOGEQUIDISTANT = 6 };
-enum { KO_CRIT_D = 0, KO_CRIT_A = 1 };
+enum { KO_CRIT_D = 0, KO_CRIT_A = 1, KO_CRIT_DEXP = 2 };
 enum { KO_TRAFO_IDENTITY = 0, KO_TRAFO_DELTA = 1 };
 
 typedef struct {
@@ -96,6 +96,9 @@ static void ko_covariate(const ko_problem *p, const double *z, double *c)
             c[1] = z[1];
         }
         break;
+    case KO_LINLOGREG: /* CopyVector, docs/src/extend-model.md:147-155 */
+        for (int j = 0; j < p->d; j++) c[j] = z[j];
+        break;
     default:
         c[0] = z[0];
     }
@@ -118,8 +121,43 @@ static void ko_vcov(const ko_problem *p, const double *c, double *S)
     case KO_DTR:
         for (int j = 0; j < m; j++) S[IDX(j, j, m)] = p->mp[0] * p->mp[0];
         break;
+    default: S[0] = 1.0; /* logistic regression has no unit covariance */
     }
 }
+
+/* ---- logistic regression, the user-defined Model supertype of docs/src/extend-model.md:59-106 ---- */
+static int ko_is_logistic(const ko_problem *p)
+{
+    return p->model_id == KO_LINLOGREG || p->model_id == KO_SINLOGREG;
+}
+
+/* nonlinear_predictor: LinLogReg docs/src/extend-model.md:157-167, SinLogReg :344-346 */
+static double ko_predictor(const ko_problem *p, const double *c, const double *th)
+{
+    if (p->model_id == KO_LINLOGREG) {
+        double np = th[0];
+        for (int j = 0; j < p->d; j++) np += th[1 + j] * c[j];
+        return np;
+    }
+    return th[0] * sin(2 * M_PI * th[1] * (c[0] - th[2]));
+}
+
+/* predictor_jacobianmatrix!: LinLogReg docs/src/extend-model.md:169-179, SinLogReg :348-355 */
+static void ko_predictor_jacobian(const ko_problem *p, const double *c, const double *th, double *jm)
+{
+    if (p->model_id == KO_LINLOGREG) {
+        jm[0] = 1;
+        for (int j = 0; j < p->d; j++) jm[1 + j] = c[j];
+        return;
+    }
+    double sin_term = sin(2 * M_PI * th[1] * (c[0] - th[2]));
+    double cos_term = cos(2 * M_PI * th[1] * (c[0] - th[2]));
+    jm[0] = sin_term;
+    jm[1] = th[0] * cos_term * 2 * M_PI * (c[0] - th[2]);
+    jm[2] = -th[0] * cos_term * 2 * M_PI * th[1];
+}
+
+static double ko_expit(double x) { return 1 / (1 + exp(-x)); } /* docs/src/extend-model.md:86 */
 
 /* jacobianmatrix!: Emax test/example-emax.jl:41-47; sigmoid Emax
  * docs/src/tutorial.md:127-142; TPC test/example-compartment.jl:14-21;
@@ -334,10 +372,12 @@ double ko_tr_prod_upper(int k, const double *A, const double *B)
 double ko_criterion_functional(int n, double *tnim, int is_inv, int crit, int *exc)
 {
     *exc = 0;
-    if (crit == KO_CRIT_D) {
+    if (crit == KO_CRIT_D || crit == KO_CRIT_DEXP) {
         double sgn = is_inv ? -1 : 1;
         double ld = ko_log_det(n, tnim);
-        return ld != -INFINITY ? sgn * ld : ld;
+        double cv = ld != -INFINITY ? sgn * ld : ld;
+        /* DexpCriterion, det^(1/t): docs/src/extend-criterion.md:114-127 (a singular draw contributes 0) */
+        return crit == KO_CRIT_D ? cv : exp(cv / n);
     }
     if (!is_inv) {
         if (ko_potrf_upper(n, tnim)) { *exc = 1; return -INFINITY; }
@@ -427,6 +467,15 @@ static void ko_average_fishermatrix(const ko_problem *p, int K, const double *wt
 {
     int r = p->r, m = p->m;
     for (int i = 0; i < r * r; i++) w->rxr[i] = 0.0;
+    if (ko_is_logistic(p)) { /* average_fishermatrix! of docs/src/extend-model.md:88-105 */
+        for (int k = 0; k < K; k++) {
+            ko_predictor_jacobian(p, w->c + k * KO_MAXC, th, w->mxr);
+            double prob = ko_expit(ko_predictor(p, w->c + k * KO_MAXC, th));
+            double p1mp = prob * (1 - prob);
+            ko_syrk_ut(r, 1, p1mp * wts[k], w->mxr, w->rxr);
+        }
+        return;
+    }
     for (int k = 0; k < K; k++) {
         ko_jacobian(p, w->c + k * KO_MAXC, th, w->mxr);
         ko_trsm_lutn(m, r, w->chol + k * KO_MAXM * KO_MAXM, w->mxr);
@@ -520,7 +569,13 @@ int ko_gateaux_constants(const ko_problem *p, int K, const double *pts, const do
         if (ko_inv_sym(r, w.rxr, iM)) return 1;
         double *Aj = A + (size_t)j * r * r;
         const double *DT = p->dt ? p->dt + (size_t)j * t * r : NULL;
-        if (p->trafo == KO_TRAFO_IDENTITY && p->crit == KO_CRIT_D) {
+        if (p->trafo == KO_TRAFO_IDENTITY && p->crit == KO_CRIT_DEXP) {
+            /* docs/src/extend-criterion.md:129-150: trB = exp(-log(det(iM))/r), A = iM trB / r */
+            double tmp[KO_MAXR * KO_MAXR];
+            memcpy(tmp, iM, sizeof(double) * r * r);
+            trB[j] = exp(-ko_log_det(r, tmp) / r);
+            for (int i = 0; i < r * r; i++) Aj[i] = iM[i] * trB[j] / r;
+        } else if (p->trafo == KO_TRAFO_IDENTITY && p->crit == KO_CRIT_D) {
             memcpy(Aj, iM, sizeof(double) * r * r);
             trB[j] = r;
         } else if (p->trafo == KO_TRAFO_IDENTITY && p->crit == KO_CRIT_A) {
@@ -533,8 +588,12 @@ int ko_gateaux_constants(const ko_problem *p, int K, const double *pts, const do
                     for (int k = 0; k < r; k++) s += iM[IDX(i, k, r)] * iM[IDX(k, c, r)];
                     Aj[IDX(i, c, r)] = s;
                 }
-        } else if (p->crit == KO_CRIT_D) {
-            /* A = iM * DT' * inv(DT iM DT') * DT * iM ; trB = t */
+        } else if (p->crit == KO_CRIT_D || p->crit == KO_CRIT_DEXP) {
+            /* A = iM * DT' * inv(DT iM DT') * DT * iM ; trB = t.
+             * DexpCriterion (docs/src/extend-criterion.md:40-52,152-182): the same A times trB/t with
+             * trB = det(M_T)^(1/t).  The listing there takes the determinant of the r x r inverse instead of
+             * the t x t one, against its own formula; we follow the formula (the finite-difference test in
+             * tests/test_oracle_golden.py shows it is the derivative of the objective). */
             double MTinv[KO_MAXR * KO_MAXR], tmp[KO_MAXR * KO_MAXR];
             int flag;
             memcpy(tmp, iM, sizeof(double) * r * r);
@@ -568,6 +627,12 @@ int ko_gateaux_constants(const ko_problem *p, int K, const double *pts, const do
                     Aj[IDX(i, c, r)] = s;
                 }
             trB[j] = t;
+            if (p->crit == KO_CRIT_DEXP) {
+                double tmp[KO_MAXR * KO_MAXR];
+                memcpy(tmp, MTinv, sizeof(double) * t * t);
+                trB[j] = exp(-ko_log_det(t, tmp) / t);
+                for (int i = 0; i < r * r; i++) Aj[i] *= trB[j] / t;
+            }
         } else {
             /* A criterion, DeltaMethod: JpJ = DT'DT; trB = tr(JpJ iM); A = iM JpJ iM */
             double JpJ[KO_MAXR * KO_MAXR], T1[KO_MAXR * KO_MAXR];
