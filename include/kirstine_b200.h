@@ -191,6 +191,17 @@ KST_API int kst_stream_synchronize(kst_problem *h);
 /* The handle's cudaStream_t, for callers that enqueue their own work or copies in order. */
 KST_API void *kst_stream(kst_problem *h);
 
+/*
+ * normal_approximation (src/designproblem.jl:31,55; src/design-common.jl:74-76).  A new handle uses FisherMatrix
+ * (the only NormalApproximation the reference ships).  This call switches it to the RegularizedFisherMatrix(R) of
+ * docs/src/extend-approximation.md:69-79, whose informationmatrix! adds the constant matrix R to every average
+ * Fisher matrix -- in objective!, in the Gateaux constants and in the direction's matrix
+ * (src/designproblem.jl:207,254; src/design-common.jl:110).  R is r x r column-major; like every normalized
+ * information matrix of the reference only its upper triangle is read.  R = NULL switches back to FisherMatrix.
+ * A prepared Gateaux state is invalidated.
+ */
+KST_API int kst_problem_set_regularization(kst_problem *h, const double *R);
+
 /* informationmatrix (src/design-common.jl:96-112) for draw `draw_index` (0-based) of the prior
  * sample: full symmetric r x r matrix. */
 KST_API int kst_informationmatrix(kst_problem *h, int K, const double *points, const double *weights,

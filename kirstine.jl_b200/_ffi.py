@@ -42,6 +42,7 @@ SIGNATURES = {
     "kst_objective_batch_noalloc": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, _vp]),
     "kst_stream_synchronize": (C.c_int, [_vp]),
     "kst_stream": (_vp, [_vp]),
+    "kst_problem_set_regularization": (C.c_int, [_vp, _dp]),
     "kst_informationmatrix": (C.c_int, [_vp, C.c_int, _dp, _dp, C.c_int64, _dp]),
     "kst_gateaux_prepare": (C.c_int, [_vp, C.c_int, _dp, _dp, _ip]),
     "kst_gateaux_constants": (C.c_int, [_vp, _dp, _dp]),
@@ -205,6 +206,18 @@ class ProblemHandle:
 
     def stream(self):
         return lib().kst_stream(self._h)
+
+    def set_regularization(self, R):
+        """RegularizedFisherMatrix(R) of docs/src/extend-approximation.md:69-79; None switches back to FisherMatrix."""
+        if R is None:
+            check(lib().kst_problem_set_regularization(self._h, None))
+            return self
+        R = f64(R)
+        if R.shape != (self.r, self.r):
+            raise ValueError("R must be (%d, %d)" % (self.r, self.r))
+        Rc = np.ascontiguousarray(R.T)   # column-major
+        check(lib().kst_problem_set_regularization(self._h, ptr(Rc)))
+        return self
 
     def informationmatrix(self, points, weights, draw=0):
         w = f64(weights).ravel()

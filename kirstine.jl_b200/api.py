@@ -268,6 +268,14 @@ class FisherMatrix:
     pass
 
 
+class RegularizedFisherMatrix:
+    """The user-extension normal approximation of docs/src/extend-approximation.md:69-79: informationmatrix!
+    adds the constant matrix R to every average Fisher matrix."""
+
+    def __init__(self, R):
+        self.R = np.asarray(R, dtype=np.float64)
+
+
 class PriorSample:
     """PriorSample(p[, weights]) (src/priorknowledge.jl:11-38)."""
 
@@ -350,8 +358,9 @@ class DesignProblem:
         if not isinstance(model, Model) or model.model_id is None:
             raise TypeError("model type %s is not registered with the B200 engine; keep using stock Kirstine "
                             "for arbitrary user models" % type(model).__name__)
-        if not isinstance(self.na, FisherMatrix):
-            raise TypeError("only the FisherMatrix normal approximation is registered with the B200 engine")
+        if not isinstance(self.na, (FisherMatrix, RegularizedFisherMatrix)):
+            raise TypeError("only the FisherMatrix and RegularizedFisherMatrix normal approximations are registered "
+                            "with the B200 engine")
         self._handle_cache = None
 
     def handle(self):
@@ -360,6 +369,8 @@ class DesignProblem:
             h = _ffi.ProblemHandle(self.m.model_id, self.m._params(), self.pk.theta, self.pk.weight, self.dc.crit_id,
                                    dt, self.dr.lowerbound, self.dr.upperbound, m=self.m.m, cp_id=self.cp.cp_id,
                                    device=self.device, cp_params=self.cp._params())
+            if isinstance(self.na, RegularizedFisherMatrix):
+                h.set_regularization(self.na.R)
             if self.comm is not None:
                 h.comm_init(*self.comm)
             self._handle_cache = h
@@ -447,6 +458,8 @@ def informationmatrix(d, m, cp, p, na):
     h = _ffi.ProblemHandle(m.model_id, m._params(), p, [1.0], _ffi.CRIT_D, None, lo, hi, m=m.m, cp_id=cp.cp_id,
                            cp_params=cp._params())
     try:
+        if isinstance(na, RegularizedFisherMatrix):
+            h.set_regularization(na.R)
         return h.informationmatrix(d.points, d.weights, 0)
     finally:
         h.close()

@@ -303,7 +303,7 @@ extern "C" int kst_problem_destroy(kst_problem *h)
         if (r != h->rank && h->peer_map[r]) cudaIpcCloseMemHandle(h->peer_map[r]);
     if (h->peer_local) cudaFree(h->peer_local);
     kst_pso_free(h);
-    void *ptrs[] = {h->theta, h->pw, h->dc, h->cs, h->aux, h->partials, h->stage_pts, h->stage_w, h->stage_fx,
+    void *ptrs[] = {h->theta, h->pw, h->dc, h->cs, h->aux, h->reg, h->partials, h->stage_pts, h->stage_w, h->stage_fx,
                     h->gA, h->gtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials};
     for (void *p : ptrs)
         if (p) cudaFree(p);
@@ -504,6 +504,50 @@ extern "C" int kst_objective_batch(kst_problem *h, int S, int K, const double *p
     if (rc) return rc;
     KST_CUDA(cudaMemcpyAsync(fx, h->stage_fx, sizeof(double) * S, cudaMemcpyDeviceToHost, h->stream));
     KST_CUDA(cudaStreamSynchronize(h->stream));
+    return KST_OK;
+}
+
+// Rt_j = D_j^-1 R D_j^-1 (packed upper) for every draw of the handle
+__global__ void k_prep_reg(const double *__restrict__ cs, const double *__restrict__ Rm, int r, int64_t N, size_t ld,
+                           double *__restrict__ reg)
+{
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= N) return;
+    int idx = 0;
+    for (int a = 0; a < r; a++)
+        for (int b = a; b < r; b++, idx++)
+            reg[(size_t)idx * ld + j] = Rm[a + b * r] / (cs[(size_t)a * ld + j] * cs[(size_t)b * ld + j]);
+}
+
+extern "C" int kst_problem_set_regularization(kst_problem *h, const double *R)
+{
+    KST_CHECK_HANDLE(h);
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    h->g_ready = 0;
+    if (!R) {
+        if (h->reg) cudaFree(h->reg);
+        h->reg = nullptr;
+        return KST_OK;
+    }
+    const int r = h->r;
+    for (int i = 0; i < r * r; i++)
+        if (!std::isfinite(R[i])) { kst_set_error("set_regularization: R must be finite"); return KST_EINVAL; }
+    if (!h->reg) KST_CUDA(cudaMalloc(&h->reg, sizeof(double) * (size_t)(r * (r + 1) / 2) * h->ld));
+    double *d_R = nullptr;
+    KST_CUDA(cudaMalloc(&d_R, sizeof(double) * r * r));
+    cudaError_t e = cudaMemcpyAsync(d_R, R, sizeof(double) * r * r, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) {
+        k_prep_reg<<<(unsigned)((h->N + 255) / 256), 256, 0, h->stream>>>(h->cs, d_R, r, h->N, h->ld, h->reg);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(d_R);
+    if (e != cudaSuccess) {
+        cudaFree(h->reg);
+        h->reg = nullptr;
+        kst_set_error("set_regularization: %s", cudaGetErrorString(e));
+        return KST_ECUDA;
+    }
     return KST_OK;
 }
 

@@ -87,6 +87,9 @@ struct kst_problem {
     double *cs = nullptr;      // r   column scales
     double *aux = nullptr;     // A/Identity: r (1/cs^2); DeltaMethod: t*r (DT/cs); else unused
     int n_aux = 0;
+    // regularised normal approximation (kst_problem_set_regularization): Rt_j = D_j^-1 R D_j^-1, packed upper
+    // [r(r+1)/2][ld], added to every Mt_j; nullptr = FisherMatrix
+    double *reg = nullptr;
     double offset = 0.0;       // sum_j pw_j * 2 sum_i log|cs_ij|  (D / Identity), else 0
     int uniform_w = 0;         // all prior weights of this handle are the same positive finite number ...
     double w_uniform = 0.0;    // ... namely this one

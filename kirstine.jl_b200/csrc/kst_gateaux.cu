@@ -70,7 +70,8 @@ __device__ __forceinline__ int kst_build_rows(double *rows, double &sw, int &ran
 template <class MF>
 __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *__restrict__ cs,
                                   const double *__restrict__ aux, const double *__restrict__ pw, size_t ld,
-                                  int64_t N, int crit, int trafo, int t, const double *__restrict__ pts,
+                                  const double *__restrict__ reg, int64_t N, int crit, int trafo, int t,
+                                  const double *__restrict__ pts,
                                   const double *__restrict__ w, int K, KstModelParams mp, double *__restrict__ gA,
                                   double *__restrict__ gtrB, double *__restrict__ wtrB, int *flag)
 {
@@ -104,10 +105,17 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
     }
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
     if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = *s_sw;
+    // regularised normal approximation: informationmatrix!(afm, na) adds R (docs/src/extend-approximation.md:69-79)
+    double Rt[KstPacked<R>::N];
+#pragma unroll
+    for (int i = 0; i < KstPacked<R>::N; i++) {
+        Rt[i] = reg ? reg[(size_t)i * ld + j] : 0.0;
+        M[i] += Rt[i];
+    }
 
     double L[R][R], dv[R], dinv[R];
     bool ok = kst_ldlt<R, false>(M, L, dv, dinv, true);
-    ok = ok && s_na[1] >= R;  // fewer rows than parameters: singular by construction
+    ok = ok && (reg || s_na[1] >= R);  // fewer rows than parameters: singular by construction
     // Mt^-1 = Li' diag(dinv) Li with Li = L^-1 (unit lower)
     double Li[R][R];
 #pragma unroll
@@ -265,7 +273,14 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
 #pragma unroll
         for (int b = 0; b < R; b++) gA[(size_t)(a * R + b) * ld + j] = At[a][b];
     gtrB[j] = trB;
-    wtrB[j] = pw[j] * trB;
+    // the direction's matrix is regularised too (src/designproblem.jl:253-254): tr_prod(A, M(delta) + R, :U) adds
+    // the direction-independent tr_U[A R], folded into the constant here
+    double trAR = 0.0;
+#pragma unroll
+    for (int a = 0; a < R; a++)
+#pragma unroll
+        for (int b = a; b < R; b++) trAR = fma(At[a][b] * (a == b ? 1.0 : 2.0), Rt[kst_pidx<R>(a, b)], trAR);
+    wtrB[j] = pw[j] * (trB - trAR);
 }
 
 // One thread per direction; draws staged in shared memory.
@@ -438,7 +453,7 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
     const unsigned nb = (unsigned)((h->N + nt - 1) / nt);
     KST_MODEL_SWITCH(h->model_id, {
         const size_t smem = sizeof(double) * ((size_t)K * h->m * KstRowW<MF>::RW + 2);
-        k_gateaux_prepare<MF><<<nb, nt, smem, h->stream>>>(h->dc, h->cs, h->aux, h->pw, h->ld, h->N, h->crit, h->trafo,
+        k_gateaux_prepare<MF><<<nb, nt, smem, h->stream>>>(h->dc, h->cs, h->aux, h->pw, h->ld, h->reg, h->N, h->crit, h->trafo,
                                                            h->t, d_pts, d_w, K, h->mp, h->gA, h->gtrB, wtrB, h->d_flag);
     });
     KST_CUDA(cudaGetLastError());

@@ -24,6 +24,7 @@
 
 struct KstObjParams {
     const double *pw, *dc, *aux;
+    const double *reg;      // REG kernels: packed upper Rt_j, [r(r+1)/2][ld]
     size_t ld;
     int64_t N;
     const double *pts, *w;  // [S][K][d], [S][K]
@@ -217,7 +218,10 @@ __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na
 // multiplies determinants and takes one log per flush instead of one per draw.  The running product is kept
 // inside (2^-600, 2^600); a draw whose determinant would leave that range or is not positive definite flushes
 // the product and is evaluated on its own by the regular path.
-template <class MF, int CRIT, int T, bool UNI>
+// REG (regularised normal approximation, docs/src/extend-approximation.md:69-79): the per-draw constant matrix Rt_j
+// is added to Mt before the criterion; a design with fewer rows than parameters is then no longer singular and
+// the first pivot is no longer a per-particle constant.
+template <class MF, int CRIT, int T, bool UNI, bool REG = false>
 __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjParams prm)
 {
     constexpr int R = MF::R;
@@ -248,10 +252,10 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
         const int na = KstTile<MF>::nact(smem, rows_max)[p];
         const double sw = KstTile<MF>::sumw(smem, rows_max)[p];
         // 1 / first pivot, hoisted per particle when the first pivot is the constant-column entry
-        constexpr bool INV0 = MF::CONST_COL == 0;
+        constexpr bool INV0 = MF::CONST_COL == 0 && !REG;
         const double inv0 = KstTile<MF>::isumw(smem, rows_max)[p];
         double acc = 0.0;
-        if (KstTile<MF>::rank(smem, rows_max)[p] < R) {
+        if (!REG && KstTile<MF>::rank(smem, rows_max)[p] < R) {
             // fewer live rows than parameters: singular by construction (one-point designs etc.).  The
             // reference reaches the same -Inf through an exactly zero pivot: weighted by the prior weight
             // for log_det! (0 * -Inf = NaN, as there), unweighted where it throws.
@@ -280,6 +284,10 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
                 }
                 double M[KstPacked<R>::N];
                 kst_fisher<MF>(M, rows_addr, na, sw, dcv, tab);
+                if (REG) {
+#pragma unroll
+                    for (int i = 0; i < KstPacked<R>::N; i++) M[i] += __ldg(prm.reg + (size_t)((unsigned)i * ld + (unsigned)j));
+                }
                 if (UNI) {
                     double det;
                     int signs;
@@ -326,8 +334,8 @@ __global__ void k_obj_finish(const double *__restrict__ partials, int n_blk, dou
 
 // informationmatrix for one draw (debugging aid of the reference, src/design-common.jl:96-112)
 template <class MF>
-__global__ void k_infomatrix(const double *dc, const double *cs, size_t ld, int64_t j, const double *pts,
-                             const double *w, int K, KstModelParams mp, double *Mout)
+__global__ void k_infomatrix(const double *dc, const double *cs, const double *reg, size_t ld, int64_t j,
+                             const double *pts, const double *w, int K, KstModelParams mp, double *Mout)
 {
     constexpr int R = MF::R;
     extern __shared__ __align__(16) double smem[];
@@ -342,7 +350,8 @@ __global__ void k_infomatrix(const double *dc, const double *cs, size_t ld, int6
                    KstTile<MF>::sumw(smem, rows_max)[0], dcv, tab);
     for (int a = 0; a < R; a++)
         for (int b = a; b < R; b++) {
-            const double v = M[kst_pidx<R>(a, b)] * cs[(size_t)a * ld + j] * cs[(size_t)b * ld + j];
+            const double mt = M[kst_pidx<R>(a, b)] + (reg ? reg[(size_t)kst_pidx<R>(a, b) * ld + j] : 0.0);
+            const double v = mt * cs[(size_t)a * ld + j] * cs[(size_t)b * ld + j];
             Mout[a + b * R] = v;
             Mout[b + a * R] = v;
         }
@@ -425,11 +434,14 @@ static int launch_obj_t(kst_problem *h, const KstObjParams &prm, dim3 grid, size
 #define KST_LAUNCH_T(TV)                                                                        \
     case TV:                                                                                    \
         if (TV <= MF::R) {                                                                      \
-            k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false><<<grid, KST_NT, smem, h->stream>>>(prm); \
+            if (h->reg)                                                                         \
+                k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false, true><<<grid, KST_NT, smem, h->stream>>>(prm); \
+            else                                                                                \
+                k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false><<<grid, KST_NT, smem, h->stream>>>(prm); \
             return KST_OK;                                                                      \
         }                                                                                       \
         break;
-    if (CRIT == 0 && T == 0 && h->uniform_w) {
+    if (CRIT == 0 && T == 0 && h->uniform_w && !h->reg) {
         k_objective<MF, 0, 0, true><<<grid, KST_NT, smem, h->stream>>>(prm);
         return KST_OK;
     }
@@ -461,7 +473,7 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
     int rc = kst_ensure_partials(h, (size_t)S * n_blk);
     if (rc) return rc;
     KstObjParams prm;
-    prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.ld = h->ld; prm.N = h->N;
+    prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.reg = h->reg; prm.ld = h->ld; prm.N = h->N;
     prm.pts = d_pts; prm.w = d_w; prm.S = S; prm.K = K; prm.partials = h->partials; prm.mp = h->mp; prm.w_uniform = h->w_uniform;
     const dim3 grid(n_blk, tiles);
     if (h->prof_on) {
@@ -493,7 +505,7 @@ int kst_launch_infomatrix(kst_problem *h, int K, const double *d_pts, const doub
         return KST_EINVAL;
     }
     KST_MODEL_SWITCH(h->model_id, (k_infomatrix<MF><<<1, 32, KstTile<MF>::bytes(K * h->m), h->stream>>>(
-                                      h->dc, h->cs, h->ld, draw, d_pts, d_w, K, h->mp, d_M)));
+                                      h->dc, h->cs, h->reg, h->ld, draw, d_pts, d_w, K, h->mp, d_M)));
     KST_CUDA(cudaGetLastError());
     return KST_OK;
 }
@@ -571,7 +583,7 @@ extern "C" int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const d
     const int tiles = kst_objective_grid(h, S, &n_blk);
     if ((size_t)n_blk * S > KST_NOALLOC_MAX_PARTIALS) n_blk = KST_NOALLOC_MAX_PARTIALS / S;  // >= 64 by the swarm limit
     KstObjParams prm;
-    prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.ld = h->ld; prm.N = h->N;
+    prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.reg = h->reg; prm.ld = h->ld; prm.N = h->N;
     prm.pts = d_points; prm.w = d_weights; prm.S = S; prm.K = K; prm.partials = scratch; prm.mp = h->mp; prm.w_uniform = h->w_uniform;
     const dim3 grid(n_blk, tiles);
     KST_MODEL_SWITCH(h->model_id, {

@@ -46,6 +46,7 @@ def lib():
         L.ko_create.argtypes = [C.c_int, _dp, C.c_int, C.c_int, _dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                 C.c_int, C.c_int, C.c_long, _dp, _dp, _dp]
         L.ko_destroy.argtypes = [C.c_void_p]
+        L.ko_set_regularization.argtypes = [C.c_void_p, _dp]
         L.ko_objective.restype = C.c_double
         L.ko_objective.argtypes = [C.c_void_p, C.c_int, _dp, _dp]
         L.ko_objective_range.restype = C.c_double
@@ -125,6 +126,12 @@ class Problem:
         if not self._h:
             raise ValueError("oracle: dimensions out of range")
         self.theta, self.pw, self.dt = theta, pw, dt
+
+    def set_regularization(self, R):
+        """normal_approximation = RegularizedFisherMatrix(R) (docs/src/extend-approximation.md:69-79); None = FisherMatrix."""
+        Rc = None if R is None else _f64(np.asarray(R, dtype=np.float64).T)   # column-major
+        lib().ko_set_regularization(self._h, _d(Rc))
+        return self
 
     def __del__(self):
         if getattr(self, "_h", None) and _lib is not None:

@@ -49,6 +49,8 @@ typedef struct {
     double *theta; /* N x r, AoS (one parameter struct after the other) */
     double *pw;    /* N prior weights */
     double *dt;    /* N x (t x r col-major), NULL for identity */
+    int has_reg;   /* normal approximation: 0 FisherMatrix, 1 RegularizedFisherMatrix */
+    double reg[KO_MAXR * KO_MAXR]; /* R (r x r col-major) of docs/src/extend-approximation.md:69-79 */
 } ko_problem;
 
 #define IDX(i, j, ld) ((i) + (size_t)(j) * (ld))
@@ -461,7 +463,11 @@ static void ko_update_workspace(const ko_problem *p, int K, const double *pts, k
     }
 }
 
-/* average_fishermatrix! (src/model-nonlinear-regression.jl:60-86) */
+/* average_fishermatrix! (src/model-nonlinear-regression.jl:60-86), followed by
+ * informationmatrix!(afm, na) (src/design-common.jl:74-76 for FisherMatrix: identity;
+ * docs/src/extend-approximation.md:69-79 for RegularizedFisherMatrix: afm .+= R).
+ * Every caller in the reference applies the two back to back (src/design-common.jl:109-110,
+ * src/designproblem.jl:206-207,253-254). */
 static void ko_average_fishermatrix(const ko_problem *p, int K, const double *wts,
                                     const double *th, ko_ws *w)
 {
@@ -474,13 +480,15 @@ static void ko_average_fishermatrix(const ko_problem *p, int K, const double *wt
             double p1mp = prob * (1 - prob);
             ko_syrk_ut(r, 1, p1mp * wts[k], w->mxr, w->rxr);
         }
-        return;
+    } else {
+        for (int k = 0; k < K; k++) {
+            ko_jacobian(p, w->c + k * KO_MAXC, th, w->mxr);
+            ko_trsm_lutn(m, r, w->chol + k * KO_MAXM * KO_MAXM, w->mxr);
+            ko_syrk_ut(r, m, wts[k], w->mxr, w->rxr);
+        }
     }
-    for (int k = 0; k < K; k++) {
-        ko_jacobian(p, w->c + k * KO_MAXC, th, w->mxr);
-        ko_trsm_lutn(m, r, w->chol + k * KO_MAXM * KO_MAXM, w->mxr);
-        ko_syrk_ut(r, m, wts[k], w->mxr, w->rxr);
-    }
+    if (p->has_reg)
+        for (int i = 0; i < r * r; i++) w->rxr[i] += p->reg[i];
 }
 
 /* informationmatrix (src/design-common.jl:96-112): full Symmetric copy */
@@ -715,6 +723,13 @@ ko_problem *ko_create(int model_id, const double *mp, int nmp, int cp_id, const 
         memcpy(p->dt, dt, sizeof(double) * N * t * r);
     }
     return p;
+}
+
+/* normal_approximation = RegularizedFisherMatrix(R); R is r x r column-major, NULL switches back to FisherMatrix */
+void ko_set_regularization(ko_problem *p, const double *R)
+{
+    p->has_reg = R != NULL;
+    if (R) memcpy(p->reg, R, sizeof(double) * p->r * p->r);
 }
 
 void ko_destroy(ko_problem *p)
