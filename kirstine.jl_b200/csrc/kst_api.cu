@@ -5,6 +5,8 @@
 #include <stddef.h>
 #include <string.h>
 
+#include <cmath>
+#include <mutex>
 #include <new>
 
 #include "kst_common.cuh"
@@ -54,8 +56,11 @@ struct NcclApi {
 } g_nccl;
 const int KST_NCCL_FLOAT64 = 8, KST_NCCL_SUM = 0;  // ncclDataType_t / ncclRedOp_t values (stable ABI)
 
+std::mutex g_nccl_mutex;
+
 int load_nccl()
 {
+    std::lock_guard<std::mutex> lock(g_nccl_mutex);  // handles on different threads may attach communicators at once
     if (g_nccl.lib) return KST_OK;
     const char *names[] = {"libnccl.so.2", "libnccl.so"};
     void *lib = nullptr;
@@ -220,10 +225,11 @@ extern "C" int kst_comm_peer_handle(kst_problem *h, int nranks, int rank, void *
     }
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     KST_CUDA(cudaSetDevice(h->device));
-    if (!h->peer_local) {
-        KST_CUDA(cudaMalloc(&h->peer_local, sizeof(KstPeerBlock)));
-        KST_CUDA(cudaMemset(h->peer_local, 0, sizeof(KstPeerBlock)));
-    }
+    if (!h->peer_local) KST_CUDA(cudaMalloc(&h->peer_local, sizeof(KstPeerBlock)));
+    // a fresh exchange starts at sequence 0 on every rank: stale flags from an earlier group must not satisfy a wait
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    KST_CUDA(cudaMemset(h->peer_local, 0, sizeof(KstPeerBlock)));
+    h->peer_ready = 0;
     cudaIpcMemHandle_t ipc;
     KST_CUDA(cudaIpcGetMemHandle(&ipc, h->peer_local));
     memcpy(handle64, &ipc, sizeof(ipc));
@@ -452,6 +458,7 @@ static int ensure_stage(kst_problem *h, size_t particles, size_t rows)
     if (particles > h->stage_cap_particles) {
         if (h->stage_fx) KST_CUDA(cudaFree(h->stage_fx));
         h->stage_fx = nullptr;
+        h->stage_cap_particles = 0;  // stays 0 if the allocation below fails
         KST_CUDA(cudaMalloc(&h->stage_fx, sizeof(double) * particles));
         h->stage_cap_particles = particles;
     }
@@ -459,6 +466,7 @@ static int ensure_stage(kst_problem *h, size_t particles, size_t rows)
         if (h->stage_pts) KST_CUDA(cudaFree(h->stage_pts));
         if (h->stage_w) KST_CUDA(cudaFree(h->stage_w));
         h->stage_pts = h->stage_w = nullptr;
+        h->stage_cap_rows = 0;
         KST_CUDA(cudaMalloc(&h->stage_pts, sizeof(double) * rows * h->d));
         KST_CUDA(cudaMalloc(&h->stage_w, sizeof(double) * rows));
         h->stage_cap_rows = rows;
@@ -580,8 +588,8 @@ extern "C" int kst_gateaux_prepare(kst_problem *h, int K, const double *points, 
     KST_CUDA(cudaMemcpyAsync(h->stage_w, weights, sizeof(double) * K, cudaMemcpyHostToDevice, h->stream));
     rc = kst_launch_gateaux_prepare(h, K, h->stage_pts, h->stage_w);
     if (rc) return rc;
-    if (h->comm) {
-        // every rank must agree on "singular": sum the per-shard flags
+    if (h->nranks > 1) {
+        // every rank must agree on "singular": sum the per-shard flags (NCCL or the peer exchange, whichever is set up)
         double f = (double)h->g_singular, *d_f = h->stage_fx;
         KST_CUDA(cudaMemcpyAsync(d_f, &f, sizeof(double), cudaMemcpyHostToDevice, h->stream));
         rc = kst_allreduce_sum(h, d_f, 1);

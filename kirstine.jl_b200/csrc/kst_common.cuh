@@ -132,7 +132,7 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
                          double *d_fx);
 int kst_launch_infomatrix(kst_problem *h, int K, const double *d_pts, const double *d_w,
                           int64_t draw, double *d_M);
-int kst_objective_grid(const kst_problem *h, int S, int *n_blk);
+int kst_objective_grid(const kst_problem *h, int S, int *n_blk, int *tile_p);
 int kst_sum_fixed(kst_problem *h, const double *d_x, int64_t n, double *host_out);
 // kst_gateaux.cu
 int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const double *d_w);

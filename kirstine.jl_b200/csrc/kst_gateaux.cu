@@ -471,7 +471,9 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
 template <class MF, int MR>
 static int launch_gd(kst_problem *h, dim3 grid, int64_t G, const double *d_dirs, size_t smem)
 {
-    if (smem > 48 * 1024)  // vector units with many rows: opt in to a large dynamic shared-memory window
+    // vector units with many rows: opt in to a large dynamic shared-memory window (the static math tables count
+    // towards the 48 KB a kernel gets without asking)
+    if (smem + sizeof(double) * KST_MATH_SMEM > 48 * 1024)
         KST_CUDA(cudaFuncSetAttribute(k_gateaux_eval<MF, MR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_gateaux_eval<MF, MR><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->pw, h->gA, h->ld, h->N, d_dirs, G, h->mp,
                                                                  h->gd_partials);

@@ -32,6 +32,7 @@ struct KstObjParams {
     double *partials;       // [S][n_blk]
     KstModelParams mp;
     double w_uniform;       // the common prior weight when all weights are equal (UNI kernels), else unused
+    int tile_p;             // particles per CTA, 1..KST_TILE_P (small problems use small tiles to fill the SMs)
 };
 
 // ------------------------------------------------------------------------------------------
@@ -109,11 +110,11 @@ struct KstTile {
 template <class MF>
 __device__ __forceinline__ void kst_build_tile(double *smem, const double *__restrict__ pts,
                                                const double *__restrict__ w, int p0, int S, int K,
-                                               const KstModelParams &mp)
+                                               const KstModelParams &mp, int tile_p = KST_TILE_P)
 {
     const int rows_max = K * mp.m;
     constexpr int RW = KstTile<MF>::RW;
-    if (threadIdx.x < KST_TILE_P) {
+    if ((int)threadIdx.x < tile_p) {
         const int p = p0 + threadIdx.x;
         double *rows = KstTile<MF>::rows(smem) + (size_t)threadIdx.x * rows_max * RW;
         int na = 0, ntriv = 0;
@@ -228,12 +229,12 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
     extern __shared__ __align__(16) double smem[];
     __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
     const int rows_max = prm.K * prm.mp.m;
-    const int p0 = blockIdx.y * KST_TILE_P;
+    const int p0 = blockIdx.y * prm.tile_p;
     KstTab tab = kst_math_init(s_mathtab);
-    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp);  // ends with __syncthreads()
+    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp, prm.tile_p);  // ends with __syncthreads()
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int np = min(KST_TILE_P, prm.S - p0);
+    const int np = min(prm.tile_p, prm.S - p0);
     double *wsum = KstTile<MF>::wsum(smem, rows_max);
     // 32-bit draw indices (the launcher guarantees N + stride < 2^31) and 32-bit shared-space addresses:
     // the loop bookkeeping is a handful of integer instructions
@@ -404,11 +405,19 @@ int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const doubl
     return rc;
 }
 
-int kst_objective_grid(const kst_problem *h, int S, int *n_blk)
+// Grid of the evaluation kernel: tiles of *tile_p particles (gridDim.y) x n_blk draw splits (gridDim.x).
+// Large problems use full tiles of KST_TILE_P particles (each draw's constants are loaded once per tile) and at
+// least 8 waves.  Small problems -- the reference's own test and vignette sizes, a few dozen particles against a
+// thousand draws -- cannot fill one wave that way and would run KST_TILE_P particles back to back on a handful of
+// SMs; they get the largest tile size that still yields a full wave of CTAs (down to one particle per CTA).
+int kst_objective_grid(const kst_problem *h, int S, int *n_blk, int *tile_p)
 {
-    const int tiles = (S + KST_TILE_P - 1) / KST_TILE_P;
     const int64_t max_chunks = (h->N + KST_NT - 1) / KST_NT;
     const int cap = h->sm_count * KST_MINB;  // resident CTAs per wave
+    int tp = KST_TILE_P;
+    while (tp > 1 && (int64_t)((S + tp - 1) / tp) * max_chunks < cap) tp >>= 1;
+    *tile_p = tp;
+    const int tiles = (S + tp - 1) / tp;
     // aim for >= 8 waves, then pick the draw split whose last wave is fullest
     int64_t lo = (8LL * cap + tiles - 1) / tiles;
     if (lo < 1) lo = 1;
@@ -427,6 +436,14 @@ int kst_objective_grid(const kst_problem *h, int S, int *n_blk)
     return tiles;
 }
 
+// Units with many rows (K * m up to KST_MAX_ROWS): the particle tile plus the static math tables can exceed the
+// 48 KB of shared memory a kernel gets without asking
+#define KST_OPT_IN(kernel)                                                                              \
+    do {                                                                                                \
+        if (smem + sizeof(double) * KST_MATH_SMEM > 48 * 1024)                                          \
+            KST_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    } while (0)
+
 template <class MF, int CRIT>
 static int launch_obj_t(kst_problem *h, const KstObjParams &prm, dim3 grid, size_t smem)
 {
@@ -434,14 +451,18 @@ static int launch_obj_t(kst_problem *h, const KstObjParams &prm, dim3 grid, size
 #define KST_LAUNCH_T(TV)                                                                        \
     case TV:                                                                                    \
         if (TV <= MF::R) {                                                                      \
-            if (h->reg)                                                                         \
+            if (h->reg) {                                                                       \
+                KST_OPT_IN((k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false, true>));       \
                 k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false, true><<<grid, KST_NT, smem, h->stream>>>(prm); \
-            else                                                                                \
+            } else {                                                                            \
+                KST_OPT_IN((k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false>));             \
                 k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false><<<grid, KST_NT, smem, h->stream>>>(prm); \
+            }                                                                                   \
             return KST_OK;                                                                      \
         }                                                                                       \
         break;
     if (CRIT == 0 && T == 0 && h->uniform_w && !h->reg) {
+        KST_OPT_IN((k_objective<MF, 0, 0, true>));
         k_objective<MF, 0, 0, true><<<grid, KST_NT, smem, h->stream>>>(prm);
         return KST_OK;
     }
@@ -468,13 +489,13 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
         kst_set_error("objective: at most 2^29 draws per GPU (shard the prior sample over more GPUs)");
         return KST_ELIMIT;
     }
-    int n_blk = 1;
-    const int tiles = kst_objective_grid(h, S, &n_blk);
+    int n_blk = 1, tile_p = KST_TILE_P;
+    const int tiles = kst_objective_grid(h, S, &n_blk, &tile_p);
     int rc = kst_ensure_partials(h, (size_t)S * n_blk);
     if (rc) return rc;
     KstObjParams prm;
     prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.reg = h->reg; prm.ld = h->ld; prm.N = h->N;
-    prm.pts = d_pts; prm.w = d_w; prm.S = S; prm.K = K; prm.partials = h->partials; prm.mp = h->mp; prm.w_uniform = h->w_uniform;
+    prm.pts = d_pts; prm.w = d_w; prm.S = S; prm.K = K; prm.partials = h->partials; prm.mp = h->mp; prm.w_uniform = h->w_uniform; prm.tile_p = tile_p;
     const dim3 grid(n_blk, tiles);
     if (h->prof_on) {
         cudaEvent_t e0, e1;
@@ -504,8 +525,11 @@ int kst_launch_infomatrix(kst_problem *h, int K, const double *d_pts, const doub
         kst_set_error("informationmatrix: bad K or draw index");
         return KST_EINVAL;
     }
-    KST_MODEL_SWITCH(h->model_id, (k_infomatrix<MF><<<1, 32, KstTile<MF>::bytes(K * h->m), h->stream>>>(
-                                      h->dc, h->cs, h->reg, h->ld, draw, d_pts, d_w, K, h->mp, d_M)));
+    KST_MODEL_SWITCH(h->model_id, {
+        const size_t smem = KstTile<MF>::bytes(K * h->m);
+        KST_OPT_IN(k_infomatrix<MF>);
+        k_infomatrix<MF><<<1, 32, smem, h->stream>>>(h->dc, h->cs, h->reg, h->ld, draw, d_pts, d_w, K, h->mp, d_M);
+    });
     KST_CUDA(cudaGetLastError());
     return KST_OK;
 }
@@ -579,12 +603,12 @@ extern "C" int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const d
     double *scratch = nullptr;
     int rc = kst_noalloc_scratch_ptr(h->device, &scratch);
     if (rc) return rc;
-    int n_blk = 1;
-    const int tiles = kst_objective_grid(h, S, &n_blk);
+    int n_blk = 1, tile_p = KST_TILE_P;
+    const int tiles = kst_objective_grid(h, S, &n_blk, &tile_p);
     if ((size_t)n_blk * S > KST_NOALLOC_MAX_PARTIALS) n_blk = KST_NOALLOC_MAX_PARTIALS / S;  // >= 64 by the swarm limit
     KstObjParams prm;
     prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.reg = h->reg; prm.ld = h->ld; prm.N = h->N;
-    prm.pts = d_points; prm.w = d_weights; prm.S = S; prm.K = K; prm.partials = scratch; prm.mp = h->mp; prm.w_uniform = h->w_uniform;
+    prm.pts = d_points; prm.w = d_weights; prm.S = S; prm.K = K; prm.partials = scratch; prm.mp = h->mp; prm.w_uniform = h->w_uniform; prm.tile_p = tile_p;
     const dim3 grid(n_blk, tiles);
     KST_MODEL_SWITCH(h->model_id, {
         const size_t smem = KstTile<MF>::bytes(K * h->m);

@@ -94,3 +94,25 @@ def test_dtr_solve_and_equivalence_theorem():  # docs/src/dtr.md:263-300 (CopyBo
         kb.objective(s, kb.DesignProblem(criterion=kb.DCriterion(), region=kb.DesignInterval(dose=(0, 100)),
                                          model=kb.DTRMod(1, 1), covariate_parameterization=kb.CopyBoth(),
                                          prior_knowledge=prior))
+
+
+def test_dtr_maximum_unit_size():
+    """K * m = KST_MAX_ROWS = 128 rows per particle with the widest row record: the particle tile plus the math
+    tables need more than the 48 KB of shared memory a kernel gets by default (opt-in path)."""
+    theta = wl.dtr_prior(100, seed=7)
+    times = list(np.linspace(0.5, 24.0, 16))
+    pw = np.full(len(theta), 1.0 / len(theta))
+    h = kb.ProblemHandle(5, [1.0], theta, pw, 0, None, [0.0], [100.0], m=16, cp_id=4, cp_params=times)
+    o = ko.Problem(ko.DTR, [1.0], theta, m=16, d=1, cp_id=4, cp_params=times)
+    pts, w = wl.jittered_swarm_nd(9, 8, [0.0], [100.0], seed=11)
+    got, want = h.objective_batch(pts, w), o.objective_batch(pts, w, nthreads=8)
+    rf.assert_parity(got, want, lambda i: rf.objective(5, [1.0], pts[i], w[i], theta, pw, m=16, cov=(4, times)),
+                     rtol=RTOL)
+    M = h.informationmatrix(pts[0], w[0], 5)
+    np.testing.assert_allclose(M, o.informationmatrix(pts[0], w[0], 5), rtol=1e-9, atol=1e-14 * np.abs(M).max())
+    dirs = np.linspace(0.0, 100.0, 300)
+    assert not h.gateaux_prepare(pts[0], w[0])
+    gd, wgd = h.gateaux_eval(dirs), o.gateauxderivative(pts[0], w[0], dirs, nthreads=8)
+    np.testing.assert_allclose(gd, wgd, rtol=1e-8, atol=1e-8 * np.abs(wgd).max())
+    with pytest.raises(kb.EngineError):
+        h.objective_batch(np.zeros((2, 9, 1)), np.full((2, 9), 1 / 9))   # 9 * 16 rows > KST_MAX_ROWS
