@@ -1,0 +1,6 @@
+// explicit instantiations of the objective evaluation kernels (see kst_objective_kernel.cuh)
+#include "kst_objective_kernel.cuh"
+
+template int kst_obj_launch<KstEmax>(kst_problem *, const KstObjParams &, dim3, int);
+template int kst_obj_launch<KstTpc>(kst_problem *, const KstObjParams &, dim3, int);
+template int kst_obj_launch<KstVu>(kst_problem *, const KstObjParams &, dim3, int);

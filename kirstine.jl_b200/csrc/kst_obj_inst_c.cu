@@ -1,0 +1,4 @@
+// explicit instantiations of the objective evaluation kernels (see kst_objective_kernel.cuh)
+#include "kst_objective_kernel.cuh"
+
+template int kst_obj_launch<KstDtr>(kst_problem *, const KstObjParams &, dim3, int);

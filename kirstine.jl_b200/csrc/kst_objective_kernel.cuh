@@ -1,0 +1,322 @@
+// Evaluation kernel of the objective and its per-family launch code (see kst_objective.cu for the mapping).
+// Included by kst_objective.cu (host entry points, small kernels) and by the kst_obj_inst_*.cu files, each of
+// which instantiates kst_obj_launch for some model families so that the families compile in parallel.
+#pragma once
+#ifndef KST_ROWS_OVERRIDE
+#define KST_ROWS_OVERRIDE 0  // tuning: force the row interleave factor (1, 2, 4, 8) for every family
+#endif
+
+
+
+#include "kst_common.cuh"
+#include "kst_linalg.cuh"
+
+struct KstObjParams {
+    const double *pw, *dc, *aux;
+    const double *reg;      // REG kernels: packed upper Rt_j, [r(r+1)/2][ld]
+    size_t ld;
+    int64_t N;
+    const double *pts, *w;  // [S][K][d], [S][K]
+    int S, K;
+    double *partials;       // [S][n_blk]
+    KstModelParams mp;
+    double w_uniform;       // the common prior weight when all weights are equal (UNI kernels), else unused
+    int tile_p;             // particles per CTA, 1..KST_TILE_P (small problems use small tiles to fill the SMs)
+};
+
+// ------------------------------------------------------------------------------------------
+// shared-memory particle tile
+// ------------------------------------------------------------------------------------------
+template <class MF>
+struct KstTile {
+    // doubles per row: sqrt(omega), pc...; padded to an even count so rows can be read as 16-byte vectors
+    static constexpr int RW = (1 + MF::NPC + 1) / 2 * 2;
+    // layout (doubles): rows[P][rows_max][RW] | sumw[P] | isumw[P] | wsum[P][NT/32] ; then ints nact[P], rank[P]
+    __device__ static double *rows(double *s) { return s; }
+    __device__ static double *sumw(double *s, int rows_max) { return s + (size_t)KST_TILE_P * rows_max * RW; }
+    __device__ static double *isumw(double *s, int rows_max) { return sumw(s, rows_max) + KST_TILE_P; }
+    __device__ static double *wsum(double *s, int rows_max) { return isumw(s, rows_max) + KST_TILE_P; }
+    __device__ static int *nact(double *s, int rows_max) { return (int *)(wsum(s, rows_max) + KST_TILE_P * (KST_NT / 32)); }
+    // upper bound on rank(Mt): below R the design is singular whatever the rounding does
+    __device__ static int *rank(double *s, int rows_max) { return nact(s, rows_max) + KST_TILE_P; }
+    __host__ static size_t bytes(int rows_max)
+    {
+        return sizeof(double) * ((size_t)KST_TILE_P * rows_max * RW + 2 * KST_TILE_P + KST_TILE_P * (KST_NT / 32)) +
+               sizeof(int) * 2 * KST_TILE_P;
+    }
+};
+
+// One thread per particle of the tile: map design points to rows (map_to_covariate! +
+// update_model_vcov!, src/design-common.jl:51-61, src/model-nonlinear-regression.jl:39-49),
+// hoist covariate-only transcendentals, drop trivial and zero-weight rows.
+template <class MF>
+__device__ __forceinline__ void kst_build_tile(double *smem, const double *__restrict__ pts,
+                                               const double *__restrict__ w, int p0, int S, int K,
+                                               const KstModelParams &mp, int tile_p = KST_TILE_P)
+{
+    const int rows_max = K * mp.m;
+    constexpr int RW = KstTile<MF>::RW;
+    if ((int)threadIdx.x < tile_p) {
+        const int p = p0 + threadIdx.x;
+        double *rows = KstTile<MF>::rows(smem) + (size_t)threadIdx.x * rows_max * RW;
+        int na = 0, ntriv = 0;
+        double sw = 0.0;
+        if (p < S) {
+            for (int k = 0; k < K; k++) {
+                const double *z = pts + ((size_t)p * K + k) * mp.d;
+                const double wk = w[(size_t)p * K + k];
+                for (int i = 0; i < mp.m; i++) {
+                    double pc[MF::NPC], varfac;
+                    const bool trivial = MF::prep_row(z, i, mp, pc, varfac);
+                    const double om = wk * varfac;
+                    sw += om;
+                    if (om == 0.0) continue;  // zero weight: contributes nothing, not even rank
+                    if (!trivial) {
+                        const double sq = sqrt(om);
+                        MF::post_row(pc, sq);
+                        rows[na * RW] = sq;
+#pragma unroll
+                        for (int c = 0; c < MF::NPC; c++) rows[na * RW + 1 + c] = pc[c];
+                        na++;
+                    } else {
+                        ntriv++;
+                    }
+                }
+            }
+        }
+        int rank = na + ((MF::CONST_COL >= 0 && ntriv > 0) ? 1 : 0);
+        // the hoisted first pivot must be a positive, finite number; otherwise the design is singular
+        // (or its weights are NaN) and every draw takes the rank-deficient path
+        if (MF::CONST_COL >= 0 && !(sw > 0.0 && sw < KST_INF)) rank = 0;
+        if (na == 0) {
+            // the evaluation loop always runs the first row: give it a weightless, harmless one
+            double pc[MF::NPC], vf;
+            const double one = 1.0;
+            MF::prep_row(&one, 1, mp, pc, vf);
+            MF::post_row(pc, 0.0);
+            rows[0] = 0.0;
+#pragma unroll
+            for (int c = 0; c < MF::NPC; c++) rows[1 + c] = pc[c];
+            na = 1;
+        }
+        KstTile<MF>::sumw(smem, rows_max)[threadIdx.x] = sw;
+        KstTile<MF>::isumw(smem, rows_max)[threadIdx.x] = 1.0 / sw;
+        KstTile<MF>::nact(smem, rows_max)[threadIdx.x] = na;
+        KstTile<MF>::rank(smem, rows_max)[threadIdx.x] = rank;
+    }
+    __syncthreads();
+}
+
+// one row record (RW doubles at a 32-bit shared-space address) -> weighted row g
+template <class MF>
+__device__ __forceinline__ void kst_row_at(unsigned addr, const double *dcv, double *g, KstTab tab)
+{
+    constexpr int RW = KstTile<MF>::RW;
+    double rw[RW];
+#pragma unroll
+    for (int c = 0; c < RW; c += 2)
+        asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rw[c]), "=d"(rw[c + 1]) : "r"(addr + 8u * c));
+    MF::row(rw + 1, dcv, rw[0], g, tab);
+}
+
+// NR consecutive rows: all reduced rows first, then all rank-one updates, so that the NR exp / reciprocal
+// chains are independent instruction streams the scheduler can interleave
+template <class MF, int NR>
+__device__ __forceinline__ void kst_rows(double *M, unsigned addr, const double *dcv, KstTab tab)
+{
+    constexpr int R = MF::R, RW = KstTile<MF>::RW;
+    double g[NR][R];
+#pragma unroll
+    for (int k = 0; k < NR; k++) kst_row_at<MF>(addr + (unsigned)(k * RW * 8), dcv, g[k], tab);
+#pragma unroll
+    for (int k = 0; k < NR; k++) kst_accum<R, MF::CONST_COL>(M, g[k]);
+}
+
+// Mt = sum over the particle's live rows (at least one) of g g'; rows_addr is a shared-space address.
+// Remainders first (1, 2, 4 rows by the bits of na), then groups of MF::ROWS rows: the FP64 pipe only
+// saturates with about four independent dependency chains per warp (tools/fp64_probe.cu), which the
+// interleaved rows provide; there is no remainder code after the loop.
+template <class MF>
+__device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na, double sw, const double *dcv,
+                                           KstTab tab)
+{
+    constexpr int R = MF::R, RW = KstTile<MF>::RW, UN = KST_ROWS_OVERRIDE > 0 ? KST_ROWS_OVERRIDE : MF::ROWS;
+#pragma unroll
+    for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
+    unsigned addr = rows_addr;
+    int left = na;
+    if (UN > 1 && (left & 1)) { kst_rows<MF, 1>(M, addr, dcv, tab); addr += RW * 8; left -= 1; }
+    if (UN > 2 && (left & 2)) { kst_rows<MF, 2>(M, addr, dcv, tab); addr += 2 * RW * 8; left -= 2; }
+    if (UN > 4 && (left & 4)) { kst_rows<MF, 4>(M, addr, dcv, tab); addr += 4 * RW * 8; left -= 4; }
+#pragma unroll 1
+    for (; left > 0; left -= UN, addr += UN * RW * 8) kst_rows<MF, UN>(M, addr, dcv, tab);
+    constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
+    if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = sw;
+}
+
+// ------------------------------------------------------------------------------------------
+// the hot kernel
+// ------------------------------------------------------------------------------------------
+// UNI (D criterion, Identity, all prior weights equal): sum_j w log det_j = w log prod_j det_j, so the thread
+// multiplies determinants and takes one log per flush instead of one per draw.  The running product is kept
+// inside (2^-600, 2^600); a draw whose determinant would leave that range or is not positive definite flushes
+// the product and is evaluated on its own by the regular path.
+// REG (regularised normal approximation, docs/src/extend-approximation.md:69-79): the per-draw constant matrix Rt_j
+// is added to Mt before the criterion; a design with fewer rows than parameters is then no longer singular and
+// the first pivot is no longer a per-particle constant.
+template <class MF, int CRIT, int T, bool UNI, bool REG = false>
+__global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjParams prm)
+{
+    constexpr int R = MF::R;
+    extern __shared__ __align__(16) double smem[];
+    __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
+    const int rows_max = prm.K * prm.mp.m;
+    const int p0 = blockIdx.y * prm.tile_p;
+    KstTab tab = kst_math_init(s_mathtab);
+    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp, prm.tile_p);  // ends with __syncthreads()
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int np = min(prm.tile_p, prm.S - p0);
+    double *wsum = KstTile<MF>::wsum(smem, rows_max);
+    // 32-bit draw indices (the launcher guarantees N + stride < 2^31) and 32-bit shared-space addresses:
+    // the loop bookkeeping is a handful of integer instructions
+    const int n = (int)prm.N, stride = (int)gridDim.x * KST_NT, j0 = (int)blockIdx.x * KST_NT + (int)threadIdx.x;
+    unsigned rows_base = (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem));
+    // make both shared-space bases opaque: otherwise the compiler rebuilds them from SR_CgaCtaId (a
+    // variable-latency S2R/S2UR + LEA) in front of every use instead of keeping them in a register
+    asm volatile("" : "+r"(tab), "+r"(rows_base));
+    const double *__restrict__ pw = prm.pw;
+    const double *__restrict__ dc = prm.dc;
+    const unsigned ld = (unsigned)prm.ld;
+
+#pragma unroll 1
+    for (int p = 0; p < np; p++) {
+        const unsigned rows_addr = rows_base + (unsigned)(p * rows_max * KstTile<MF>::RW * 8);
+        const int na = KstTile<MF>::nact(smem, rows_max)[p];
+        const double sw = KstTile<MF>::sumw(smem, rows_max)[p];
+        // 1 / first pivot, hoisted per particle when the first pivot is the constant-column entry
+        constexpr bool INV0 = MF::CONST_COL == 0 && !REG;
+        const double inv0 = KstTile<MF>::isumw(smem, rows_max)[p];
+        double acc = 0.0;
+        if (!REG && KstTile<MF>::rank(smem, rows_max)[p] < R) {
+            // fewer live rows than parameters: singular by construction (one-point designs etc.).  The
+            // reference reaches the same -Inf through an exactly zero pivot: weighted by the prior weight
+            // for log_det! (0 * -Inf = NaN, as there), unweighted where it throws.
+            // (Dexp: exp(-Inf / t) = 0 for such a draw.)
+            for (int j = j0; j < n; j += stride)
+                acc += T != 0 ? -KST_INF : (CRIT == 0 ? pw[j] * -KST_INF : (CRIT == 2 ? pw[j] * 0.0 : -KST_INF));
+        } else {
+            double run = 1.0;  // UNI: running product of determinants
+            // software prefetch: the next draw's constants are requested before this draw's rows are evaluated
+            double dcn[MF::NDC], pwn = 0.0;
+            if (j0 < n) {
+#pragma unroll
+                for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)j0));
+                pwn = __ldg(pw + j0);
+            }
+            for (int j = j0; j < n; j += stride) {
+                double dcv[MF::NDC];
+#pragma unroll
+                for (int c = 0; c < MF::NDC; c++) dcv[c] = dcn[c];
+                const double pwj = pwn;
+                const int jn = j + stride;
+                if (jn < n) {
+#pragma unroll
+                    for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
+                    pwn = __ldg(pw + jn);
+                }
+                double M[KstPacked<R>::N];
+                kst_fisher<MF>(M, rows_addr, na, sw, dcv, tab);
+                if (REG) {
+#pragma unroll
+                    for (int i = 0; i < KstPacked<R>::N; i++) M[i] += __ldg(prm.reg + (size_t)((unsigned)i * ld + (unsigned)j));
+                }
+                if (UNI) {
+                    double det;
+                    int signs;
+                    kst_det_signs<R, INV0>(M, inv0, det, signs);
+                    const double pn = run * det;
+                    const unsigned key = ((unsigned)signs & 0x80000000u) | (unsigned)__double2hiint(pn);
+                    if (((key >> 20) - 423u) < 1200u) {
+                        run = pn;
+                    } else {
+                        acc += kst_log(run, tab) + kst_log_checked(det, signs, tab);
+                        run = 1.0;
+                    }
+                } else {
+                    bool exc;
+                    const double val = kst_criterion<R, CRIT, T, INV0>(M, prm.aux + j, prm.ld, exc, inv0, tab);
+                    acc += exc ? -KST_INF : pwj * val;
+                }
+            }
+            if (UNI) acc = prm.w_uniform * (acc + kst_log(run, tab));
+        }
+        // fixed-order reduction over the CTA's draws
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+        if (lane == 0) wsum[p * (KST_NT / 32) + warp] = acc;
+    }
+    __syncthreads();
+    if (threadIdx.x < np) {
+        double s = 0.0;
+#pragma unroll
+        for (int wi = 0; wi < KST_NT / 32; wi++) s += wsum[threadIdx.x * (KST_NT / 32) + wi];
+        prm.partials[(size_t)(p0 + threadIdx.x) * gridDim.x + blockIdx.x] = s;
+    }
+}
+
+// Units with many rows (K * m up to KST_MAX_ROWS): the particle tile plus the static math tables can exceed the
+// 48 KB of shared memory a kernel gets without asking
+#define KST_OPT_IN(kernel)                                                                              \
+    do {                                                                                                \
+        if (smem + sizeof(double) * KST_MATH_SMEM > 48 * 1024)                                          \
+            KST_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    } while (0)
+
+template <class MF, int CRIT>
+static int launch_obj_t(kst_problem *h, const KstObjParams &prm, dim3 grid, size_t smem)
+{
+    const int T = h->trafo == KST_TRAFO_IDENTITY ? 0 : h->t;
+#define KST_LAUNCH_T(TV)                                                                        \
+    case TV:                                                                                    \
+        if (TV <= MF::R) {                                                                      \
+            if (h->reg) {                                                                       \
+                KST_OPT_IN((k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false, true>));       \
+                k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false, true><<<grid, KST_NT, smem, h->stream>>>(prm); \
+            } else {                                                                            \
+                KST_OPT_IN((k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false>));             \
+                k_objective<MF, CRIT, (TV <= MF::R ? TV : 0), false><<<grid, KST_NT, smem, h->stream>>>(prm); \
+            }                                                                                   \
+            return KST_OK;                                                                      \
+        }                                                                                       \
+        break;
+    if (CRIT == 0 && T == 0 && h->uniform_w && !h->reg) {
+        KST_OPT_IN((k_objective<MF, 0, 0, true>));
+        k_objective<MF, 0, 0, true><<<grid, KST_NT, smem, h->stream>>>(prm);
+        return KST_OK;
+    }
+    switch (T) {
+        KST_LAUNCH_T(0)
+        KST_LAUNCH_T(1)
+        KST_LAUNCH_T(2)
+        KST_LAUNCH_T(3)
+        KST_LAUNCH_T(4)
+        KST_LAUNCH_T(5)
+    }
+#undef KST_LAUNCH_T
+    kst_set_error("unsupported transformation dimension t = %d for r = %d", T, MF::R);
+    return KST_EINVAL;
+}
+
+// criterion dispatch for one model family; instantiated explicitly in kst_obj_inst_*.cu
+template <class MF>
+int kst_obj_launch(kst_problem *h, const KstObjParams &prm, dim3 grid, int K)
+{
+    const size_t smem = KstTile<MF>::bytes(K * h->m);
+    return h->crit == KST_CRIT_D   ? launch_obj_t<MF, 0>(h, prm, grid, smem)
+           : h->crit == KST_CRIT_A ? launch_obj_t<MF, 1>(h, prm, grid, smem)
+                                   : launch_obj_t<MF, 2>(h, prm, grid, smem);
+}
+#define KST_OBJ_FAMILIES(X) \
+    X(KstEmax) X(KstSigEmax) X(KstTpc) X(KstVu) X(KstDtr) X(KstLinLogReg<1>) X(KstLinLogReg<2>) X(KstLinLogReg<3>) X(KstSinLogReg)
+
