@@ -283,6 +283,92 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
     wtrB[j] = pw[j] * (trB - trAR);
 }
 
+// Draw loop of k_gateaux_eval for one direction (thread): sum over the CTA's draws [j0, j1) of
+// pw_j * sum_rows omega gt' At_j gt.  NL >= 0: exactly NL rows, constants in registers (lsq, lpc), no branch inside
+// the loop.  NL = -1: m rows with constants in shared memory (s_rows), rows outside live_mask skipped.
+template <class MF, int NL>
+__device__ __forceinline__ double kst_gd_draws(const double *__restrict__ dc, const double *__restrict__ pw,
+                                               const double *__restrict__ gA, size_t ld, int64_t j0, int64_t j1,
+                                               double *s_draw, const double *s_rows, int m, unsigned live_mask,
+                                               const double *lsq, const double (*lpc)[MF::NPC], double sw_triv,
+                                               KstTab tab)
+{
+    constexpr int R = MF::R, RW = KstRowW<MF>::RW, NP = KstPacked<R>::N, NS = MF::NDC + NP, NSP = (NS + 1) / 2 * 2;
+    double acc = 0.0;
+    for (int64_t jb = j0; jb < j1; jb += KST_GD_CHUNK) {
+        const int nj = (int)min((int64_t)KST_GD_CHUNK, j1 - jb);
+        __syncthreads();
+        for (int e = threadIdx.x; e < NSP * KST_GD_CHUNK; e += KST_GD_NT) {
+            const int c = e / KST_GD_CHUNK, jj = e % KST_GD_CHUNK;  // consecutive threads read consecutive draws
+            double v = 0.0;
+            if (jj < nj && c < NS) {
+                const int64_t j = jb + jj;
+                if (c < MF::NDC) {
+                    v = dc[(size_t)c * ld + j];
+                } else {
+                    // packed upper of pw_j * At_j, off-diagonals doubled
+                    int q = c - MF::NDC, a = 0;
+                    while (q >= R - a) { q -= R - a; a++; }
+                    const int b = a + q;
+                    v = pw[j] * gA[(size_t)(a * R + b) * ld + j] * (a == b ? 1.0 : 2.0);
+                }
+            }
+            s_draw[jj * NSP + c] = v;
+        }
+        __syncthreads();
+#pragma unroll kGdUnroll
+        for (int jj = 0; jj < nj; jj++) {
+            double dv[NSP];
+#pragma unroll
+            for (int c = 0; c < NSP; c += 2) {
+                const double2 v = *reinterpret_cast<const double2 *>(s_draw + jj * NSP + c);
+                dv[c] = v.x;
+                dv[c + 1] = v.y;
+            }
+            const double *dcv = dv, *Ap = dv + MF::NDC;
+            double qsum = 0.0;
+            if (NL >= 0) {
+#pragma unroll
+                for (int i = 0; i < (NL > 0 ? NL : 0); i++) {
+                    double gv[R];
+                    MF::row(lpc[i], dcv, lsq[i], gv, tab);  // weighted row: gv' A gv = omega * gt' A gt
+                    double q = 0.0;
+#pragma unroll
+                    for (int a = 0; a < R; a++) {
+                        double s = 0.0;
+#pragma unroll
+                        for (int b = a; b < R; b++) s = fma(Ap[kst_pidx<R>(a, b)], gv[b], s);
+                        q = fma(s, gv[a], q);
+                    }
+                    qsum += q;
+                }
+            } else {
+                for (int i = 0; i < m; i++) {
+                    if (!((live_mask >> i) & 1u)) continue;  // uniform over the CTA
+                    double pc[MF::NPC], gv[R];
+                    const double sq = s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x];
+#pragma unroll
+                    for (int c = 0; c < MF::NPC; c++) pc[c] = s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x];
+                    MF::row(pc, dcv, sq, gv, tab);
+                    double q = 0.0;
+#pragma unroll
+                    for (int a = 0; a < R; a++) {
+                        double s = 0.0;
+#pragma unroll
+                        for (int b = a; b < R; b++) s = fma(Ap[kst_pidx<R>(a, b)], gv[b], s);
+                        q = fma(s, gv[a], q);
+                    }
+                    qsum += q;
+                }
+            }
+            constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
+            if (MF::CONST_COL >= 0) qsum = fma(sw_triv, Ap[kst_pidx<R>(cc, cc)], qsum);
+            acc += qsum;
+        }
+    }
+    return acc;
+}
+
 // One thread per direction; draws staged in shared memory.
 // MR > 0: the unit has exactly MR rows and their constants stay in registers; MR = 0: any unit length, row
 // constants in shared memory.  A draw's constants (NDC hoisted constants + packed pw_j At_j) are stored
@@ -346,77 +432,40 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
     const int64_t per = (N + gridDim.y - 1) / gridDim.y;
     const int64_t j0 = per * blockIdx.y, j1 = min(N, j0 + per);
     double acc = 0.0;
-    for (int64_t jb = j0; jb < j1; jb += KST_GD_CHUNK) {
-        const int nj = (int)min((int64_t)KST_GD_CHUNK, j1 - jb);
-        __syncthreads();
-        for (int e = threadIdx.x; e < NSP * KST_GD_CHUNK; e += KST_GD_NT) {
-            const int c = e / KST_GD_CHUNK, jj = e % KST_GD_CHUNK;  // consecutive threads read consecutive draws
-            double v = 0.0;
-            if (jj < nj && c < NS) {
-                const int64_t j = jb + jj;
-                if (c < MF::NDC) {
-                    v = dc[(size_t)c * ld + j];
-                } else {
-                    // packed upper of pw_j * At_j, off-diagonals doubled
-                    int q = c - MF::NDC, a = 0;
-                    while (q >= R - a) { q -= R - a; a++; }
-                    const int b = a + q;
-                    v = pw[j] * gA[(size_t)(a * R + b) * ld + j] * (a == b ? 1.0 : 2.0);
-                }
-            }
-            s_draw[jj * NSP + c] = v;
+    if (MR > 0) {
+        // Compact the rows that are live for at least one direction of the CTA to the front (uniform over the CTA),
+        // then run the draw loop specialised on their number: with no per-row branch inside it, the compiler
+        // interleaves the rows of the kGdUnroll draws evaluated side by side.
+        double lsq[MRR], lpc[MRR][MF::NPC];
+        int nl = 0;
+#pragma unroll
+        for (int i = 0; i < MRR; i++) {
+            lsq[i] = 0.0;
+#pragma unroll
+            for (int c = 0; c < MF::NPC; c++) lpc[i][c] = 1.0;
         }
-        __syncthreads();
-#pragma unroll kGdUnroll
-        for (int jj = 0; jj < nj; jj++) {
-            double dv[NSP];
 #pragma unroll
-            for (int c = 0; c < NSP; c += 2) {
-                const double2 v = *reinterpret_cast<const double2 *>(s_draw + jj * NSP + c);
-                dv[c] = v.x;
-                dv[c + 1] = v.y;
-            }
-            const double *dcv = dv, *Ap = dv + MF::NDC;
-            double qsum = 0.0;
+        for (int i = 0; i < MRR; i++) {
+            if ((live_mask >> i) & 1u) {
 #pragma unroll
-            for (int i = 0; i < (MR > 0 ? MR : 1); i++) {
-                if (MR == 0) break;
-                if (!((live_mask >> i) & 1u)) continue;  // uniform over the CTA
-                double gv[R];
-                MF::row(rpc[i], dcv, rsq[i], gv, tab);  // weighted row: gv' A gv = omega * gt' A gt
-                double q = 0.0;
+                for (int o = 0; o < MRR; o++)
+                    if (o == nl) {
+                        lsq[o] = rsq[i];
 #pragma unroll
-                for (int a = 0; a < R; a++) {
-                    double s = 0.0;
-#pragma unroll
-                    for (int b = a; b < R; b++) s = fma(Ap[kst_pidx<R>(a, b)], gv[b], s);
-                    q = fma(s, gv[a], q);
-                }
-                qsum += q;
-            }
-            if (MR == 0) {
-                for (int i = 0; i < m; i++) {
-                    if (!((live_mask >> i) & 1u)) continue;  // uniform over the CTA
-                    double pc[MF::NPC], gv[R];
-                    const double sq = s_rows[(size_t)(i * RW) * KST_GD_NT + threadIdx.x];
-#pragma unroll
-                    for (int c = 0; c < MF::NPC; c++) pc[c] = s_rows[(size_t)(i * RW + 1 + c) * KST_GD_NT + threadIdx.x];
-                    MF::row(pc, dcv, sq, gv, tab);
-                    double q = 0.0;
-#pragma unroll
-                    for (int a = 0; a < R; a++) {
-                        double s = 0.0;
-#pragma unroll
-                        for (int b = a; b < R; b++) s = fma(Ap[kst_pidx<R>(a, b)], gv[b], s);
-                        q = fma(s, gv[a], q);
+                        for (int c = 0; c < MF::NPC; c++) lpc[o][c] = rpc[i][c];
                     }
-                    qsum += q;
-                }
+                nl++;
             }
-            constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
-            if (MF::CONST_COL >= 0) qsum = fma(sw_triv, Ap[kst_pidx<R>(cc, cc)], qsum);
-            acc += qsum;
         }
+        switch (nl) {
+        case 0: acc = kst_gd_draws<MF, 0>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        case 1: acc = kst_gd_draws<MF, 1>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        case 2: acc = kst_gd_draws<MF, (MR >= 2 ? 2 : 1)>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        case 3: acc = kst_gd_draws<MF, (MR >= 3 ? 3 : 1)>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        default: acc = kst_gd_draws<MF, (MR >= 4 ? 4 : 1)>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        }
+    } else {
+        acc = kst_gd_draws<MF, -1>(dc, pw, gA, ld, j0, j1, s_draw, s_rows, m, live_mask, rsq, rpc, sw_triv, tab);
     }
     if (live) partials[g * gridDim.y + blockIdx.y] = acc;
 }
