@@ -310,7 +310,7 @@ extern "C" int kst_problem_destroy(kst_problem *h)
     if (h->peer_local) cudaFree(h->peer_local);
     kst_pso_free(h);
     void *ptrs[] = {h->theta, h->pw, h->dc, h->cs, h->aux, h->reg, h->partials, h->stage_pts, h->stage_w, h->stage_fx,
-                    h->gA, h->gtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials};
+                    h->gA, h->gAp, h->gtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);

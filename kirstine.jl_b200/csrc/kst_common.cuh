@@ -20,7 +20,7 @@
 #define KST_TILE_P 8        // particles per CTA tile (objective kernel)
 #endif
 #define KST_GD_NT 128       // threads (= directions) per CTA of the Gateaux kernel
-#define KST_GD_CHUNK 64     // draws staged per shared-memory chunk in the Gateaux kernel
+#define KST_GD_CHUNK 128    // draws staged per shared-memory chunk in the Gateaux kernel (= KST_GD_NT: one draw per thread)
 #define KST_PEER_CAP 16384  // doubles per peer-exchange buffer (larger all-reduces go through NCCL)
 #define KST_PEER_MAX 16     // ranks in one peer-exchange group
 
@@ -103,6 +103,7 @@ struct kst_problem {
 
     // Gateaux constants at the last prepared design: At [r*r][ld] (scaled space), trB [ld]
     double *gA = nullptr, *gtrB = nullptr;
+    double *gAp = nullptr;     // what the evaluation kernel streams: packed upper of pw_j At_j, off-diagonals doubled, [r(r+1)/2][ld]
     int g_ready = 0, g_singular = 0;
     double g_offset = 0.0;     // sum_j pw_j trB_j
     int *d_flag = nullptr;     // device flag word (singular detection)

@@ -73,7 +73,7 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
                                   const double *__restrict__ reg, int64_t N, int crit, int trafo, int t,
                                   const double *__restrict__ pts,
                                   const double *__restrict__ w, int K, KstModelParams mp, double *__restrict__ gA,
-                                  double *__restrict__ gtrB, double *__restrict__ wtrB, int *flag)
+                                  double *__restrict__ gAp, double *__restrict__ gtrB, double *__restrict__ wtrB, int *flag)
 {
     constexpr int R = MF::R, RW = KstRowW<MF>::RW;
     extern __shared__ __align__(16) double smem[];  // rows[K*m][RW], sw, (na, rank)
@@ -272,6 +272,11 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
     for (int a = 0; a < R; a++)
 #pragma unroll
         for (int b = 0; b < R; b++) gA[(size_t)(a * R + b) * ld + j] = At[a][b];
+    // the form k_gateaux_eval streams: pw_j At_j, upper triangle, off-diagonals doubled
+#pragma unroll
+    for (int a = 0; a < R; a++)
+#pragma unroll
+        for (int b = a; b < R; b++) gAp[(size_t)kst_pidx<R>(a, b) * ld + j] = pw[j] * At[a][b] * (a == b ? 1.0 : 2.0);
     gtrB[j] = trB;
     // the direction's matrix is regularised too (src/designproblem.jl:253-254): tr_prod(A, M(delta) + R, :U) adds
     // the direction-independent tr_U[A R], folded into the constant here
@@ -287,35 +292,38 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
 // pw_j * sum_rows omega gt' At_j gt.  NL >= 0: exactly NL rows, constants in registers (lsq, lpc), no branch inside
 // the loop.  NL = -1: m rows with constants in shared memory (s_rows), rows outside live_mask skipped.
 template <class MF, int NL>
-__device__ __forceinline__ double kst_gd_draws(const double *__restrict__ dc, const double *__restrict__ pw,
-                                               const double *__restrict__ gA, size_t ld, int64_t j0, int64_t j1,
+__device__ __forceinline__ double kst_gd_draws(const double *__restrict__ dc, const double *__restrict__ gAp,
+                                               size_t ld, int64_t j0, int64_t j1,
                                                double *s_draw, const double *s_rows, int m, unsigned live_mask,
                                                const double *lsq, const double (*lpc)[MF::NPC], double sw_triv,
                                                KstTab tab)
 {
     constexpr int R = MF::R, RW = KstRowW<MF>::RW, NP = KstPacked<R>::N, NS = MF::NDC + NP, NSP = (NS + 1) / 2 * 2;
+    static_assert(KST_GD_CHUNK == KST_GD_NT, "one staged draw per thread");
     double acc = 0.0;
+    // Software pipeline: the next chunk's constants travel from L2 into registers while the current chunk is being
+    // evaluated out of shared memory, so the only exposed memory latency is the first chunk's.
+    double nxt[NS];
+    {
+        const int64_t j = j0 + threadIdx.x;
+#pragma unroll
+        for (int c = 0; c < NS; c++)
+            nxt[c] = j < j1 ? (c < MF::NDC ? dc[(size_t)c * ld + j] : gAp[(size_t)(c - MF::NDC) * ld + j]) : 0.0;
+    }
     for (int64_t jb = j0; jb < j1; jb += KST_GD_CHUNK) {
         const int nj = (int)min((int64_t)KST_GD_CHUNK, j1 - jb);
+        __syncthreads();  // the previous chunk has been consumed (first pass: the math tables are in place)
+#pragma unroll
+        for (int c = 0; c < NSP; c++) s_draw[threadIdx.x * NSP + c] = c < NS ? nxt[c < NS ? c : 0] : 0.0;
         __syncthreads();
-        for (int e = threadIdx.x; e < NSP * KST_GD_CHUNK; e += KST_GD_NT) {
-            const int c = e / KST_GD_CHUNK, jj = e % KST_GD_CHUNK;  // consecutive threads read consecutive draws
-            double v = 0.0;
-            if (jj < nj && c < NS) {
-                const int64_t j = jb + jj;
-                if (c < MF::NDC) {
-                    v = dc[(size_t)c * ld + j];
-                } else {
-                    // packed upper of pw_j * At_j, off-diagonals doubled
-                    int q = c - MF::NDC, a = 0;
-                    while (q >= R - a) { q -= R - a; a++; }
-                    const int b = a + q;
-                    v = pw[j] * gA[(size_t)(a * R + b) * ld + j] * (a == b ? 1.0 : 2.0);
-                }
+        {
+            const int64_t j = jb + KST_GD_CHUNK + threadIdx.x;
+            if (j < j1) {
+#pragma unroll
+                for (int c = 0; c < NS; c++)
+                    nxt[c] = c < MF::NDC ? dc[(size_t)c * ld + j] : gAp[(size_t)(c - MF::NDC) * ld + j];
             }
-            s_draw[jj * NSP + c] = v;
         }
-        __syncthreads();
 #pragma unroll kGdUnroll
         for (int jj = 0; jj < nj; jj++) {
             double dv[NSP];
@@ -374,8 +382,8 @@ __device__ __forceinline__ double kst_gd_draws(const double *__restrict__ dc, co
 // constants in shared memory.  A draw's constants (NDC hoisted constants + packed pw_j At_j) are stored
 // contiguously and read as 16-byte broadcasts.
 template <class MF, int MR>
-__global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__restrict__ dc, const double *__restrict__ pw,
-                                                            const double *__restrict__ gA, size_t ld, int64_t N,
+__global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__restrict__ dc,
+                                                            const double *__restrict__ gAp, size_t ld, int64_t N,
                                                             const double *__restrict__ dirs, int64_t G,
                                                             KstModelParams mp, double *__restrict__ partials)
 {
@@ -458,14 +466,14 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
             }
         }
         switch (nl) {
-        case 0: acc = kst_gd_draws<MF, 0>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
-        case 1: acc = kst_gd_draws<MF, 1>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
-        case 2: acc = kst_gd_draws<MF, (MR >= 2 ? 2 : 1)>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
-        case 3: acc = kst_gd_draws<MF, (MR >= 3 ? 3 : 1)>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
-        default: acc = kst_gd_draws<MF, (MR >= 4 ? 4 : 1)>(dc, pw, gA, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        case 0: acc = kst_gd_draws<MF, 0>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        case 1: acc = kst_gd_draws<MF, 1>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        case 2: acc = kst_gd_draws<MF, (MR >= 2 ? 2 : 1)>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        case 3: acc = kst_gd_draws<MF, (MR >= 3 ? 3 : 1)>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        default: acc = kst_gd_draws<MF, (MR >= 4 ? 4 : 1)>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
         }
     } else {
-        acc = kst_gd_draws<MF, -1>(dc, pw, gA, ld, j0, j1, s_draw, s_rows, m, live_mask, rsq, rpc, sw_triv, tab);
+        acc = kst_gd_draws<MF, -1>(dc, gAp, ld, j0, j1, s_draw, s_rows, m, live_mask, rsq, rpc, sw_triv, tab);
     }
     if (live) partials[g * gridDim.y + blockIdx.y] = acc;
 }
@@ -493,6 +501,7 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
     }
     if (!h->gA) {
         KST_CUDA(cudaMalloc(&h->gA, sizeof(double) * h->r * h->r * h->ld));
+        KST_CUDA(cudaMalloc(&h->gAp, sizeof(double) * (h->r * (h->r + 1) / 2) * h->ld));
         KST_CUDA(cudaMalloc(&h->gtrB, sizeof(double) * h->ld));
     }
     double *wtrB = nullptr;
@@ -503,7 +512,7 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
     KST_MODEL_SWITCH(h->model_id, {
         const size_t smem = sizeof(double) * ((size_t)K * h->m * KstRowW<MF>::RW + 2);
         k_gateaux_prepare<MF><<<nb, nt, smem, h->stream>>>(h->dc, h->cs, h->aux, h->pw, h->ld, h->reg, h->N, h->crit, h->trafo,
-                                                           h->t, d_pts, d_w, K, h->mp, h->gA, h->gtrB, wtrB, h->d_flag);
+                                                           h->t, d_pts, d_w, K, h->mp, h->gA, h->gAp, h->gtrB, wtrB, h->d_flag);
     });
     KST_CUDA(cudaGetLastError());
     int rc = kst_sum_fixed(h, wtrB, h->N, &h->g_offset);
@@ -517,31 +526,67 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
     return KST_OK;
 }
 
+// Draw split of the evaluation grid: gblocks CTAs of KST_GD_NT directions each, times n_split draw ranges.  All CTAs
+// take the same time, so the aim is one wave that fills every SM's resident-CTA slots as evenly as possible (or a
+// whole number of waves when there are more direction blocks than slots).
+static int64_t kst_gd_split(const kst_problem *h, int64_t gblocks, int resident_per_sm)
+{
+    const int64_t max_split = (h->N + KST_GD_CHUNK - 1) / KST_GD_CHUNK;
+    const int64_t cap = (int64_t)h->sm_count * (resident_per_sm > 0 ? resident_per_sm : 1);
+    int64_t best = 1;
+    double best_waste = 1e30;
+    const int64_t hi = (cap + gblocks - 1) / gblocks;  // smallest split that reaches a full wave
+    for (int64_t ns = 1; ns <= hi && ns <= max_split; ns++) {
+        const int64_t tot = ns * gblocks, waves = (tot + cap - 1) / cap;
+        // idle slots in the last wave, plus a mild preference for more CTAs (latency hiding) at equal balance
+        const double waste = (double)(waves * cap - tot) / (double)(waves * cap);
+        if (waste < best_waste - 1e-9) { best_waste = waste; best = ns; }
+    }
+    if (best > 65535) best = 65535;
+    return best;
+}
+
 template <class MF, int MR>
-static int launch_gd(kst_problem *h, dim3 grid, int64_t G, const double *d_dirs, size_t smem)
+static int launch_gd(kst_problem *h, int64_t G, const double *d_dirs, size_t smem, int *n_split_out)
 {
     // vector units with many rows: opt in to a large dynamic shared-memory window (the static math tables count
     // towards the 48 KB a kernel gets without asking)
     if (smem + sizeof(double) * KST_MATH_SMEM > 48 * 1024)
         KST_CUDA(cudaFuncSetAttribute(k_gateaux_eval<MF, MR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_gateaux_eval<MF, MR><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->pw, h->gA, h->ld, h->N, d_dirs, G, h->mp,
+    int resident = 0;
+    KST_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_gateaux_eval<MF, MR>, KST_GD_NT, smem));
+    const int64_t gblocks = (G + KST_GD_NT - 1) / KST_GD_NT;
+    const int64_t n_split = kst_gd_split(h, gblocks, resident);
+    const size_t need = (size_t)G * n_split;
+    if (need > h->gd_partials_cap) {
+        if (h->gd_partials) KST_CUDA(cudaFree(h->gd_partials));
+        h->gd_partials = nullptr;
+        h->gd_partials_cap = 0;
+        KST_CUDA(cudaMalloc(&h->gd_partials, sizeof(double) * need));
+        h->gd_partials_cap = need;
+    }
+    *n_split_out = (int)n_split;
+    if (h->g_singular) return KST_OK;  // the finishing kernel fills NaN
+    const dim3 grid((unsigned)gblocks, (unsigned)n_split);
+    k_gateaux_eval<MF, MR><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->gAp, h->ld, h->N, d_dirs, G, h->mp,
                                                                  h->gd_partials);
+    KST_CUDA(cudaGetLastError());
     return KST_OK;
 }
 
 template <class MF>
-static int launch_gd_model(kst_problem *h, dim3 grid, int64_t G, const double *d_dirs)
+static int launch_gd_model(kst_problem *h, int64_t G, const double *d_dirs, int *n_split)
 {
     constexpr int NSP = (MF::NDC + KstPacked<MF::R>::N + 1) / 2 * 2;
     const bool in_regs = h->m <= 4;
     const size_t smem =
         sizeof(double) * ((size_t)NSP * KST_GD_CHUNK + (in_regs ? 0 : (size_t)h->m * KstRowW<MF>::RW * KST_GD_NT));
     switch (in_regs ? h->m : 0) {
-    case 1: return launch_gd<MF, 1>(h, grid, G, d_dirs, smem);
-    case 2: return launch_gd<MF, 2>(h, grid, G, d_dirs, smem);
-    case 3: return launch_gd<MF, 3>(h, grid, G, d_dirs, smem);
-    case 4: return launch_gd<MF, 4>(h, grid, G, d_dirs, smem);
-    default: return launch_gd<MF, 0>(h, grid, G, d_dirs, smem);
+    case 1: return launch_gd<MF, 1>(h, G, d_dirs, smem, n_split);
+    case 2: return launch_gd<MF, 2>(h, G, d_dirs, smem, n_split);
+    case 3: return launch_gd<MF, 3>(h, G, d_dirs, smem, n_split);
+    case 4: return launch_gd<MF, 4>(h, G, d_dirs, smem, n_split);
+    default: return launch_gd<MF, 0>(h, G, d_dirs, smem, n_split);
     }
 }
 
@@ -555,27 +600,11 @@ int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, dou
         kst_set_error("gateaux_eval: need G >= 1");
         return KST_EINVAL;
     }
-    const int64_t gblocks = (G + KST_GD_NT - 1) / KST_GD_NT;
-    const int64_t max_split = (h->N + KST_GD_CHUNK - 1) / KST_GD_CHUNK;
-    int64_t n_split = (4LL * h->sm_count + gblocks - 1) / gblocks;
-    if (n_split > max_split) n_split = max_split;
-    if (n_split < 1) n_split = 1;
-    if (n_split > 65535) n_split = 65535;
-    const size_t need = (size_t)G * n_split;
-    if (need > h->gd_partials_cap) {
-        if (h->gd_partials) KST_CUDA(cudaFree(h->gd_partials));
-        h->gd_partials = nullptr;
-        KST_CUDA(cudaMalloc(&h->gd_partials, sizeof(double) * need));
-        h->gd_partials_cap = need;
-    }
-    const dim3 grid((unsigned)gblocks, (unsigned)n_split);
-    if (!h->g_singular) {
-        int rc = KST_OK;
-        KST_MODEL_SWITCH(h->model_id, rc = launch_gd_model<MF>(h, grid, G, d_dirs));
-        if (rc) return rc;
-        KST_CUDA(cudaGetLastError());
-    }
-    k_gd_finish<<<(unsigned)((G + 127) / 128), 128, 0, h->stream>>>(h->gd_partials, (int)n_split, h->g_offset,
+    int n_split = 1;
+    int rc = KST_OK;
+    KST_MODEL_SWITCH(h->model_id, rc = launch_gd_model<MF>(h, G, d_dirs, &n_split));
+    if (rc) return rc;
+    k_gd_finish<<<(unsigned)((G + 127) / 128), 128, 0, h->stream>>>(h->gd_partials, n_split, h->g_offset,
                                                                    h->g_singular, d_out, G);
     KST_CUDA(cudaGetLastError());
     return KST_OK;
