@@ -163,7 +163,8 @@ int kst_objective_grid(const kst_problem *h, int S, int *n_blk, int *tile_p)
     while (tp > 1 && (int64_t)((S + tp - 1) / tp) * max_chunks < cap) tp >>= 1;
     *tile_p = tp;
     const int tiles = (S + tp - 1) / tp;
-    // aim for >= 8 waves, then pick the draw split whose last wave is fullest
+    // Many short CTAs beat few long ones (measured on cfg 3 and cfg 5: the ragged end of the last wave costs more
+    // than the per-CTA prologue): aim for >= 8 waves and pick the draw split whose last wave is fullest ...
     int64_t lo = (8LL * cap + tiles - 1) / tiles;
     if (lo < 1) lo = 1;
     int64_t best = lo;
@@ -174,6 +175,12 @@ int kst_objective_grid(const kst_problem *h, int S, int *n_blk, int *tile_p)
         const double waste = (double)(waves * cap - tot) / (double)tot;
         if (waste < best_waste - 1e-12) { best_waste = waste; best = nb; }
     }
+    // ... but not below ~4 draws per thread, where the prologue (math tables into shared memory, particle tile)
+    // starts to dominate (measured on cfg 2), unless that would leave SMs without a CTA
+    int64_t nb_dpt = h->N / (KST_NT * 4);
+    const int64_t fill = cap / tiles > 0 ? cap / tiles : 1;  // the split that just fits one wave
+    if (nb_dpt < fill) nb_dpt = fill;
+    if (best > nb_dpt) best = nb_dpt;
     if (best > max_chunks) best = max_chunks;
     if (best < 1) best = 1;
     if (best > 65535) best = 65535;
