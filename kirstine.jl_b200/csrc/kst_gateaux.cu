@@ -14,8 +14,9 @@
 // Evaluation mapping: one thread per direction (no cross-thread reduction at all), draws are
 // staged chunk-wise in shared memory and read as broadcasts, so the per-draw constants
 // (8*(NDC + r(r+1)/2) bytes) are loaded once per CTA of KST_GD_NT directions instead of once
-// per (direction, draw) pair.  The draw range is split over gridDim.y for small G; partial sums
-// are combined in fixed order.
+// per (direction, draw) pair; the next chunk is fetched into registers while the current one is
+// evaluated.  The draw range is split over gridDim.y so that one wave of CTAs fills the GPU (split
+// taken from the kernel's occupancy); partial sums are combined in fixed order.
 #include "kst_common.cuh"
 #include "kst_linalg.cuh"
 
@@ -24,10 +25,6 @@
 #endif
 // draws evaluated side by side per thread in k_gateaux_eval (independent FP64 chains for the scheduler)
 constexpr int kGdUnroll = KST_GD_UNROLL;
-
-#ifndef KST_GD_UNROLL
-#define KST_GD_UNROLL 4
-#endif
 
 // doubles per row in shared memory: sqrt(omega), pc...
 template <class MF>
