@@ -302,7 +302,10 @@ def main():
         threads = os.cpu_count() or 1
         sp, sd = 256, 1_000_000  # about 10 s on 16 host threads
         rate, secs = cpu_port_rate(theta, pts, w, sp, sd, threads)
+        # the stock reference runs on one thread: the same port on one thread, on 1/16 of the sample
+        rate1, secs1 = cpu_port_rate(theta, pts, w, max(1, sp // 16), sd, 1)
         cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port", "seconds": secs,
+               "single_thread": {"value": rate1, "seconds": secs1, "sample": "%d particles x %d draws" % (max(1, sp // 16), sd)},
                "sample": "%d particles x %d draws of the cfg5 workload, oracle/kirstine_oracle.c with OpenMP over "
                          "particles (the Julia reference is single-threaded and not installable here)" % (sp, sd)}
 
