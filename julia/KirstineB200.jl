@@ -42,6 +42,25 @@ cp_id(::VUMod) = 1
 crit_id(::DCriterion) = 0
 crit_id(::ACriterion) = 1
 
+# ---- the reference's vignette extensions, registered as well ----------------------------------------
+# docs/src/extend-criterion.md: det^(1/t)
+struct DexpCriterion <: Kirstine.DesignCriterion end
+crit_id(::DexpCriterion) = 2
+# docs/src/extend-approximation.md: informationmatrix! adds R; sent to the engine once per handle
+struct RegularizedFisherMatrix <: Kirstine.NormalApproximation
+    R::Matrix{Float64}
+end
+# docs/src/extend-model.md: logistic regression has its own average_fishermatrix!, so it is a Model, not a
+# NonlinearRegression; the handle/evaluator methods below dispatch on the union of both registered supertypes
+abstract type RegisteredLogistic <: Kirstine.Model end
+struct LinLogReg <: RegisteredLogistic; dim_covariate::Int64; end   # theta = (beta_0, beta_rest...), d = 1..3
+struct SinLogReg <: RegisteredLogistic end                          # theta = (a, b, c)
+model_id(::LinLogReg) = 6; model_id(::SinLogReg) = 7
+model_params(::RegisteredLogistic) = [0.0]                          # ignored by the engine
+Kirstine.unit_length(::RegisteredLogistic) = 1
+cp_id(::RegisteredLogistic) = 0
+const Registered = Union{RegisteredModel,RegisteredLogistic}
+
 struct EngineError <: Exception
     code::Cint
     msg::String
@@ -58,7 +77,7 @@ end
 
 const HANDLES = IdDict{Any,Handle}()
 
-function handle(dp::DesignProblem{<:Any,<:Any,<:RegisteredModel}; device = 0)
+function handle(dp::DesignProblem{<:Any,<:Any,<:Registered}; device = 0)
     get!(HANDLES, dp) do
         pk = prior_knowledge(dp)
         r = parameter_dimension(pk)
@@ -81,6 +100,10 @@ function handle(dp::DesignProblem{<:Any,<:Any,<:RegisteredModel}; device = 0)
             isdelta ? dt : C_NULL, lb, ub, device, out))
         h = Handle(out[])
         finalizer(x -> ccall((:kst_problem_destroy, LIB), Cint, (Ptr{Cvoid},), x.ptr), h)
+        na = Kirstine.normal_approximation(dp)
+        if na isa RegularizedFisherMatrix   # Matrix{Float64} is column-major, as the ABI wants
+            check(ccall((:kst_problem_set_regularization, LIB), Cint, (Ptr{Cvoid}, Ptr{Cdouble}), h.ptr, na.R))
+        end
         h
     end
 end
@@ -97,10 +120,10 @@ function objective_batch(dp, ds::AbstractVector{DesignMeasure})
     return fx
 end
 
-objective(d::DesignMeasure, dp::DesignProblem{<:Any,<:Any,<:RegisteredModel}) = objective_batch(dp, [d])[1]
+objective(d::DesignMeasure, dp::DesignProblem{<:Any,<:Any,<:Registered}) = objective_batch(dp, [d])[1]
 
 function gateauxderivative(at::DesignMeasure, directions::AbstractArray{DesignMeasure},
-                           dp::DesignProblem{<:Any,<:Any,<:RegisteredModel})
+                           dp::DesignProblem{<:Any,<:Any,<:Registered})
     any(d -> numpoints(d) != 1, directions) &&
         throw(ErrorException("derivative only implemented for one-point directions"))
     isinf(objective(at, dp)) && return fill(NaN, size(directions))
@@ -116,7 +139,7 @@ function gateauxderivative(at::DesignMeasure, directions::AbstractArray{DesignMe
 end
 
 # ---- whole PSO on the device ------------------------------------------------------------------------
-function solve_with(dp::DesignProblem{<:Any,<:Any,<:RegisteredModel}, strategy::DirectMaximization{Pso},
+function solve_with(dp::DesignProblem{<:Any,<:Any,<:Registered}, strategy::DirectMaximization{Pso},
                     trace_state::Bool)
     constraints = Kirstine.DesignConstraints(strategy.prototype, region(dp), strategy.fixedweights,
                                              strategy.fixedpoints)
