@@ -87,6 +87,7 @@ struct kst_problem {
     double *cs = nullptr;      // r   column scales
     double *aux = nullptr;     // A/Identity: r (1/cs^2); DeltaMethod: t*r (DT/cs); else unused
     int n_aux = 0;
+    double dcmax[8] = {};      // max_j |dc[c][j]| over this handle's draws (NaN / Inf poison the entry)
     // regularised normal approximation (kst_problem_set_regularization): Rt_j = D_j^-1 R D_j^-1, packed upper
     // [r(r+1)/2][ld], added to every Mt_j; nullptr = FisherMatrix
     double *reg = nullptr;

@@ -65,6 +65,9 @@ struct KstEmax {
         return z[0] == 0.0;
     }
     __device__ static void post_row(double *pc, double sw) { pc[1] = sw * pc[0]; }
+    static constexpr bool FAST_EXP = false;
+    __device__ static double arg_bound(const double *, const double *) { return 0.0; }
+    template <bool CLAMP = true>
     __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab)
     {
         const double rho = kst_rcp(pc[0] + dc[0]);
@@ -101,10 +104,14 @@ struct KstSigEmax {
         return z[0] == 0.0;
     }
     __device__ static void post_row(double *, double) {}
+    // upper bound of |q| over all draws for a row, from the per-problem maxima of |dc| (see KstObjParams::dcmax)
+    static constexpr bool FAST_EXP = true;
+    __device__ static double arg_bound(const double *pc, const double *dcmax) { return fma(dcmax[0], fabs(pc[0]), dcmax[1]); }
+    template <bool CLAMP = true>
     __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
         const double q = fma(-dc[0], pc[0], dc[1]);
-        const double e = kst_exp<KST_EXP_RED>(q, tab);
+        const double e = kst_exp<KST_EXP_RED, CLAMP>(q, tab);
         const double a = kst_rcp(1.0 + e);
         const double sa = sw * a;
 #if KST_SU_FMA
@@ -143,10 +150,13 @@ struct KstTpc {
         return z[0] == 0.0;
     }
     __device__ static void post_row(double *pc, double sw) { pc[1] = sw * pc[0]; }
+    static constexpr bool FAST_EXP = true;
+    __device__ static double arg_bound(const double *pc, const double *dcmax) { return fmax(dcmax[0], dcmax[1]) * fabs(pc[0]); }
+    template <bool CLAMP = true>
     __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
-        const double A = kst_exp<KST_EXP_RED>(dc[0] * pc[0], tab);
-        const double E = kst_exp<KST_EXP_RED>(dc[1] * pc[0], tab);
+        const double A = kst_exp<KST_EXP_RED, CLAMP>(dc[0] * pc[0], tab);
+        const double E = kst_exp<KST_EXP_RED, CLAMP>(dc[1] * pc[0], tab);
         g[0] = pc[1] * A;  // sw t A
         g[1] = pc[1] * E;
         g[2] = sw * (E - A);
@@ -226,11 +236,14 @@ struct KstDtr {
         return dose == 0.0 || t == 0.0;
     }
     __device__ static void post_row(double *pc, double sw) { pc[2] = sw * pc[1]; }
+    static constexpr bool FAST_EXP = true;
+    __device__ static double arg_bound(const double *pc, const double *dcmax) { return fmax(dcmax[0], dcmax[1]) * fabs(pc[0]); }
+    template <bool CLAMP = true>
     __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
         const double t = pc[0];
-        const double A = kst_exp<KST_EXP_RED>(dc[0] * t, tab);
-        const double B = kst_exp<KST_EXP_RED>(dc[1] * t, tab);
+        const double A = kst_exp<KST_EXP_RED, CLAMP>(dc[0] * t, tab);
+        const double B = kst_exp<KST_EXP_RED, CLAMP>(dc[1] * t, tab);
         const double C = B - A;
         const double w = kst_rcp(fma(pc[1] * C, dc[2], dc[6]));  // 1 / (dose C a - rd ec50)
         const double sdw = pc[2] * w;                             // sw dose w
@@ -275,6 +288,9 @@ struct KstLinLogReg {
         return false;
     }
     __device__ static void post_row(double *, double) {}
+    static constexpr bool FAST_EXP = false;
+    __device__ static double arg_bound(const double *, const double *) { return 0.0; }
+    template <bool CLAMP = true>
     __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
         double q = dc[0];  // -eta / 2
@@ -310,6 +326,9 @@ struct KstSinLogReg {
         return false;
     }
     __device__ static void post_row(double *, double) {}
+    static constexpr bool FAST_EXP = false;
+    __device__ static double arg_bound(const double *, const double *) { return 0.0; }
+    template <bool CLAMP = true>
     __device__ __forceinline__ static void row(const double *pc, const double *dc, double sw, double *g, KstTab tab)
     {
         const double u = pc[0] - dc[1];

@@ -11,6 +11,8 @@
 // matrix, its LDL' factor and everything after live in FP64 registers.  Per particle one
 // fixed-order block reduction; per-CTA partial sums go to scratch [S][n_blk] and are summed in
 // fixed order by k_obj_finish, so results are bit-reproducible run to run.
+#include <string.h>
+
 #include <mutex>
 
 #include "kst_objective_kernel.cuh"
@@ -103,6 +105,25 @@ __global__ void k_infomatrix(const double *dc, const double *cs, const double *r
         }
 }
 
+// max_j |x[c][j]| for the rows c of an [rows][ld] array, as the bit pattern of the absolute value (monotone for
+// non-negative doubles; a NaN sorts above Inf and so poisons the result, which is what the caller wants)
+__global__ void k_absmax(const double *__restrict__ x, int rows, size_t ld, int64_t n, unsigned long long *out)
+{
+    for (int c = 0; c < rows; c++) {
+        unsigned long long m = 0;
+        for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+            const unsigned long long b = (unsigned long long)__double_as_longlong(x[(size_t)c * ld + j]) & 0x7fffffffffffffffull;
+            m = b > m ? b : m;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long t = __shfl_down_sync(0xffffffffu, m, o);
+            m = t > m ? t : m;
+        }
+        if ((threadIdx.x & 31) == 0 && m) atomicMax(out + c, m);
+    }
+}
+
 // Deterministic sum of n doubles: 1024 threads take strided slices, then a fixed tree.
 __global__ void k_sum_fixed(const double *__restrict__ x, int64_t n, double *__restrict__ out)
 {
@@ -147,7 +168,23 @@ int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const doubl
     KST_CUDA(cudaGetLastError());
     int rc = kst_sum_fixed(h, woff, h->N, &h->offset);
     cudaFree(woff);
-    return rc;
+    if (rc) return rc;
+    // per-problem maxima of the hoisted constants (KstObjParams::dcmax)
+    int ndc = 0;
+    KST_MODEL_SWITCH(h->model_id, ndc = MF::NDC);
+    unsigned long long *d_max = nullptr, bits[8] = {};
+    KST_CUDA(cudaMalloc(&d_max, sizeof(bits)));
+    cudaError_t e = cudaMemsetAsync(d_max, 0, sizeof(bits), h->stream);
+    if (e == cudaSuccess) {
+        k_absmax<<<h->sm_count * 4, 256, 0, h->stream>>>(h->dc, ndc, h->ld, h->N, d_max);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(bits, d_max, sizeof(bits), cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(d_max);
+    if (e != cudaSuccess) { kst_set_error("prep_draws: %s", cudaGetErrorString(e)); return KST_ECUDA; }
+    for (int c = 0; c < 8; c++) memcpy(&h->dcmax[c], &bits[c], sizeof(double));
+    return KST_OK;
 }
 
 // Grid of the evaluation kernel: tiles of *tile_p particles (gridDim.y) x n_blk draw splits (gridDim.x).
@@ -205,6 +242,7 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
     KstObjParams prm;
     prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.reg = h->reg; prm.ld = h->ld; prm.N = h->N;
     prm.pts = d_pts; prm.w = d_w; prm.S = S; prm.K = K; prm.partials = h->partials; prm.mp = h->mp; prm.w_uniform = h->w_uniform; prm.tile_p = tile_p;
+    for (int c = 0; c < 8; c++) prm.dcmax[c] = h->dcmax[c];
     const dim3 grid(n_blk, tiles);
     if (h->prof_on) {
         cudaEvent_t e0, e1;
@@ -313,6 +351,7 @@ extern "C" int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const d
     KstObjParams prm;
     prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.reg = h->reg; prm.ld = h->ld; prm.N = h->N;
     prm.pts = d_points; prm.w = d_weights; prm.S = S; prm.K = K; prm.partials = scratch; prm.mp = h->mp; prm.w_uniform = h->w_uniform; prm.tile_p = tile_p;
+    for (int c = 0; c < 8; c++) prm.dcmax[c] = h->dcmax[c];
     const dim3 grid(n_blk, tiles);
     KST_MODEL_SWITCH(h->model_id, rc = kst_obj_launch<MF>(h, prm, grid, K));
     if (rc) return rc;

@@ -22,6 +22,8 @@ struct KstObjParams {
     KstModelParams mp;
     double w_uniform;       // the common prior weight when all weights are equal (UNI kernels), else unused
     int tile_p;             // particles per CTA, 1..KST_TILE_P (small problems use small tiles to fill the SMs)
+    double dcmax[8];        // max_j |dc[c][j]| per hoisted constant (Inf / NaN when a draw is not finite): lets a
+                            // particle prove that its exp arguments stay inside the exponent range (MF::arg_bound)
 };
 
 // ------------------------------------------------------------------------------------------
@@ -39,10 +41,12 @@ struct KstTile {
     __device__ static int *nact(double *s, int rows_max) { return (int *)(wsum(s, rows_max) + KST_TILE_P * (KST_NT / 32)); }
     // upper bound on rank(Mt): below R the design is singular whatever the rounding does
     __device__ static int *rank(double *s, int rows_max) { return nact(s, rows_max) + KST_TILE_P; }
+    // 1 when every exp argument of the particle is provably within +-700 for every draw (no exponent clamp needed)
+    __device__ static int *safe(double *s, int rows_max) { return rank(s, rows_max) + KST_TILE_P; }
     __host__ static size_t bytes(int rows_max)
     {
         return sizeof(double) * ((size_t)KST_TILE_P * rows_max * RW + 2 * KST_TILE_P + KST_TILE_P * (KST_NT / 32)) +
-               sizeof(int) * 2 * KST_TILE_P;
+               sizeof(int) * 3 * KST_TILE_P;
     }
 };
 
@@ -52,7 +56,8 @@ struct KstTile {
 template <class MF>
 __device__ __forceinline__ void kst_build_tile(double *smem, const double *__restrict__ pts,
                                                const double *__restrict__ w, int p0, int S, int K,
-                                               const KstModelParams &mp, int tile_p = KST_TILE_P)
+                                               const KstModelParams &mp, int tile_p = KST_TILE_P,
+                                               const double *dcmax = nullptr)
 {
     const int rows_max = K * mp.m;
     constexpr int RW = KstTile<MF>::RW;
@@ -60,7 +65,7 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
         const int p = p0 + threadIdx.x;
         double *rows = KstTile<MF>::rows(smem) + (size_t)threadIdx.x * rows_max * RW;
         int na = 0, ntriv = 0;
-        double sw = 0.0;
+        double sw = 0.0, bound = 0.0;
         if (p < S) {
             for (int k = 0; k < K; k++) {
                 const double *z = pts + ((size_t)p * K + k) * mp.d;
@@ -73,6 +78,7 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
                     if (om == 0.0) continue;  // zero weight: contributes nothing, not even rank
                     if (!trivial) {
                         const double sq = sqrt(om);
+                        if (MF::FAST_EXP && dcmax) bound = fmax(bound, MF::arg_bound(pc, dcmax));
                         MF::post_row(pc, sq);
                         rows[na * RW] = sq;
 #pragma unroll
@@ -103,12 +109,14 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
         KstTile<MF>::isumw(smem, rows_max)[threadIdx.x] = 1.0 / sw;
         KstTile<MF>::nact(smem, rows_max)[threadIdx.x] = na;
         KstTile<MF>::rank(smem, rows_max)[threadIdx.x] = rank;
+        // (a NaN bound compares false: not safe)
+        KstTile<MF>::safe(smem, rows_max)[threadIdx.x] = (MF::FAST_EXP && dcmax && bound <= 700.0) ? 1 : 0;
     }
     __syncthreads();
 }
 
 // one row record (RW doubles at a 32-bit shared-space address) -> weighted row g
-template <class MF>
+template <class MF, bool CLAMP = true>
 __device__ __forceinline__ void kst_row_at(unsigned addr, const double *dcv, double *g, KstTab tab)
 {
     constexpr int RW = KstTile<MF>::RW;
@@ -116,18 +124,18 @@ __device__ __forceinline__ void kst_row_at(unsigned addr, const double *dcv, dou
 #pragma unroll
     for (int c = 0; c < RW; c += 2)
         asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rw[c]), "=d"(rw[c + 1]) : "r"(addr + 8u * c));
-    MF::row(rw + 1, dcv, rw[0], g, tab);
+    MF::template row<CLAMP>(rw + 1, dcv, rw[0], g, tab);
 }
 
 // NR consecutive rows: all reduced rows first, then all rank-one updates, so that the NR exp / reciprocal
 // chains are independent instruction streams the scheduler can interleave
-template <class MF, int NR>
+template <class MF, int NR, bool CLAMP = true>
 __device__ __forceinline__ void kst_rows(double *M, unsigned addr, const double *dcv, KstTab tab)
 {
     constexpr int R = MF::R, RW = KstTile<MF>::RW;
     double g[NR][R];
 #pragma unroll
-    for (int k = 0; k < NR; k++) kst_row_at<MF>(addr + (unsigned)(k * RW * 8), dcv, g[k], tab);
+    for (int k = 0; k < NR; k++) kst_row_at<MF, CLAMP>(addr + (unsigned)(k * RW * 8), dcv, g[k], tab);
 #pragma unroll
     for (int k = 0; k < NR; k++) kst_accum<R, MF::CONST_COL>(M, g[k]);
 }
@@ -136,7 +144,7 @@ __device__ __forceinline__ void kst_rows(double *M, unsigned addr, const double 
 // Remainders first (1, 2, 4 rows by the bits of na), then groups of MF::ROWS rows: the FP64 pipe only
 // saturates with about four independent dependency chains per warp (tools/fp64_probe.cu), which the
 // interleaved rows provide; there is no remainder code after the loop.
-template <class MF>
+template <class MF, bool CLAMP = true>
 __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na, double sw, const double *dcv,
                                            KstTab tab)
 {
@@ -145,14 +153,17 @@ __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na
     for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
     unsigned addr = rows_addr;
     int left = na;
-    if (UN > 1 && (left & 1)) { kst_rows<MF, 1>(M, addr, dcv, tab); addr += RW * 8; left -= 1; }
-    if (UN > 2 && (left & 2)) { kst_rows<MF, 2>(M, addr, dcv, tab); addr += 2 * RW * 8; left -= 2; }
-    if (UN > 4 && (left & 4)) { kst_rows<MF, 4>(M, addr, dcv, tab); addr += 4 * RW * 8; left -= 4; }
+    if (UN > 1 && (left & 1)) { kst_rows<MF, 1, CLAMP>(M, addr, dcv, tab); addr += RW * 8; left -= 1; }
+    if (UN > 2 && (left & 2)) { kst_rows<MF, 2, CLAMP>(M, addr, dcv, tab); addr += 2 * RW * 8; left -= 2; }
+    if (UN > 4 && (left & 4)) { kst_rows<MF, 4, CLAMP>(M, addr, dcv, tab); addr += 4 * RW * 8; left -= 4; }
 #pragma unroll 1
-    for (; left > 0; left -= UN, addr += UN * RW * 8) kst_rows<MF, UN>(M, addr, dcv, tab);
+    for (; left > 0; left -= UN, addr += UN * RW * 8) kst_rows<MF, UN, CLAMP>(M, addr, dcv, tab);
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
     if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = sw;
 }
+
+struct KstTrue { static constexpr bool value = true; };
+struct KstFalse { static constexpr bool value = false; };
 
 // ------------------------------------------------------------------------------------------
 // the hot kernel
@@ -173,7 +184,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
     const int rows_max = prm.K * prm.mp.m;
     const int p0 = blockIdx.y * prm.tile_p;
     KstTab tab = kst_math_init(s_mathtab);
-    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp, prm.tile_p);  // ends with __syncthreads()
+    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp, prm.tile_p, prm.dcmax);  // ends with __syncthreads()
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int np = min(prm.tile_p, prm.S - p0);
@@ -196,6 +207,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
         const double sw = KstTile<MF>::sumw(smem, rows_max)[p];
         // 1 / first pivot, hoisted per particle when the first pivot is the constant-column entry
         constexpr bool INV0 = MF::CONST_COL == 0 && !REG;
+        constexpr bool DUAL = MF::FAST_EXP && UNI;  // the unclamped copy of the draw loop only where it pays
         const double inv0 = KstTile<MF>::isumw(smem, rows_max)[p];
         double acc = 0.0;
         if (!REG && KstTile<MF>::rank(smem, rows_max)[p] < R) {
@@ -214,6 +226,9 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
                 for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)j0));
                 pwn = __ldg(pw + j0);
             }
+            // the draw loop, compiled twice for the kernels worth it: with and without the exponent clamp inside exp
+            auto draws = [&](auto clamp_tag) {
+            constexpr bool CL = decltype(clamp_tag)::value;
             for (int j = j0; j < n; j += stride) {
                 double dcv[MF::NDC];
 #pragma unroll
@@ -226,7 +241,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
                     pwn = __ldg(pw + jn);
                 }
                 double M[KstPacked<R>::N];
-                kst_fisher<MF>(M, rows_addr, na, sw, dcv, tab);
+                kst_fisher<MF, CL>(M, rows_addr, na, sw, dcv, tab);
                 if (REG) {
 #pragma unroll
                     for (int i = 0; i < KstPacked<R>::N; i++) M[i] += __ldg(prm.reg + (size_t)((unsigned)i * ld + (unsigned)j));
@@ -248,6 +263,14 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
                     const double val = kst_criterion<R, CRIT, T, INV0>(M, prm.aux + j, prm.ld, exc, inv0, tab);
                     acc += exc ? -KST_INF : pwj * val;
                 }
+            }
+            };
+            // uniform over the warp: all lanes work on the same particle
+            if constexpr (DUAL) {
+                if (KstTile<MF>::safe(smem, rows_max)[p]) draws(KstFalse{});
+                else draws(KstTrue{});
+            } else {
+                draws(KstTrue{});
             }
             if (UNI) acc = prm.w_uniform * (acc + kst_log(run, tab));
         }

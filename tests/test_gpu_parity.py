@@ -375,3 +375,29 @@ def test_engine_math_accuracy():
     near1 = 1.0 + rng.uniform(-1e-3, 1e-3, 500)
     _, _, l1 = kb._ffi.math_selftest(near1)
     assert np.max(np.abs(l1 - np.log(near1))) <= 3e-16
+
+
+def test_objective_exponent_range_paths():
+    """The D/Identity/uniform-weights kernel keeps two copies of its draw loop: particles that can prove their exp
+    arguments stay within +-700 for every draw skip the exponent clamp, the others keep it.  One swarm mixes
+    both kinds (doses down to 1e-250, where h log(ed50/x) overflows the exponent range) and a prior with one
+    steep draw flips more particles to the clamped copy; results must not depend on the path."""
+    th = wl.sigemax_prior(400, seed=8)
+    pts, w = wl.jittered_swarm(16, 8, 0.0, 1.0, seed=8)
+    pts[1, 0], pts[2, 3], pts[3, 5], pts[4, 1] = 1e-250, 1e-120, 1e-30, 1e-300
+    h, o = H(2, [1.0], th), O(2, [1.0], th)
+    got, want = h.objective_batch(pts, w), o.objective_batch(pts, w)
+    pw = np.full(len(th), 1.0 / len(th))
+    rf.assert_parity(got, want, lambda i: rf.objective(2, [1.0], pts[i], w[i], th, pw), rtol=RTOL)
+    # one draw with a steep Hill coefficient pushes |h log(ed50 / x)| past 700 for the small doses of every
+    # particle: all of them take the clamped copy now
+    th2 = th.copy()
+    th2[7, 3] = 12.0
+    got2 = H(2, [1.0], th2).objective_batch(pts, w)
+    want2 = O(2, [1.0], th2).objective_batch(pts, w)
+    rf.assert_parity(got2, want2, lambda i: rf.objective(2, [1.0], pts[i], w[i], th2, pw), rtol=RTOL)
+    # two-exponential family: a prior draw with a huge elimination rate sends exp(-a t) far below the range
+    tt = wl.tpc_prior(300, seed=2)
+    tt[5, 0] = 60.0
+    ptt, wt = wl.jittered_swarm(12, 5, 0.0, 48.0, seed=3, log_lo=0.05)
+    close(H(3, [1.0], tt, ub=(48.0,)).objective_batch(ptt, wt), O(3, [1.0], tt).objective_batch(ptt, wt), 1e-9)
