@@ -288,7 +288,8 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
 // Draw loop of k_gateaux_eval for one direction (thread): sum over the CTA's draws [j0, j1) of
 // pw_j * sum_rows omega gt' At_j gt.  NL >= 0: exactly NL rows, constants in registers (lsq, lpc), no branch inside
 // the loop.  NL = -1: m rows with constants in shared memory (s_rows), rows outside live_mask skipped.
-template <class MF, int NL>
+// CL = false: the CTA has proven that no exp argument leaves +-700 (MF::arg_bound), rows skip the exponent clamp.
+template <class MF, int NL, bool CL = true>
 __device__ __forceinline__ double kst_gd_draws(const double *__restrict__ dc, const double *__restrict__ gAp,
                                                size_t ld, int64_t j0, int64_t j1,
                                                double *s_draw, const double *s_rows, int m, unsigned live_mask,
@@ -336,7 +337,7 @@ __device__ __forceinline__ double kst_gd_draws(const double *__restrict__ dc, co
 #pragma unroll
                 for (int i = 0; i < (NL > 0 ? NL : 0); i++) {
                     double gv[R];
-                    MF::row(lpc[i], dcv, lsq[i], gv, tab);  // weighted row: gv' A gv = omega * gt' A gt
+                    MF::template row<CL>(lpc[i], dcv, lsq[i], gv, tab);  // weighted row: gv' A gv = omega * gt' A gt
                     double q = 0.0;
 #pragma unroll
                     for (int a = 0; a < R; a++) {
@@ -374,6 +375,10 @@ __device__ __forceinline__ double kst_gd_draws(const double *__restrict__ dc, co
     return acc;
 }
 
+struct KstDcMax {
+    double v[8];  // max_j |dc[c][j]| (kst_problem::dcmax)
+};
+
 // One thread per direction; draws staged in shared memory.
 // MR > 0: the unit has exactly MR rows and their constants stay in registers; MR = 0: any unit length, row
 // constants in shared memory.  A draw's constants (NDC hoisted constants + packed pw_j At_j) are stored
@@ -382,7 +387,8 @@ template <class MF, int MR>
 __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__restrict__ dc,
                                                             const double *__restrict__ gAp, size_t ld, int64_t N,
                                                             const double *__restrict__ dirs, int64_t G,
-                                                            KstModelParams mp, double *__restrict__ partials)
+                                                            KstModelParams mp, KstDcMax dcmax,
+                                                            double *__restrict__ partials)
 {
     constexpr int R = MF::R, RW = KstRowW<MF>::RW, NP = KstPacked<R>::N, NS = MF::NDC + NP, NSP = (NS + 1) / 2 * 2;
     constexpr int MRR = MR > 0 ? MR : 1;
@@ -398,7 +404,7 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
     // rows of this thread's direction (weight 1); trivial rows get sqrt(omega) = 0 and benign pc.
     // live_mask: bit i is set when row i is live for at least one direction of the CTA; rows that are
     // trivial for the whole CTA (time 0 of every vector unit) are skipped outright in the draw loop.
-    double sw_triv = 0.0;
+    double sw_triv = 0.0, bound = 0.0;
     unsigned live_mask = 0;
     double rsq[MRR], rpc[MRR][MF::NPC];
 #pragma unroll
@@ -417,6 +423,7 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
             sq = 0.0;
             for (int c = 0; c < MF::NPC; c++) pc[c] = 1.0;
         }
+        if (MF::FAST_EXP) bound = fmax(bound, MF::arg_bound(pc, dcmax.v));
         MF::post_row(pc, sq);
         if (MR > 0) {
 #pragma unroll
@@ -462,13 +469,20 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
                 nl++;
             }
         }
+        // every exp argument of every direction of the CTA within +-700 for every draw: rows without the exponent
+        // clamp (register-row kernels only; a NaN bound compares false)
+        const bool fast = MF::FAST_EXP && __syncthreads_and(bound <= 700.0);
+#define KST_GD_CASE(NLV)                                                                                          \
+    acc = fast ? kst_gd_draws<MF, NLV, !MF::FAST_EXP>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab) \
+               : kst_gd_draws<MF, NLV, true>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab)
         switch (nl) {
-        case 0: acc = kst_gd_draws<MF, 0>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
-        case 1: acc = kst_gd_draws<MF, 1>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
-        case 2: acc = kst_gd_draws<MF, (MR >= 2 ? 2 : 1)>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
-        case 3: acc = kst_gd_draws<MF, (MR >= 3 ? 3 : 1)>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
-        default: acc = kst_gd_draws<MF, (MR >= 4 ? 4 : 1)>(dc, gAp, ld, j0, j1, s_draw, nullptr, 0, 0u, lsq, lpc, sw_triv, tab); break;
+        case 0: KST_GD_CASE(0); break;
+        case 1: KST_GD_CASE(1); break;
+        case 2: KST_GD_CASE((MR >= 2 ? 2 : 1)); break;
+        case 3: KST_GD_CASE((MR >= 3 ? 3 : 1)); break;
+        default: KST_GD_CASE((MR >= 4 ? 4 : 1)); break;
         }
+#undef KST_GD_CASE
     } else {
         acc = kst_gd_draws<MF, -1>(dc, gAp, ld, j0, j1, s_draw, s_rows, m, live_mask, rsq, rpc, sw_triv, tab);
     }
@@ -565,7 +579,9 @@ static int launch_gd(kst_problem *h, int64_t G, const double *d_dirs, size_t sme
     *n_split_out = (int)n_split;
     if (h->g_singular) return KST_OK;  // the finishing kernel fills NaN
     const dim3 grid((unsigned)gblocks, (unsigned)n_split);
-    k_gateaux_eval<MF, MR><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->gAp, h->ld, h->N, d_dirs, G, h->mp,
+    KstDcMax dm;
+    for (int c = 0; c < 8; c++) dm.v[c] = h->dcmax[c];
+    k_gateaux_eval<MF, MR><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->gAp, h->ld, h->N, d_dirs, G, h->mp, dm,
                                                                  h->gd_partials);
     KST_CUDA(cudaGetLastError());
     return KST_OK;
