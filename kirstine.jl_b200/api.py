@@ -465,6 +465,61 @@ def informationmatrix(d, m, cp, p, na):
         h.close()
 
 
+def implied_covariates(d, m, cp):
+    """implied_covariates(d, m, cp) (src/design-common.jl:35-49): the covariates a design implies, one dict per
+    design point -- the host-side statement of what the device functors' prep_row does (a debugging helper, like
+    in the reference)."""
+    out = []
+    for z in d.points:
+        if isinstance(m, (EmaxModel, SigEmaxModel)):
+            out.append({"dose": float(z[0])})
+        elif isinstance(m, TPCModel):
+            out.append({"time": float(z[0])})
+        elif isinstance(m, VUMod):
+            out.append({"time": [float(j * z[0]) for j in range(m.m)]})
+        elif isinstance(m, DTRMod):
+            if isinstance(cp, FixedDose):
+                dose, time = cp.dose, [float(z[0])]
+            elif isinstance(cp, FixedTimes):
+                dose, time = float(z[0]), list(cp.time)
+            elif isinstance(cp, LogEquidistantTimes):
+                time = [0.0] + ([float(z[1])] if m.m > 1 else [])
+                for _ in range(2, m.m):
+                    time.append(cp.b * time[-1])
+                dose = float(z[0])
+            elif isinstance(cp, EquidistantTimes):
+                dose, time = float(z[0]), [float(j * z[1]) for j in range(m.m)]
+            else:
+                dose, time = float(z[0]), [float(z[1])]
+            out.append({"dose": dose, "time": time})
+        elif isinstance(m, LinLogReg):
+            if len(z) != m.dim_covariate:
+                raise ValueError("dimension of covariate and design point don't match")
+            out.append({"x": [float(v) for v in z]})
+        elif isinstance(m, SinLogReg):
+            out.append({"t": float(z[0])})
+        else:
+            raise TypeError("model type %s is not registered with the B200 engine" % type(m).__name__)
+    return out
+
+
+def apply_transformation(M, p, trafo):
+    """apply_transformation(nim, p, trafo) (src/design-common.jl:113-142): the information matrix of the
+    transformed parameter for ONE matrix and ONE parameter value, M_T = (DT M^-1 DT')^-1 (Identity: M itself).
+    A debugging helper of the reference on a single r x r matrix; the engine evaluates the same expression for
+    every (particle, draw) inside kst_criterion.  Only the upper triangle of M is read."""
+    M = np.asarray(M, dtype=np.float64)
+    M = np.triu(M) + np.triu(M, 1).T
+    if isinstance(trafo, Identity):
+        return M.copy()
+    DT = np.atleast_2d(np.asarray(trafo.jacobian_matrix(p), dtype=np.float64))
+    if DT.shape[1] != M.shape[0]:
+        raise ValueError("trafo Jacobian must have %d columns, got %d" % (M.shape[0], DT.shape[1]))
+    L = np.linalg.cholesky(M)                      # PosDefException in the reference when M is not PD
+    B = np.linalg.solve(L.T, np.linalg.solve(L, DT.T))
+    return np.linalg.inv(DT @ B)
+
+
 def simplify(d, dp, maxweight=0, maxdist=0, **uargs):
     """src/designproblem.jl:185-190."""
     d = dp.cp.simplify_unique(d, dp.dr, dp.m, **uargs)

@@ -100,3 +100,68 @@ def test_shard_range_partitions_the_prior():
         assert ranges[0][0] == 0 and ranges[-1][1] == N
         assert all(a[1] == b[0] for a, b in zip(ranges, ranges[1:]))
         assert all(0 <= j1 - j0 <= -(-N // world) for j0, j1 in ranges)
+
+
+def test_apportion_pukelsheim_exhibit():  # test/designmeasure.jl:129-139 (Pukelsheim p. 310, Exhibit 12.2)
+    w = np.array([1 / 6, 1 / 3, 1 / 2])
+    ref = {7: [2, 2, 3], 8: [1, 3, 4], 9: [2, 3, 4], 10: [2, 3, 5], 11: [2, 4, 5], 12: [2, 4, 6]}
+    for n, want in ref.items():
+        assert kb.apportion(w, n).tolist() == want
+
+
+def test_simplify_drop_reference_cases():  # test/designmeasure.jl:141-156
+    d = kb.DesignMeasure([[1], [2], [3]], [1e-6, 0.5 - 5e-7, 0.5 - 5e-7])
+    assert kb.simplify_drop(d, 1e-4) == kb.uniform_design([[2], [3]])
+    assert kb.simplify_drop(d, 1e-6) == kb.uniform_design([[2], [3]])      # drop also on equality
+    same = kb.simplify_drop(d, 1e-7)
+    assert same == d and same is not d                                      # unchanged copy
+    o = kb.one_point_design([42])
+    o_simp = kb.simplify_drop(o, 1e-4)
+    assert o_simp == o and o_simp is not o
+
+
+def test_simplify_merge_reference_cases():  # test/designmeasure.jl:158-189
+    d = kb.DesignMeasure([[1, 1], [5, 1], [3, 10]], [0.3, 0.1, 0.6])
+    dr = kb.DesignInterval(a=(0, 100), b=(0, 100))
+    ref = kb.DesignMeasure([[2, 1], [3, 10]], [0.4, 0.6])
+    assert kb.simplify_merge(d, dr, 0.05) == ref
+    assert kb.simplify_merge(d, dr, 0.04) == ref                           # merge also on equality
+    same = kb.simplify_merge(d, dr, 0.03)
+    assert same == d and same is not d
+    o = kb.one_point_design([42, 42])
+    o_simp = kb.simplify_merge(o, kb.DesignInterval(a=(0, 100), b=(1, 100)), 0.05)
+    assert o_simp == o and o_simp is not o
+    # unmerged points stay bit-identical (no round trip through the unit cube)
+    dr1 = kb.DesignInterval(a=(0, 0.95))
+    d1 = kb.uniform_design([[0.1], [0.5], [0.8], [0.81]])
+    assert kb.simplify_merge(d1, dr1, 0) == d1
+    merged = kb.simplify_merge(d1, dr1, 0.1)
+    assert d1.points[:2].tolist() == merged.points[1:3].tolist()
+
+
+def test_sort_points_reference_case():  # test/designmeasure.jl:192-200
+    d = kb.DesignMeasure([[3, 4], [2, 1], [1, 1], [2, 3]], [0.4, 0.2, 0.3, 0.1])
+    s = kb.sort_points(d)
+    assert s == kb.DesignMeasure([[1, 1], [2, 1], [2, 3], [3, 4]], [0.3, 0.2, 0.1, 0.4])
+
+
+def test_apply_transformation_values():  # test/design-common.jl:84-106
+    M = np.array([[2.0, 1.0], [1.0, 3.0]])
+    p = kb.EmaxPar(1, 2, 3)[:2]
+    np.testing.assert_allclose(kb.apply_transformation(M, p, kb.Identity()), M)
+    np.testing.assert_allclose(kb.apply_transformation(M, p, kb.DeltaMethod(lambda q: [[0, 1]])), [[2.5]], rtol=1e-15)
+    np.testing.assert_allclose(kb.apply_transformation(M, p, kb.DeltaMethod(lambda q: [[2, 0], [-1, 1]])),
+                               [[1.75, 2.0], [2.0, 3.0]], rtol=1e-14)
+    # only the upper triangle is read
+    junk = np.array([[2.0, 1.0], [99.0, 3.0]])
+    np.testing.assert_allclose(kb.apply_transformation(junk, p, kb.DeltaMethod(lambda q: [[0, 1]])), [[2.5]], rtol=1e-15)
+
+
+def test_implied_covariates():  # test/design-common.jl:205-216
+    d = kb.DesignMeasure([[0], [1], [2]], [0.2, 0.3, 0.5])
+    c = kb.implied_covariates(d, kb.EmaxModel(1), kb.CopyDose())
+    assert [ci["dose"] for ci in c] == [0.0, 1.0, 2.0]
+    cv = kb.implied_covariates(kb.DesignMeasure([[5], [20]], [0.25, 0.75]), kb.VUMod(0.1, 3), kb.EquiTime())
+    assert cv[0]["time"] == [0.0, 5.0, 10.0] and cv[1]["time"] == [0.0, 20.0, 40.0]   # test/example-vector.jl:45-50
+    cd = kb.implied_covariates(kb.DesignMeasure([[10, 0.5]], [1.0]), kb.DTRMod(1, 4), kb.LogEquidistantTimes(2.0))
+    assert cd[0] == {"dose": 10.0, "time": [0.0, 0.5, 1.0, 2.0]}                       # docs/src/dtr.md:663-681
