@@ -520,6 +520,44 @@ def apply_transformation(M, p, trafo):
     return np.linalg.inv(DT @ B)
 
 
+def gateauxderivative_grid(d, dp, n_grid=None, csv_path=None):
+    """The data plot_gateauxderivative draws (src/plot.jl:103-187), without a plotting backend: the Gateaux
+    derivative of `d` on a grid over the bounding box of the design region.
+
+    1-d regions: n_grid equidistant points (default 101) merged with the design's own points and sorted; returns
+    (x_grid, gd).  2-d regions: an n_grid[0] x n_grid[1] product grid (default 51 x 51); returns (range_x, range_y,
+    gd) with gd[i, j] at (range_x[i], range_y[j]).  Points outside the region would be NaN (every DesignInterval
+    point of its bounding box is inside).  csv_path: also write the grid as CSV (columns = coordinates, gd)."""
+    lb, ub = np.asarray(dp.dr.lowerbound), np.asarray(dp.dr.upperbound)
+    dim = len(lb)
+    if dim == 1:
+        n = 101 if n_grid is None else n_grid
+        if np.ndim(n) != 0:
+            raise ValueError("n_grid must be a single integer")
+        if n < 2:
+            raise ValueError("n_grid must be >= 2")
+        x = np.sort(np.concatenate([np.linspace(lb[0], ub[0], int(n)), d.points.ravel()]))
+        gd = gateauxderivative(d, [one_point_design([v]) for v in x], dp)
+        out = (x, gd)
+        table = np.column_stack([x, gd])
+    elif dim == 2:
+        n = (51, 51) if n_grid is None else tuple(np.atleast_1d(n_grid).tolist())
+        if len(n) != 2:
+            raise ValueError("n_grid must be a 2-tuple")
+        if min(n) < 2:
+            raise ValueError("all elements of n_grid must be >= 2")
+        rx, ry = np.linspace(lb[0], ub[0], n[0]), np.linspace(lb[1], ub[1], n[1])
+        gx, gy = np.meshgrid(rx, ry, indexing="ij")
+        gd = gateauxderivative(d, [one_point_design([a, b]) for a, b in zip(gx.ravel(), gy.ravel())], dp).reshape(n)
+        out = (rx, ry, gd)
+        table = np.column_stack([gx.ravel(), gy.ravel(), gd.ravel()])
+    else:
+        raise ValueError("grids are defined for 1- and 2-dimensional design regions")
+    if csv_path is not None:
+        np.savetxt(csv_path, table, delimiter=",", header=",".join(list(dp.dr.name) + ["gateauxderivative"]), comments="")
+    return out
+
+
 def simplify(d, dp, maxweight=0, maxdist=0, **uargs):
     """src/designproblem.jl:185-190."""
     d = dp.cp.simplify_unique(d, dp.dr, dp.m, **uargs)

@@ -200,3 +200,43 @@ def test_exchange_strategy():  # test/solve-exchange.jl:69-88 + src/solve-exchan
     dm, _ = kb.solve(dp, kb.DirectMaximization(optimizer=kb.Pso(iterations=100, swarmsize=50),
                                                prototype=kb.DesignMeasure(([0.3], 1 / 3), ([2.0], 1 / 3), ([20.0], 1 / 3))))
     assert kb.efficiency(d, dm, dp) > 0.97
+
+
+def test_gateauxderivative_grid_export(tmp_path):
+    """Headless form of plot_gateauxderivative (src/plot.jl:103-187; sizes as checked in test/plot.jl:17-60)."""
+    import kirstine_b200 as kb
+    # 1-d: Emax, locally optimal design on [0, 1] (test/example-emax.jl:49-61)
+    e0, emax, ec50 = 0.0, 1.0, 0.2
+    a, b = 0.0, 1.0
+    xstar = (a * (b + ec50) + b * (a + ec50)) / (a + b + 2 * ec50)
+    d = kb.uniform_design([[a], [xstar], [b]])
+    dp = kb.DesignProblem(criterion=kb.DCriterion(), region=kb.DesignInterval(dose=(0, 1)),
+                          prior_knowledge=kb.PriorSample([kb.EmaxPar(e0, emax, ec50)]), model=kb.EmaxModel(1),
+                          covariate_parameterization=kb.CopyDose())
+    x, gd = kb.gateauxderivative_grid(d, dp)
+    assert len(x) == len(gd) == 101 + 3 and np.all(np.diff(x) >= 0)
+    assert gd.max() < 1e-9                                    # equivalence theorem at the optimal design
+    csv = tmp_path / "gd.csv"
+    x2, gd2 = kb.gateauxderivative_grid(d, dp, n_grid=11, csv_path=str(csv))
+    assert len(x2) == 14                                      # grid with 11 points plus the three design points
+    tab = np.loadtxt(csv, delimiter=",", skiprows=1)
+    assert tab.shape == (14, 2) and open(csv).readline().strip() == "dose,gateauxderivative"
+    np.testing.assert_array_equal(tab[:, 1], gd2)
+    with pytest.raises(ValueError, match="single integer"):
+        kb.gateauxderivative_grid(d, dp, n_grid=(3, 3))
+    with pytest.raises(ValueError, match=">= 2"):
+        kb.gateauxderivative_grid(d, dp, n_grid=1)
+    # 2-d: dose-time-response with CopyBoth (test/example-dtr.jl)
+    th = wl.dtr_prior(50)
+    dp2 = kb.DesignProblem(criterion=kb.DCriterion(), region=kb.DesignInterval(dose=(0, 100), time=(0, 24)),
+                           prior_knowledge=kb.PriorSample(th), model=kb.DTRMod(1, 1),
+                           covariate_parameterization=kb.CopyBoth())
+    d2 = kb.uniform_design([[100, 1], [100, 4], [50, 8], [20, 12], [100, 24], [60, 2]])
+    rx, ry, g2 = kb.gateauxderivative_grid(d2, dp2)
+    assert rx.shape == (51,) and ry.shape == (51,) and g2.shape == (51, 51) and np.all(np.isfinite(g2))
+    one = kb.gateauxderivative(d2, [kb.one_point_design([rx[7], ry[30]])], dp2)[0]
+    assert g2[7, 30] == pytest.approx(one, rel=1e-12)
+    rx, ry, g3 = kb.gateauxderivative_grid(d2, dp2, n_grid=(4, 6))
+    assert g3.shape == (4, 6)
+    with pytest.raises(ValueError, match="2-tuple"):
+        kb.gateauxderivative_grid(d2, dp2, n_grid=5)
