@@ -240,3 +240,29 @@ def test_gateauxderivative_grid_export(tmp_path):
     assert g3.shape == (4, 6)
     with pytest.raises(ValueError, match="2-tuple"):
         kb.gateauxderivative_grid(d2, dp2, n_grid=5)
+
+
+def test_pso_long_run_in_pieces_equals_one_run():
+    """cfg-5-shaped swarm (1024 particles, K = 8) for 500 iterations, the iteration count BASELINE.json quotes:
+    monotone trace, and running it as 5 x 100 iterations gives the same bits as one run of 500 (the state lives
+    on the device between calls, the random stream is keyed on the iteration counter)."""
+    import kirstine_b200 as kb
+    th = wl.sigemax_prior(2000, seed=5)
+    pw = np.full(len(th), 1.0 / len(th))
+    proto = (np.linspace(0, 1, 8)[:, None], np.full(8, 1 / 8))
+    h1 = kb.ProblemHandle(2, [1.0], th, pw, 0, None, (0.0,), (1.0,))
+    assert h1.pso_init(1024, 8, *proto, seed=7) == 0
+    t1 = h1.pso_run(500)[0]
+    h5 = kb.ProblemHandle(2, [1.0], th, pw, 0, None, (0.0,), (1.0,))
+    assert h5.pso_init(1024, 8, *proto, seed=7) == 0
+    t5 = np.concatenate([h5.pso_run(100)[0] for _ in range(5)])
+    assert np.array_equal(t1, t5)
+    assert np.all(np.diff(t1) >= 0) and np.isfinite(t1[-1])
+    s1, s5 = h1.pso_state(), h5.pso_state()
+    for key in ("x_pts", "x_w", "v_pts", "v_w", "p_pts", "p_w", "g_pts", "g_w", "fx", "fp"):
+        assert np.array_equal(s1[key], s5[key]), key
+    assert s1["n_eval"] == 1024 * 501
+    # the solved design is (near) optimal: Gateaux derivative <= ~0 over the region
+    g = kb.DesignMeasure(s1["g_pts"], s1["g_w"] / s1["g_w"].sum())
+    assert not h1.gateaux_prepare(g.points, g.weights)
+    assert h1.gateaux_eval(np.linspace(0, 1, 501)).max() < 1e-2
