@@ -157,13 +157,27 @@ __device__ __forceinline__ double kst_ld_peer(const double *p)
     return v;
 }
 
+// partials != nullptr fuses the last step of the objective evaluation into the collective: entry i of this rank's
+// vector is the fixed-order sum of partials[i][0..n_blk) plus `offset` (exactly what k_obj_finish computes), so a
+// swarm evaluation on several GPUs is k_objective + this one kernel.
 __global__ void __launch_bounds__(1024) k_peer_allreduce(double *buf, int count, KstPeerPtrs peers, int nranks, int rank,
-                                                         unsigned long long seq)
+                                                         unsigned long long seq, const double *__restrict__ partials,
+                                                         int n_blk, double offset)
 {
     __shared__ int s_fail;
     const int par = (int)(seq & 1ull);
     KstPeerBlock *mine = peers.blk[rank];
-    for (int i = threadIdx.x; i < count; i += blockDim.x) mine->data[par][i] = buf[i];
+    for (int i = threadIdx.x; i < count; i += blockDim.x) {
+        double v;
+        if (partials) {
+            double s = 0.0;
+            for (int b = 0; b < n_blk; b++) s += partials[(size_t)i * n_blk + b];
+            v = s + offset;
+        } else {
+            v = buf[i];
+        }
+        mine->data[par][i] = v;
+    }
     if (threadIdx.x == 0) s_fail = 0;
     __threadfence_system();
     __syncthreads();
@@ -207,13 +221,31 @@ int kst_allreduce_sum(kst_problem *h, double *d_buf, size_t count)
     if (h->peer_ready && count <= KST_PEER_CAP) {
         KstPeerPtrs pp;
         for (int r = 0; r < KST_PEER_MAX; r++) pp.blk[r] = (KstPeerBlock *)h->peer_map[r];
-        k_peer_allreduce<<<1, 1024, 0, h->stream>>>(d_buf, (int)count, pp, h->nranks, h->rank, ++h->peer_seq);
+        k_peer_allreduce<<<1, 1024, 0, h->stream>>>(d_buf, (int)count, pp, h->nranks, h->rank, ++h->peer_seq, nullptr, 0,
+                                                    0.0);
         KST_CUDA(cudaGetLastError());
         return KST_OK;
     }
     if (!h->comm) { kst_set_error("all-reduce of %zu doubles needs the NCCL communicator (kst_comm_init)", count); return KST_ESTATE; }
     const int rc = g_nccl.all_reduce(d_buf, d_buf, count, KST_NCCL_FLOAT64, KST_NCCL_SUM, h->comm, h->stream);
     if (rc) return nccl_fail("ncclAllReduce", rc);
+    return KST_OK;
+}
+
+// Swarm evaluation + sum over the ranks.  On the peer-memory path the per-CTA partial sums of k_objective go straight
+// into the exchange kernel (no k_obj_finish launch in between).
+int kst_objective_allreduce(kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *d_fx)
+{
+    const bool fuse = h->nranks > 1 && h->peer_ready && S <= KST_PEER_CAP;
+    int n_blk = 0;
+    int rc = kst_launch_objective(h, S, K, d_pts, d_w, d_fx, fuse ? &n_blk : nullptr);
+    if (rc) return rc;
+    if (!fuse) return kst_allreduce_sum(h, d_fx, (size_t)S);
+    KstPeerPtrs pp;
+    for (int r = 0; r < KST_PEER_MAX; r++) pp.blk[r] = (KstPeerBlock *)h->peer_map[r];
+    k_peer_allreduce<<<1, 1024, 0, h->stream>>>(d_fx, S, pp, h->nranks, h->rank, ++h->peer_seq, h->partials, n_blk,
+                                                h->offset);
+    KST_CUDA(cudaGetLastError());
     return KST_OK;
 }
 
@@ -494,9 +526,7 @@ extern "C" int kst_objective_batch_device(kst_problem *h, int S, int K, const do
 {
     KST_CHECK_HANDLE(h);
     if (!d_points || !d_weights || !d_fx) { kst_set_error("objective_batch_device: NULL buffer"); return KST_EINVAL; }
-    int rc = kst_launch_objective(h, S, K, d_points, d_weights, d_fx);
-    if (rc) return rc;
-    return kst_allreduce_sum(h, d_fx, (size_t)S);
+    return kst_objective_allreduce(h, S, K, d_points, d_weights, d_fx);
 }
 
 extern "C" int kst_objective_batch(kst_problem *h, int S, int K, const double *points, const double *weights, double *fx)
@@ -662,12 +692,13 @@ static int pso_evaluate(kst_problem *h)
 {
     KstPso &p = h->pso;
     int rc;
-    if (p.mode == KST_PSO_MODE_OBJECTIVE)
-        rc = kst_launch_objective(h, p.S, p.K, p.x_pts, p.x_w, p.fx);
-    else
+    if (p.mode == KST_PSO_MODE_OBJECTIVE) {
+        rc = kst_objective_allreduce(h, p.S, p.K, p.x_pts, p.x_w, p.fx);
+    } else {
         rc = kst_launch_gateaux_eval(h, p.S, p.x_pts, p.fx);
-    if (rc) return rc;
-    rc = kst_allreduce_sum(h, p.fx, (size_t)p.S);
+        if (rc) return rc;
+        rc = kst_allreduce_sum(h, p.fx, (size_t)p.S);
+    }
     p.n_eval += p.S;
     return rc;
 }

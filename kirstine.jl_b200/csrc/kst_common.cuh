@@ -130,8 +130,10 @@ struct kst_problem {
 
 // kst_objective.cu
 int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const double *d_dt);
+// defer_n_blk != nullptr: the per-CTA partial sums stay in h->partials ([S][*defer_n_blk]) and the caller finishes them
+// (kst_api.cu fuses that step into the peer-memory all-reduce)
 int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, const double *d_w,
-                         double *d_fx);
+                         double *d_fx, int *defer_n_blk = nullptr);
 int kst_launch_infomatrix(kst_problem *h, int K, const double *d_pts, const double *d_w,
                           int64_t draw, double *d_M);
 int kst_objective_grid(const kst_problem *h, int S, int *n_blk, int *tile_p);

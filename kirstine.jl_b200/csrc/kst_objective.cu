@@ -225,7 +225,8 @@ int kst_objective_grid(const kst_problem *h, int S, int *n_blk, int *tile_p)
     return tiles;
 }
 
-int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *d_fx)
+int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *d_fx,
+                         int *defer_n_blk)
 {
     if (S < 1 || K < 1 || K * h->m > KST_MAX_ROWS) {
         kst_set_error("objective: need S >= 1, K >= 1, K*m <= %d (S=%d K=%d m=%d)", KST_MAX_ROWS, S, K, h->m);
@@ -256,6 +257,10 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
     if (rc) return rc;
     KST_CUDA(cudaGetLastError());
     if (h->prof_on) KST_CUDA(cudaEventRecord(h->prof_events.back(), h->stream));
+    if (defer_n_blk) {
+        *defer_n_blk = n_blk;
+        return KST_OK;
+    }
     k_obj_finish<<<(S + 127) / 128, 128, 0, h->stream>>>(h->partials, n_blk, h->offset, d_fx, S);
     KST_CUDA(cudaGetLastError());
     return KST_OK;
