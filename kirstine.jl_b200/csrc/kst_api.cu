@@ -692,7 +692,10 @@ static int pso_evaluate(kst_problem *h)
 {
     KstPso &p = h->pso;
     int rc;
-    if (p.mode == KST_PSO_MODE_OBJECTIVE) {
+    if (p.mode == KST_PSO_MODE_OBJECTIVE && h->nranks <= 1) {
+        // one GPU: the finish step rides along in k_pso_best, which follows every evaluation of the swarm
+        rc = kst_launch_objective(h, p.S, p.K, p.x_pts, p.x_w, p.fx, &p.pending_n_blk);
+    } else if (p.mode == KST_PSO_MODE_OBJECTIVE) {
         rc = kst_objective_allreduce(h, p.S, p.K, p.x_pts, p.x_w, p.fx);
     } else {
         rc = kst_launch_gateaux_eval(h, p.S, p.x_pts, p.fx);

@@ -56,6 +56,7 @@ void kst_set_error(const char *fmt, ...);
 
 struct KstPso {
     int S = 0, K = 0, mode = 0, iter = 0;
+    int pending_n_blk = 0;  // > 0: fx still sits in h->partials as per-CTA sums, k_pso_best finishes it
     double c1 = 0, c2 = 0;
     uint64_t seed = 0;
     int64_t n_eval = 0;

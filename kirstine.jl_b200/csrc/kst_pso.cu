@@ -204,8 +204,11 @@ __global__ void k_pso_move(KstPsoDev s, uint32_t iter, double c1, double c2, dou
 // pso_update_best!: strict '>', sequential semantics => the lowest index attaining the maximum
 // among improved particles becomes the global best iff it beats fg; NaN never wins.
 // status (init only): 1 = fg == +Inf, 2 = all fx NaN.
+// partials != nullptr: the evaluation kernel's per-CTA partial sums are still unfinished; fx[i] is their fixed-order
+// sum plus `offset` (what k_obj_finish would have written), computed here to save a launch per iteration.
 __global__ void __launch_bounds__(1024) k_pso_best(KstPsoDev s, int init, double *tr_fx, double *tr_pts, double *tr_w,
-                                                   int slot, int *status)
+                                                   int slot, int *status, const double *__restrict__ partials,
+                                                   int n_blk, double offset)
 {
     __shared__ double s_val[1024];
     __shared__ int s_idx[1024];
@@ -218,7 +221,15 @@ __global__ void __launch_bounds__(1024) k_pso_best(KstPsoDev s, int init, double
     bool have = false;
     bool notnan = false;
     for (int i = tid; i < s.S; i += blockDim.x) {
-        const double f = s.fx[i];
+        double f;
+        if (partials) {
+            double acc = 0.0;
+            for (int b = 0; b < n_blk; b++) acc += partials[(size_t)i * n_blk + b];
+            f = acc + offset;
+            s.fx[i] = f;
+        } else {
+            f = s.fx[i];
+        }
         const double fpi = init ? (-KST_DINF) : s.fp[i];
         notnan = notnan || (f == f);
         if (f > fpi) {
@@ -341,7 +352,9 @@ int kst_launch_pso_best(kst_problem *h, int init, int trace_slot)
     KstPso &p = h->pso;
     k_pso_best<<<1, 1024, 0, h->stream>>>(s, init, trace_slot >= 0 ? p.tr_fx : nullptr,
                                            trace_slot >= 0 ? p.tr_pts : nullptr, trace_slot >= 0 ? p.tr_w : nullptr,
-                                           trace_slot >= 0 ? trace_slot : 0, init ? h->d_flag : nullptr);
+                                           trace_slot >= 0 ? trace_slot : 0, init ? h->d_flag : nullptr,
+                                           p.pending_n_blk ? h->partials : nullptr, p.pending_n_blk, h->offset);
+    p.pending_n_blk = 0;
     KST_CUDA(cudaGetLastError());
     return KST_OK;
 }
