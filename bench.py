@@ -278,7 +278,7 @@ def main():
         pass
     roofline = {
         "bound": "fp64", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-        "frac": achieved_tf / peak_tf if peak_tf else None, "traffic": traffic,
+        "frac": achieved_tf / peak_tf if peak_tf else None, "frac_of_nominal": achieved_tf / 37.2, "traffic": traffic,
         "kernel": "k_objective<KstSigEmax,D,Identity>", "kernel_ms": kern_avg_ms, "launches_timed": kern_launches,
         "flops_per_unit": FLOPS_PER_UNIT,
         "peak_source": "DFMA micro-kernel measured in this run (MEASURED_PEAKS.json has no FP64 figure; "
