@@ -342,7 +342,7 @@ extern "C" int kst_problem_destroy(kst_problem *h)
     if (h->peer_local) cudaFree(h->peer_local);
     kst_pso_free(h);
     void *ptrs[] = {h->theta, h->pw, h->dc, h->cs, h->aux, h->reg, h->partials, h->stage_pts, h->stage_w, h->stage_fx,
-                    h->gA, h->gAp, h->gtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials};
+                    h->gA, h->gAp, h->gtrB, h->g_wtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
@@ -450,7 +450,7 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
     KST_TRY(cudaMalloc(&h->dc, sizeof(double) * ndc * h->ld));
     KST_TRY(cudaMalloc(&h->cs, sizeof(double) * r * h->ld));
     if (h->n_aux) KST_TRY(cudaMalloc(&h->aux, sizeof(double) * h->n_aux * h->ld));
-    KST_TRY(cudaMalloc(&h->d_flag, sizeof(int)));
+    KST_TRY(cudaMalloc(&h->d_flag, 16));  // flag word at offset 0, one double of scratch at offset 8 (kst_sum_fixed)
     KST_TRY(cudaMalloc(&d_theta_aos, sizeof(double) * N * r));
     KST_TRY(cudaMemsetAsync(h->pw, 0, sizeof(double) * h->ld, h->stream));
     KST_TRY(cudaMemcpyAsync(d_theta_aos, theta, sizeof(double) * N * r, cudaMemcpyHostToDevice, h->stream));

@@ -105,10 +105,11 @@ struct kst_problem {
 
     // Gateaux constants at the last prepared design: At [r*r][ld] (scaled space), trB [ld]
     double *gA = nullptr, *gtrB = nullptr;
+    double *g_wtrB = nullptr;  // scratch of gateaux_prepare: pw_j (trB_j - tr[A_j R]) per draw, summed into g_offset
     double *gAp = nullptr;     // what the evaluation kernel streams: packed upper of pw_j At_j, off-diagonals doubled, [r(r+1)/2][ld]
     int g_ready = 0, g_singular = 0;
     double g_offset = 0.0;     // sum_j pw_j trB_j
-    int *d_flag = nullptr;     // device flag word (singular detection)
+    int *d_flag = nullptr;     // 16 bytes: device flag word (singular detection) + one double of scratch at offset 8
     double *gd_dirs = nullptr, *gd_out = nullptr, *gd_partials = nullptr;
     size_t gd_cap = 0, gd_partials_cap = 0;
 

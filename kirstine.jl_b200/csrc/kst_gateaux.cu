@@ -514,9 +514,9 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
         KST_CUDA(cudaMalloc(&h->gA, sizeof(double) * h->r * h->r * h->ld));
         KST_CUDA(cudaMalloc(&h->gAp, sizeof(double) * (h->r * (h->r + 1) / 2) * h->ld));
         KST_CUDA(cudaMalloc(&h->gtrB, sizeof(double) * h->ld));
+        KST_CUDA(cudaMalloc(&h->g_wtrB, sizeof(double) * h->ld));
     }
-    double *wtrB = nullptr;
-    KST_CUDA(cudaMalloc(&wtrB, sizeof(double) * h->N));
+    double *wtrB = h->g_wtrB;
     KST_CUDA(cudaMemsetAsync(h->d_flag, 0, sizeof(int), h->stream));
     const int nt = 128;
     const unsigned nb = (unsigned)((h->N + nt - 1) / nt);
@@ -527,7 +527,6 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
     });
     KST_CUDA(cudaGetLastError());
     int rc = kst_sum_fixed(h, wtrB, h->N, &h->g_offset);
-    cudaFree(wtrB);
     if (rc) return rc;
     int flag = 0;
     KST_CUDA(cudaMemcpyAsync(&flag, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));

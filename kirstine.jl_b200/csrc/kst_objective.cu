@@ -141,13 +141,11 @@ __global__ void k_sum_fixed(const double *__restrict__ x, int64_t n, double *__r
 
 int kst_sum_fixed(kst_problem *h, const double *d_x, int64_t n, double *host_out)
 {
-    double *d_out = nullptr;
-    KST_CUDA(cudaMalloc(&d_out, sizeof(double)));
+    double *d_out = (double *)((char *)h->d_flag + 8);  // the handle's scratch double: no allocation per call
     k_sum_fixed<<<1, 1024, 0, h->stream>>>(d_x, n, d_out);
     KST_CUDA(cudaGetLastError());
     KST_CUDA(cudaMemcpyAsync(host_out, d_out, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     KST_CUDA(cudaStreamSynchronize(h->stream));
-    KST_CUDA(cudaFree(d_out));
     return KST_OK;
 }
 
