@@ -583,16 +583,32 @@ class Pso:
 
 
 class PsoState:
-    """PsoState (src/pso.jl:63-76) as copied out of the device."""
+    """PsoState (src/pso.jl:63-76) as copied out of the device.  x, p (lists of DesignMeasure) and g are built from
+    the raw arrays on first access: wrapping a whole swarm in Python objects costs more than a short PSO run."""
 
     def __init__(self, st):
-        S = len(st["fx"])
-        self.x = [DesignMeasure(st["x_pts"][i], _renorm(st["x_w"][i])) for i in range(S)]
-        self.p = [DesignMeasure(st["p_pts"][i], _renorm(st["p_w"][i])) for i in range(S)]
-        self.g = DesignMeasure(st["g_pts"], _renorm(st["g_w"]))
         self.v_atoms, self.v_weights = st["v_pts"], st["v_w"]
         self.fx, self.fp, self.fg, self.n_eval = st["fx"], st["fp"], st["fg"], st["n_eval"]
         self.raw = st
+        self._x = self._p = self._g = None
+
+    @property
+    def x(self):
+        if self._x is None:
+            self._x = [DesignMeasure(self.raw["x_pts"][i], _renorm(self.raw["x_w"][i])) for i in range(len(self.fx))]
+        return self._x
+
+    @property
+    def p(self):
+        if self._p is None:
+            self._p = [DesignMeasure(self.raw["p_pts"][i], _renorm(self.raw["p_w"][i])) for i in range(len(self.fx))]
+        return self._p
+
+    @property
+    def g(self):
+        if self._g is None:
+            self._g = DesignMeasure(self.raw["g_pts"], _renorm(self.raw["g_w"]))
+        return self._g
 
 
 def _renorm(w):
