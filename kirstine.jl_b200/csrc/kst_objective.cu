@@ -234,6 +234,10 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
         kst_set_error("objective: at most 2^29 draws per GPU (shard the prior sample over more GPUs)");
         return KST_ELIMIT;
     }
+    if (S > 65535 * KST_TILE_P) {  // gridDim.y holds the particle tiles
+        kst_set_error("objective: at most %d particles per call (split the swarm)", 65535 * KST_TILE_P);
+        return KST_ELIMIT;
+    }
     int n_blk = 1, tile_p = KST_TILE_P;
     const int tiles = kst_objective_grid(h, S, &n_blk, &tile_p);
     int rc = kst_ensure_partials(h, (size_t)S * n_blk);

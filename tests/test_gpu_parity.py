@@ -401,3 +401,13 @@ def test_objective_exponent_range_paths():
     tt[5, 0] = 60.0
     ptt, wt = wl.jittered_swarm(12, 5, 0.0, 48.0, seed=3, log_lo=0.05)
     close(H(3, [1.0], tt, ub=(48.0,)).objective_batch(ptt, wt), O(3, [1.0], tt).objective_batch(ptt, wt), 1e-9)
+
+
+def test_objective_swarm_size_limit():
+    """More particle tiles than gridDim.y can hold is refused with KST_ELIMIT, not launched."""
+    h = H(1, [1.0], wl.emax_prior(4), ub=(10.0,))
+    S = 65535 * 8 + 1
+    with pytest.raises(kb.EngineError, match="at most"):
+        h.objective_batch(np.full((S, 1, 1), 1.0), np.ones((S, 1)))
+    big = h.objective_batch(np.full((65535 * 8, 1, 1), 1.0), np.ones((65535 * 8, 1)))     # the limit itself runs
+    assert np.all(big == -np.inf)                                                        # one point, three parameters
