@@ -231,7 +231,7 @@ def test_objective_reproducible_bitwise():
 
 
 def test_objective_full_size_properties():
-    """BASELINE config-5 sized prior (10^6 draws): size-independent properties instead of the oracle."""
+    """BASELINE config-5 sized prior (10^6 draws): size-independent properties, and the oracle on a few particles."""
     th = wl.sigemax_prior(1_000_000, seed=5)
     pts, w = wl.jittered_swarm(16, 8, 0.0, 1.0, seed=1)
     full = H(2, [1.0], th).objective_batch(pts, w)
@@ -244,6 +244,10 @@ def test_objective_full_size_properties():
     # sigma only shifts the D objective by -r log sigma^2
     s = H(2, [2.0], th).objective_batch(pts, w)
     np.testing.assert_allclose(s, full - 4 * np.log(4.0), rtol=1e-12)
+    # the oracle itself on the full prior (all host threads; a second of CPU time for these 16 particles)
+    import os
+    want = O(2, [1.0], th).objective_batch(pts, w, nthreads=os.cpu_count() or 1)
+    np.testing.assert_allclose(full, want, rtol=RTOL)
     # a bounded sample of the same prior agrees with the oracle
     sub = th[:4000]
     _parity(dict(model=2, mp=[1.0], theta=sub), H(2, [1.0], sub), O(2, [1.0], sub), pts, w, 0, None, 1)
