@@ -329,6 +329,29 @@ def test_gateaux_grid_config4_size():
     np.testing.assert_allclose(got[::50], want, rtol=RTOL, atol=RTOL * np.abs(want).max())
 
 
+def test_gateaux_grid_large_prior():
+    """The same grid against 10^5 draws (draw range split over the grid, chunks prefetched through registers): a
+    strided sample of directions against the oracle, and the whole grid against two half priors (linearity)."""
+    import os
+    th = wl.tpc_prior(100_000, seed=4)
+    pw = np.full(len(th), 1.0 / len(th))
+    h = H(4, [0.1], th, ub=(24.0,), m=3, cp=1)
+    o = O(ko.VU, [0.1, 3], th, m=3, cp=1)
+    at_p, at_w = [2.0, 8.0, 20.0], [0.3, 0.3, 0.4]
+    dirs = np.linspace(0, 24, 10_000)
+    assert not h.gateaux_prepare(at_p, at_w)
+    got = h.gateaux_eval(dirs)
+    want = o.gateauxderivative(at_p, at_w, dirs[::250], nthreads=os.cpu_count() or 1)
+    np.testing.assert_allclose(got[::250], want, rtol=RTOL, atol=RTOL * np.abs(want).max())
+    half = len(th) // 2
+    parts = []
+    for sl in (slice(0, half), slice(half, None)):
+        hh = H(4, [0.1], th[sl], pw=pw[sl], ub=(24.0,), m=3, cp=1)
+        assert not hh.gateaux_prepare(at_p, at_w)
+        parts.append(hh.gateaux_eval(dirs))
+    np.testing.assert_allclose(parts[0] + parts[1], got, rtol=1e-11, atol=1e-11 * np.abs(got).max())
+
+
 # ---- error behaviour of the boundary ----------------------------------------------------------------
 
 def test_abi_errors():
