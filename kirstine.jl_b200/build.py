@@ -17,7 +17,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 # per-file extras: the swarm move must round exactly like the scalar reference arithmetic
 EXTRA = {"kst_pso.cu": ["-fmad=false"]}
-SOURCES = ["kst_api.cu", "kst_objective.cu", "kst_obj_inst_a.cu", "kst_obj_inst_b.cu", "kst_obj_inst_c.cu", "kst_obj_inst_d.cu",
+SOURCES = ["kst_api.cu", "kst_comm.cu", "kst_objective.cu", "kst_obj_inst_a.cu", "kst_obj_inst_b.cu", "kst_obj_inst_c.cu", "kst_obj_inst_d.cu",
            "kst_obj_inst_e.cu", "kst_gateaux.cu", "kst_pso.cu"]
 
 

@@ -149,6 +149,9 @@ void kst_pso_free(kst_problem *h);
 int kst_launch_pso_init(kst_problem *h, const double *d_proto_pts, const double *d_proto_w, int P);
 int kst_launch_pso_move(kst_problem *h);
 int kst_launch_pso_best(kst_problem *h, int init, int trace_slot);
-// kst_api.cu
+// kst_comm.cu
 int kst_allreduce_sum(kst_problem *h, double *d_buf, size_t count);
+int kst_objective_allreduce(kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *d_fx);
+void kst_comm_release(kst_problem *h);
+// kst_api.cu
 int kst_ensure_partials(kst_problem *h, size_t n);
