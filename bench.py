@@ -256,6 +256,13 @@ def main():
         assert h.comm_peer_error() == 0, "peer exchange timed out"
     fx_check = pin_fx.numpy().copy()
     assert np.all(np.isfinite(fx_check[:1])), "prototype particle must have a finite objective"
+    if world > 1:
+        # the swarm replicas must have moved in lock-step and every rank must hold the same all-reduced objectives
+        st = h.pso_state()
+        mine = torch.from_numpy(np.concatenate([st["fx"], st["x_w"].ravel(), [st["fg"]], fx_check])).cuda()
+        everyone = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(everyone, mine)
+        assert all(torch.equal(everyone[0], t) for t in everyone), "ranks disagree on the swarm state"
 
     # ---- roofline of the dominant kernel (k_objective) ----------------------------------------------------
     peak_tf = kb.fp64_peak_probe(local)
