@@ -92,10 +92,13 @@ __device__ __forceinline__ bool kst_ldlt(const double *M, double (&L)[R][R], dou
 //   otherwise: LDL' pivots.
 // Positive definite <=> all leading minors (equivalently all pivots) > 0 <=> sign bit of `signs` clear and
 // prod > 0; this is the reference's "potrf! succeeded and every U[i,i] > 0" (src/design-common.jl:213-220).
-template <int R, bool INV0>
+// CLOSED = false forces the pivot form: it is invariant under diagonal scaling of the matrix, which the cofactor
+// expansions are not -- needed for DT M^-1 DT' of a DeltaMethod transformation, whose rows carry the scales of DT
+// (the column-scaled Mt of the Identity path is well scaled by construction).
+template <int R, bool INV0, bool CLOSED = true>
 __device__ __forceinline__ void kst_det_signs(const double *M, double inv0, double &prod, int &signs)
 {
-    if (R == 4 && INV0) {
+    if (CLOSED && R == 4 && INV0) {
         const double t1 = M[kst_pidx<R>(0, 1)] * inv0, t2 = M[kst_pidx<R>(0, 2)] * inv0, t3 = M[kst_pidx<R>(0, 3)] * inv0;
         const double s00 = fma(-t1, M[kst_pidx<R>(0, 1)], M[kst_pidx<R>(1, 1)]);
         const double s01 = fma(-t1, M[kst_pidx<R>(0, 2)], M[kst_pidx<R>(1, 2)]);
@@ -109,7 +112,7 @@ __device__ __forceinline__ void kst_det_signs(const double *M, double inv0, doub
         const double m3 = fma(s22, m2, fma(s02, c02, -(s12 * c12)));
         prod = M[kst_pidx<R>(0, 0)] * m3;
         signs = __double2hiint(s00) | __double2hiint(m2) | __double2hiint(m3);
-    } else if (R == 3 && INV0) {
+    } else if (CLOSED && R == 3 && INV0) {
         const double t1 = M[kst_pidx<R>(0, 1)] * inv0, t2 = M[kst_pidx<R>(0, 2)] * inv0;
         const double s00 = fma(-t1, M[kst_pidx<R>(0, 1)], M[kst_pidx<R>(1, 1)]);
         const double s01 = fma(-t1, M[kst_pidx<R>(0, 2)], M[kst_pidx<R>(1, 2)]);
@@ -117,7 +120,7 @@ __device__ __forceinline__ void kst_det_signs(const double *M, double inv0, doub
         const double m2 = fma(s00, s11, -(s01 * s01));
         prod = M[kst_pidx<R>(0, 0)] * m2;
         signs = __double2hiint(s00) | __double2hiint(m2);
-    } else if (R == 3) {
+    } else if (CLOSED && R == 3) {
         const double a = M[kst_pidx<R>(0, 0)], b = M[kst_pidx<R>(0, 1)], c = M[kst_pidx<R>(0, 2)];
         const double d = M[kst_pidx<R>(1, 1)], e = M[kst_pidx<R>(1, 2)], f = M[kst_pidx<R>(2, 2)];
         const double m2 = fma(a, d, -(b * b));
@@ -234,7 +237,7 @@ __device__ __forceinline__ double kst_criterion(const double *M, const double *a
         }
     double prod2;
     int signs2;
-    kst_det_signs<TT, false>(Mi, 0.0, prod2, signs2);
+    kst_det_signs<TT, false, false>(Mi, 0.0, prod2, signs2);
     // log det of the *inverse*: the sign flips unless it is -Inf (src/criterion-d.jl:35-37)
     const double ldi = kst_log_checked(prod2, signs2, tab);
     if (CRIT == 2) return ldi == -KST_INF ? 0.0 : kst_exp(-ldi * (1.0 / TT), tab);
