@@ -111,3 +111,56 @@ def test_random_shapes_vector_units(seed):
     rf.assert_parity(got[fin], want[fin],
                      lambda i: rf.objective(model, mp, pts[fin][i], w[fin][i], th, pw, crit=crit, dt=dt, m=m, cov=cov),
                      rtol=RTOL)
+
+
+@pytest.mark.parametrize("seed", range(int(os.environ.get("KST_FUZZ_CASES", "24")) // 2))
+def test_random_shapes_extension_seams(seed):
+    """Logistic families, the regularised normal approximation and the Dexp criterion on random shapes (no 80-bit
+    referee for these: well-separated designs, engine against oracle at the 1e-10 bar, Gateaux grid included)."""
+    import kirstine_b200 as kb
+    rng = np.random.default_rng(9000 + seed)
+    kind = seed % 3
+    N = int(rng.choice([1, 5, 33, 129, 400]))
+    S = int(rng.choice([1, 2, 8, 11, 24]))
+    crit = int(rng.integers(0, 3))
+    pw = rng.dirichlet(np.ones(N)) if rng.random() < 0.5 else np.full(N, 1.0 / N)
+    reg = None
+    if kind == 0:      # LinLogReg, d = 1..3
+        d = int(rng.integers(1, 4))
+        model, mp, r = 6, [0.0], d + 1
+        th = np.column_stack([rng.normal(-1.0, 0.5, N)] + [rng.normal(1.5, 0.7, N) for _ in range(d)])
+        lb, ub = [0.0] * d, [1.0] * d
+        K = int(rng.integers(r + 1, r + 6))
+        pts = rng.uniform(0, 1, (S, K, d))
+        w = rng.dirichlet(np.full(K, 4.0), S)
+        o = ko.Problem(ko.LINLOGREG, [], th, pw, crit=crit, d=d)
+    elif kind == 1:    # SinLogReg
+        model, mp, r, d = 7, [0.0], 3, 1
+        th = np.column_stack([rng.uniform(0.5, 1.5, N), rng.uniform(1.0, 2.0, N), rng.uniform(0.0, 0.5, N)])
+        lb, ub = [0.0], [1.0]
+        K = int(rng.integers(4, 9))
+        pts, w = wl.jittered_swarm(S, K, 0.0, 1.0, seed=seed)
+        o = ko.Problem(ko.SINLOGREG, [], th, pw, crit=crit, d=1)
+    else:              # regularised sigmoid Emax / TPC
+        sig = rng.random() < 0.5
+        model, mp, r, d = (2, [0.9], 4, 1) if sig else (3, [1.2], 3, 1)
+        th = wl.sigemax_prior(N, seed=seed) if sig else wl.tpc_prior(N, seed=seed)
+        lb, ub = [0.0], [1.0 if sig else 48.0]
+        K = int(rng.integers(2, 8))                 # fewer points than parameters are fine with R
+        pts, w = wl.jittered_swarm(S, K, 0.0, ub[0], seed=seed, log_lo=None if sig else 0.05)
+        q = rng.normal(size=(r, r))
+        reg = 10.0 ** rng.uniform(-4, -1) * (q @ q.T + r * np.eye(r))
+        o = ko.Problem(model, mp, th, pw, crit=crit).set_regularization(reg)
+    h = kb.ProblemHandle(model, mp, th, pw, crit, None, lb, ub)
+    if reg is not None:
+        h.set_regularization(reg)
+    got, want = h.objective_batch(pts, w), o.objective_batch(pts, w)
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin)
+    np.testing.assert_allclose(got[fin], want[fin], rtol=1e-9)
+    if fin.any():
+        s0 = int(np.flatnonzero(fin)[0])
+        dirs = rng.uniform(np.array(lb) + 0.01, ub, (29, len(lb)))
+        if not h.gateaux_prepare(pts[s0], w[s0]):
+            wg = o.gateauxderivative(pts[s0], w[s0], dirs)
+            np.testing.assert_allclose(h.gateaux_eval(dirs), wg, rtol=1e-8, atol=1e-9 * np.abs(wg).max())
