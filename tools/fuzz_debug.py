@@ -33,3 +33,14 @@ for seed in [int(a) for a in sys.argv[1:]]:
                 M = o.informationmatrix(pts[i], w[i], j); conds.append(np.linalg.cond(M))
             print("  particle", i, "got", got[i], "oracle", want[i], "referee", float(ref), "rel err engine %.1e oracle %.1e" % (abs(got[i]-ref)/abs(ref), abs(want[i]-ref)/abs(ref)),
                   "live rows", int((w[i] > 0).sum()), "zeros", int((pts[i,:,0]==0).sum()), "max cond %.1e" % max(conds))
+    fin = np.isfinite(want) & np.isfinite(got)
+    if fin.any():
+        s0 = int(np.flatnonzero(fin)[0])
+        dirs = np.linspace(ub * 0.01, ub, 37)
+        if not h.gateaux_prepare(pts[s0], w[s0]):
+            gd, wg = h.gateaux_eval(dirs), o.gateauxderivative(pts[s0], w[s0], dirs)
+            ref = np.array([float(rf.gateaux(model, mp, pts[s0], w[s0], [z], th, pw, crit=crit, dt=dt)[0]) for z in dirs])
+            sc = np.abs(ref).max()
+            conds = [np.linalg.cond(o.informationmatrix(pts[s0], w[s0], j)) for j in range(min(N, 50))]
+            print("  gateaux at particle", s0, "max err engine %.1e oracle %.1e (relative to max |gd| %.3g)  max cond %.1e  live rows %d"
+                  % (np.abs(gd - ref).max() / sc, np.abs(wg - ref).max() / sc, sc, max(conds), int((w[s0] > 0).sum())))
