@@ -266,3 +266,41 @@ def test_pso_long_run_in_pieces_equals_one_run():
     g = kb.DesignMeasure(s1["g_pts"], s1["g_w"] / s1["g_w"].sum())
     assert not h1.gateaux_prepare(g.points, g.weights)
     assert h1.gateaux_eval(np.linspace(0, 1, 501)).max() < 1e-2
+
+
+@pytest.mark.parametrize("family", ["tpc", "vu", "dtr"])
+def test_direction_pso_trajectory_matches_oracle(family):
+    """The Exchange strategy's inner swarm (src/solve-exchange.jl:133-149): one-point directions, objective = Gateaux
+    derivative at the prepared candidate.  Engine state against the oracle's on the shared random stream."""
+    import kirstine_b200 as kb
+    if family == "tpc":
+        model, mp, omp, th, lb, ub, kw, okw = 3, [1.0], [1.0], wl.tpc_prior(150, seed=8), [0.0], [48.0], {}, {}
+        cand = ([[0.3], [2.0], [20.0]], [0.3, 0.3, 0.4])
+    elif family == "vu":
+        model, mp, omp, th, lb, ub = 4, [0.1], [0.1, 3], wl.tpc_prior(150, seed=9), [0.0], [24.0]
+        kw, okw = dict(m=3, cp_id=1), dict(m=3, cp_id=ko.CP_EQUITIME)
+        cand = ([[2.0], [8.0], [20.0]], [0.3, 0.3, 0.4])
+    else:
+        model, mp, omp, th, lb, ub = 5, [1.0], [1.0], wl.dtr_prior(100, seed=3), [0.0, 0.0], [100.0, 24.0]
+        kw, okw = dict(m=1, cp_id=2), dict(m=1, d=2, cp_id=2)
+        pts, w = wl.jittered_swarm_nd(1, 7, lb, ub, seed=4)
+        cand = (pts[0], w[0])
+    pw = np.full(len(th), 1.0 / len(th))
+    h = kb.ProblemHandle(model, mp, th, pw, 0, None, lb, ub, **kw)
+    o = ko.Problem(model, omp, th, pw, **okw)
+    assert not h.gateaux_prepare(*cand)
+    gconst = o.gateaux_constants(*cand)
+    S = 25
+    protos = np.asarray(cand[0], float).reshape(-1, 1, len(lb))[:3]
+    pwts = np.ones((len(protos), 1))
+    assert h.pso_init(S, 1, protos, pwts, fixw=[0], fixp=[0], seed=5, mode=kb._ffi.PSO_MODE_GATEAUX) == 0
+    po = ko.Pso(o, S, 1, lb, ub, seed=5, mode=1, gconst=gconst)
+    po.init(protos, pwts)
+    for it in range(8):
+        a, b = h.pso_state(), po.state()
+        for key in ("x_pts", "v_pts", "p_pts", "g_pts"):
+            np.testing.assert_allclose(a[key], b[key], rtol=1e-11, atol=1e-13, err_msg="%s at tick %d" % (key, it))
+        np.testing.assert_allclose(a["fx"], b["fx"], rtol=1e-8, atol=1e-9 * np.abs(b["fx"]).max())
+        assert np.all(a["x_w"] == 1.0)
+        h.pso_run(1)
+        po.tick()
