@@ -120,6 +120,185 @@ def run_reference(args):
     }))
 
 
+# ------------------------------------------------------------------------------------------------------------------
+# the other BASELINE.json configs at their own sizes, measured in the same run at N = 1
+# ------------------------------------------------------------------------------------------------------------------
+FLOPS = {"1": 107.0, "1b": 441.0, "2": 373.0, "3": 221.0, "4": 123.0}   # SURVEY.md 8(d), per unit of work
+
+
+def _ev_ms(torch, stream, fn, reps, flush=None):
+    """Mean device time of fn() over reps calls, CUDA events on the engine's stream, L2 flushed in between."""
+    evs = []
+    for _ in range(reps):
+        if flush is not None:
+            with torch.cuda.stream(stream):
+                flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        fn()
+        e1.record(stream)
+        evs.append((e0, e1))
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in evs) / reps
+
+
+def bench_objective_config(kb, torch, name, desc, model, mp, theta, ub, K, S, iters, peak_tf, flush, crit=0, dt=None,
+                           kernel=""):
+    n = len(theta)
+    h = kb.ProblemHandle(model, mp, theta, np.full(n, 1.0 / n), crit, dt, [0.0], [ub])
+    stream = torch.cuda.ExternalStream(h.stream())
+    pts, w = wl.random_swarm(S, K, 0.0, ub, seed=5)
+    pin_pts, pin_w = torch.from_numpy(pts.copy()).pin_memory(), torch.from_numpy(w.copy()).pin_memory()
+    pin_fx = torch.empty(S, dtype=torch.float64).pin_memory()
+    e2e_fn = lambda: h.objective_batch_raw(S, K, pin_pts.data_ptr(), pin_w.data_ptr(), pin_fx.data_ptr())  # noqa: E731
+    for _ in range(3):
+        e2e_fn()
+    reps = 20
+    h.profile_enable(True)
+    t0 = time.perf_counter()
+    e2e_ms = _ev_ms(torch, stream, e2e_fn, reps, flush)
+    e2e_wall_ms = (time.perf_counter() - t0) * 1e3 / reps
+    kern_ms, launches = h.profile_read()
+    h.profile_enable(False)
+    kern_ms /= max(1, launches)
+    # the swarm on the device: `iters` PSO iterations enqueued in one call, timed as a whole
+    assert h.pso_init(S, K, pts[0], w[0], seed=5) == 0
+    h.pso_run(3)
+    pso_ms = _ev_ms(torch, stream, lambda: h.pso_run_async(iters), 3) / iters
+    h.synchronize()
+    units = float(S) * n
+    ach = FLOPS[name] * units / (kern_ms * 1e-3) / 1e12
+    out = {"cfg": name, "workload": desc, "unit": UNIT, "units_per_evaluation": units,
+           "value": units / (pso_ms * 1e-3), "pso_iteration_us": pso_ms * 1e3, "pso_iterations_timed": 3 * iters,
+           "kernel": kernel, "kernel_ms": kern_ms, "kernel_launches_timed": launches,
+           "flops_per_unit": FLOPS[name], "achieved_tflops": ach, "frac": ach / peak_tf if peak_tf else None,
+           "e2e": {"value": units / (e2e_ms * 1e-3), "unit": UNIT, "ms_per_call": e2e_ms, "wall_ms_per_call": e2e_wall_ms,
+                   "h2d_bytes_per_call": int(pin_pts.numel() * 8 + pin_w.numel() * 8), "d2h_bytes_per_call": int(S * 8),
+                   "call": "kst_objective_batch (host buffers, pinned)"},
+           "l2": "flushed before every timed evaluation call; not inside a pso_run (the iterations of one solve re-read "
+                 "the same prior sample, as in the reference)"}
+    h.close()
+    return out
+
+
+def bench_gateaux_config(kb, torch, name, desc, theta, G, peak_tf, flush):
+    n = len(theta)
+    h = kb.ProblemHandle(kb._ffi.MODEL_VU, [0.1], theta, np.full(n, 1.0 / n), 0, None, [0.0], [24.0], m=3,
+                         cp_id=kb._ffi.CP_EQUITIME)
+    stream = torch.cuda.ExternalStream(h.stream())
+    dirs = np.linspace(0.0, 24.0, G)
+    t0 = time.perf_counter()
+    assert not h.gateaux_prepare([2.0, 8.0, 20.0], [0.3, 0.3, 0.4])
+    prep_first_ms = (time.perf_counter() - t0) * 1e3
+    t0 = time.perf_counter()
+    for _ in range(5):
+        h.gateaux_prepare([2.0, 8.0, 20.0], [0.3, 0.3, 0.4])
+    prep_ms = (time.perf_counter() - t0) * 1e3 / 5
+    for _ in range(3):
+        h.gateaux_eval(dirs)
+    reps = 20
+    h.profile_enable(True)
+    t0 = time.perf_counter()
+    e2e_ms = _ev_ms(torch, stream, lambda: h.gateaux_eval(dirs), reps, flush)
+    e2e_wall_ms = (time.perf_counter() - t0) * 1e3 / reps
+    kern_ms, launches = h.profile_read()
+    h.profile_enable(False)
+    kern_ms /= max(1, launches)
+    units = float(G) * n
+    ach = FLOPS["4"] * units / (kern_ms * 1e-3) / 1e12
+    out = {"cfg": name, "workload": desc, "unit": "(direction x draw)/s", "units_per_evaluation": units,
+           "value": units / (kern_ms * 1e-3), "kernel": "k_gateaux_eval<KstVu,3>", "kernel_ms": kern_ms,
+           "kernel_launches_timed": launches, "flops_per_unit": FLOPS["4"], "achieved_tflops": ach,
+           "frac": ach / peak_tf if peak_tf else None,
+           "gateaux_prepare_ms": prep_ms, "gateaux_prepare_first_call_ms": prep_first_ms,
+           "e2e": {"value": units / (e2e_ms * 1e-3), "unit": "(direction x draw)/s", "ms_per_call": e2e_ms,
+                   "wall_ms_per_call": e2e_wall_ms, "h2d_bytes_per_call": int(G * 8), "d2h_bytes_per_call": int(G * 8),
+                   "call": "kst_gateaux_eval (host buffers)"},
+           "l2": "flushed before every timed call"}
+    h.close()
+    return out
+
+
+def bench_solves(kb):
+    """Whole-solve wall time through the public API (second run of each, after CUDA context and module load)."""
+    out = {}
+    dp1 = kb.DesignProblem(criterion=kb.DCriterion(), region=kb.DesignInterval(dose=(0, 10)), model=kb.EmaxModel(1),
+                           covariate_parameterization=kb.CopyDose(), prior_knowledge=kb.PriorSample(wl.emax_prior(1000)))
+    st1 = kb.DirectMaximization(optimizer=kb.Pso(swarmsize=50, iterations=100),
+                                prototype=kb.equidistant_design(kb.region(dp1), 3))
+    dp1b = kb.DesignProblem(criterion=kb.DCriterion(), region=kb.DesignInterval(dose=(0, 1)), model=kb.SigEmaxModel(1),
+                            covariate_parameterization=kb.CopyDose(),
+                            prior_knowledge=kb.PriorSample(wl.sigemax_prior(1000)))
+    st1b = kb.DirectMaximization(optimizer=kb.Pso(swarmsize=100, iterations=50),
+                                 prototype=kb.equidistant_design(kb.region(dp1b), 8))
+    dp4 = kb.DesignProblem(criterion=kb.DCriterion(), region=kb.DesignInterval(delta=(0, 24)), model=kb.VUMod(0.1, 3),
+                           covariate_parameterization=kb.EquiTime(),
+                           prior_knowledge=kb.PriorSample(wl.tpc_prior(1000, seed=4)))
+    st4 = kb.Exchange(optimizer_direction=kb.Pso(swarmsize=25, iterations=10),
+                      optimizer_weight=kb.Pso(swarmsize=25, iterations=10), steps=8,
+                      candidate=kb.uniform_design([[2.0], [8.0], [20.0]]))
+    for key, dp, st in (("1", dp1, st1), ("1b", dp1b, st1b), ("4", dp4, st4)):
+        kb.seed(1)
+        kb.solve(dp, st)
+        best = None
+        for _ in range(3):
+            kb.seed(1)
+            t0 = time.perf_counter()
+            d, _ = kb.solve(dp, st)
+            ms = (time.perf_counter() - t0) * 1e3
+            best = ms if best is None else min(best, ms)
+        out[key] = {"solve_wall_ms": best, "objective_at_solution": kb.objective(d, dp)}
+    return out
+
+
+def bench_configs(kb, torch, peak_tf, flush):
+    res = []
+    res.append(bench_objective_config(
+        kb, torch, "1", "cfg1: Emax r=3, K=3 on [0,10], D/Identity, 1e3 draws (seed 1), Pso 50 x 100",
+        kb._ffi.MODEL_EMAX, [1.0], wl.emax_prior(1000), 10.0, 3, 50, 100, peak_tf, flush,
+        kernel="k_objective<KstEmax,D,Identity,uniform>"))
+    res.append(bench_objective_config(
+        kb, torch, "1b", "cfg1b (tutorial): sigmoid Emax r=4, K=8 on [0,1], D/Identity, 1e3 draws (seed 31415), Pso 100 x 50",
+        kb._ffi.MODEL_SIGEMAX, [1.0], wl.sigemax_prior(1000), 1.0, 8, 100, 50, peak_tf, flush,
+        kernel="k_objective<KstSigEmax,D,Identity,uniform>"))
+    th = wl.sigemax_prior(10_000, seed=2)
+    res.append(bench_objective_config(
+        kb, torch, "2", "cfg2: sigmoid Emax, K=6, A/DeltaMethod->ED90 (t=1), 1e4 draws (seed 2), Pso 256 x 100",
+        kb._ffi.MODEL_SIGEMAX, [1.0], th, 1.0, 6, 256, 100, peak_tf, flush, crit=kb._ffi.CRIT_A,
+        dt=wl.ded90_jacobians(th), kernel="k_objective<KstSigEmax,A,DeltaMethod t=1>"))
+    res.append(bench_objective_config(
+        kb, torch, "3", "cfg3: one-compartment TPC r=3, K=6 on [0,48], D/Identity, 1e5 draws (seed 3), Pso 256 x 100",
+        kb._ffi.MODEL_TPC, [1.0], wl.tpc_prior(100_000), 48.0, 6, 256, 100, peak_tf, flush,
+        kernel="k_objective<KstTpc,D,Identity,uniform>"))
+    res.append(bench_gateaux_config(
+        kb, torch, "4", "cfg4: vector unit m=3 (VUMod + EquiTime) on [0,24], D/Identity, Gateaux derivative over a 1e4-point "
+        "grid x 1e3 draws (seed 4)", wl.tpc_prior(1000, seed=4), 10_000, peak_tf, flush))
+    res.append(bench_gateaux_config(
+        kb, torch, "4L", "cfg4 shape at 1e5 draws: the same 1e4-point grid", wl.tpc_prior(100_000, seed=4), 10_000,
+        peak_tf, flush))
+    solves = bench_solves(kb)
+    for r in res:
+        if r["cfg"] in solves:
+            r["solve"] = dict(solves[r["cfg"]], api="kirstine_b200.solve (" + ("Exchange, 8 steps of Pso(25,10) x 2"
+                                                                              if r["cfg"] == "4" else "DirectMaximization") + ")")
+    return res
+
+
+def oracle_parity_check(theta, pts, w, fx, n_check=8):
+    """After the timed region: the engine's objective values for a few particles of the e2e swarm against the CPU
+    oracle on the FULL prior sample (the oracle as the checker, outside every timed region)."""
+    import oracle as ko
+    idx = np.unique(np.linspace(0, len(fx) - 1, n_check).astype(int))
+    want = ko.Problem(ko.SIGEMAX, [1.0], theta).objective_batch(pts[idx], w[idx], nthreads=os.cpu_count() or 1)
+    got = fx[idx]
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin), "engine and oracle disagree on which particles are singular"
+    rel = np.abs(got[fin] - want[fin]) / np.abs(want[fin])
+    return {"n": int(len(idx)), "n_finite": int(fin.sum()), "max_rel": float(rel.max()) if fin.any() else 0.0,
+            "tolerance": 1e-10, "against": "oracle/kirstine_oracle.c on all %d draws, particles %s of the e2e swarm"
+                                           % (len(theta), idx.tolist())}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -129,6 +308,7 @@ def main():
     ap.add_argument("--draws", type=int, default=N_DRAWS, help="override the prior size (debugging only)")
     ap.add_argument("--swarm", type=int, default=SWARM)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip the `configs` array (the other BASELINE configs)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -277,24 +457,32 @@ def main():
     kern_avg_ms = kern_ms / max(1, kern_launches)
     achieved_tf = FLOPS_PER_UNIT * units_per_launch / (kern_avg_ms * 1e-3) / 1e12
     alg_bytes = BYTES_PER_DRAW * float(j1 - j0) * (S / 8.0)  # each 8-particle tile streams the shard once
-    traffic = None  # DRAM bytes per launch from the committed ncu capture of this kernel (cannot be measured live)
+    static_ms = e2e_kern_ms / max(1, e2e_kern_launches)
+    static_tf = FLOPS_PER_UNIT * units_per_launch / (static_ms * 1e-3) / 1e12
+    traffic, traffic_src = None, None  # DRAM bytes per launch from the committed ncu capture (cannot be measured live)
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("k_objective_cfg5_dram_bytes_per_launch")
+            tj = json.load(f)
+        traffic = tj.get("k_objective_cfg5_dram_bytes_per_launch")
+        traffic_src = {k: tj.get(k) for k in ("round", "commit", "capture")}
     except OSError:
         pass
+    # Headline fraction = the launch in which every particle carries all 8 rows (the e2e leg's static swarm): the flop
+    # count charges 8 rows per particle, and in the PSO steps particles clamped to dose 0 legitimately skip that row.
     roofline = {
-        "bound": "fp64", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-        "frac": achieved_tf / peak_tf if peak_tf else None, "frac_of_nominal": achieved_tf / 37.2, "traffic": traffic,
-        "kernel": "k_objective<KstSigEmax,D,Identity>", "kernel_ms": kern_avg_ms, "launches_timed": kern_launches,
-        "flops_per_unit": FLOPS_PER_UNIT,
+        "bound": "fp64", "achieved": static_tf, "peak": peak_tf, "unit": "TFLOP/s",
+        "frac": static_tf / peak_tf if peak_tf else None, "frac_of_nominal": static_tf / 37.2, "traffic": traffic,
+        "traffic_source": traffic_src,
+        "kernel": "k_objective<KstSigEmax,D,Identity,uniform>", "kernel_ms": static_ms,
+        "launches_timed": e2e_kern_launches, "flops_per_unit": FLOPS_PER_UNIT,
+        "measured_on": "static swarm of the e2e leg (all 8 rows live in every particle)",
         "peak_source": "DFMA micro-kernel measured in this run (MEASURED_PEAKS.json has no FP64 figure; "
                        "nominal 148 SM x 64 lanes x 2 x 1.965 GHz = 37.2)",
-        "static_swarm": {"kernel_ms": e2e_kern_ms / max(1, e2e_kern_launches),
-                         "achieved": FLOPS_PER_UNIT * units_per_launch / (e2e_kern_ms / max(1, e2e_kern_launches) * 1e-3) / 1e12,
-                         "note": "same kernel on the e2e leg's fixed initial swarm (every particle keeps all 8 rows; in the "
-                                 "PSO steps particles clamped to dose 0 drop that row, which the algorithmic count ignores)"},
-        "hbm": {"algorithmic_gbs": alg_bytes / (kern_avg_ms * 1e-3) / 1e9, "peak_gbs": hbm_peak,
+        "pso_step": {"kernel_ms": kern_avg_ms, "achieved": achieved_tf, "frac": achieved_tf / peak_tf if peak_tf else None,
+                     "launches_timed": kern_launches,
+                     "note": "same kernel inside the timed PSO steps: particles sitting on dose 0 drop that row, the "
+                             "flop count still charges 8 rows, so this figure overstates"},
+        "hbm": {"algorithmic_gbs": alg_bytes / (static_ms * 1e-3) / 1e9, "peak_gbs": hbm_peak,
                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                 "note": "served from L2 (shard <= 24 MB); HBM is not the bound"},
     }
@@ -303,6 +491,13 @@ def main():
         if world > 1:
             dist.destroy_process_group()
         return
+
+    # the N-GPU result against the CPU oracle on the full prior (rank 0, outside every timed region)
+    parity = oracle_parity_check(theta, pts, w, fx_check)
+    assert parity["max_rel"] <= parity["tolerance"], parity
+    configs = None
+    if world == 1 and not args.no_configs and args.draws == N_DRAWS and args.swarm == SWARM:
+        configs = bench_configs(kb, torch, peak_tf, flush)
 
     cpu = None
     if world == 1 and not args.no_cpu:
@@ -337,6 +532,8 @@ def main():
         "gpu_launches": int((3 if world == 1 else 4) * args.steps),
         "roofline": roofline,
         "cpu_baseline": cpu,
+        "parity_check": parity,
+        "configs": configs,
     }
     print(json.dumps(out))
     if world > 1:

@@ -181,7 +181,10 @@ KST_API int kst_objective_batch_device(kst_problem *h, int S, int K, const doubl
  * loop that cannot take the device-wide synchronisation of cudaMalloc / cudaFree): the per-CTA partial
  * sums live in a fixed 2 MiB array inside the library image, which every GPU that loads the library
  * keeps until exit.  At most 4096 particles per call (KST_ELIMIT beyond).  The first call on each GPU
- * looks up the array's device address and should come before any stream capture.  Calls that overlap
+ * looks up the array's device address and should come before any stream capture; since the CUDA runtime
+ * loads each kernel on its first launch and the evaluation kernel is compiled per (model family, criterion,
+ * transformation), make one warm-up call per such combination in use, not only per GPU.  At most 2^29 draws
+ * per handle, like the other entry points (KST_ELIMIT beyond).  Calls that overlap
  * on one GPU race on the shared array: serialise them.  Asynchronous on the handle's stream; sums only
  * the draws held by this handle (no collective even when a communicator is attached).
  */

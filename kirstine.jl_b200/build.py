@@ -29,7 +29,7 @@ def _newer(target, deps):
 
 
 def _headers():
-    hs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    hs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h", ".inc"))]
     hs.append(os.path.join(os.path.dirname(HERE), "include", "kirstine_b200.h"))
     hs.append(os.path.abspath(__file__))
     return hs

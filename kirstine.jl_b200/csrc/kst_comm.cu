@@ -230,6 +230,11 @@ extern "C" int kst_comm_peer_handle(kst_problem *h, int nranks, int rank, void *
     }
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     KST_CUDA(cudaSetDevice(h->device));
+    // setting a group up again on a live handle: unmap the previous group's blocks first
+    if (h->peer_ready) {
+        const int rc = kst_comm_peer_close(h);
+        if (rc) return rc;
+    }
     if (!h->peer_local) KST_CUDA(cudaMalloc(&h->peer_local, sizeof(KstPeerBlock)));
     // a fresh exchange starts at sequence 0 on every rank: stale flags from an earlier group must not satisfy a wait
     KST_CUDA(cudaStreamSynchronize(h->stream));
@@ -247,6 +252,10 @@ extern "C" int kst_comm_peer_open(kst_problem *h, const void *handles)
 {
     if (!h || !handles || !h->peer_local) { kst_set_error("comm_peer_open before comm_peer_handle"); return KST_ESTATE; }
     KST_CUDA(cudaSetDevice(h->device));
+    for (int r = 0; r < KST_PEER_MAX; r++) {  // a second open without a close in between
+        if (r != h->rank && h->peer_map[r]) cudaIpcCloseMemHandle(h->peer_map[r]);
+        h->peer_map[r] = nullptr;
+    }
     for (int r = 0; r < h->nranks; r++) {
         if (r == h->rank) {
             h->peer_map[r] = h->peer_local;

@@ -223,20 +223,34 @@ int kst_objective_grid(const kst_problem *h, int S, int *n_blk, int *tile_p)
     return tiles;
 }
 
-int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *d_fx,
-                         int *defer_n_blk)
+// Argument and fixed-limit checks shared by every entry point that launches k_objective
+static int kst_objective_check(const kst_problem *h, int S, int K, const char *who)
 {
     if (S < 1 || K < 1 || K * h->m > KST_MAX_ROWS) {
-        kst_set_error("objective: need S >= 1, K >= 1, K*m <= %d (S=%d K=%d m=%d)", KST_MAX_ROWS, S, K, h->m);
+        kst_set_error("%s: need S >= 1, K >= 1, K*m <= %d (S=%d K=%d m=%d)", who, KST_MAX_ROWS, S, K, h->m);
         return KST_EINVAL;
     }
-    if (h->N > (1LL << 29)) {  // 32-bit element indices into the [NDC][ld] arrays inside the kernel
-        kst_set_error("objective: at most 2^29 draws per GPU (shard the prior sample over more GPUs)");
+    // 32-bit element indices into the per-draw SoA arrays inside the kernel: the widest array has
+    // max(NDC, r(r+1)/2 with a regularisation matrix) rows of ld entries
+    const int64_t rows = h->reg ? (int64_t)h->r * (h->r + 1) / 2 : 8;
+    if (h->N > (1LL << 29) || (int64_t)h->ld * rows > (1LL << 32)) {
+        kst_set_error("%s: at most 2^29 draws per GPU (2^32 / %lld with a regularisation matrix); shard the prior "
+                      "sample over more GPUs", who, (long long)rows);
         return KST_ELIMIT;
     }
     if (S > 65535 * KST_TILE_P) {  // gridDim.y holds the particle tiles
-        kst_set_error("objective: at most %d particles per call (split the swarm)", 65535 * KST_TILE_P);
+        kst_set_error("%s: at most %d particles per call (split the swarm)", who, 65535 * KST_TILE_P);
         return KST_ELIMIT;
+    }
+    return KST_OK;
+}
+
+int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *d_fx,
+                         int *defer_n_blk)
+{
+    {
+        const int rc0 = kst_objective_check(h, S, K, "objective");
+        if (rc0) return rc0;
     }
     int n_blk = 1, tile_p = KST_TILE_P;
     const int tiles = kst_objective_grid(h, S, &n_blk, &tile_p);
@@ -332,17 +346,18 @@ static int kst_noalloc_scratch_ptr(int device, double **out)
 // Same evaluation as kst_objective_batch_device (the same k_objective / k_obj_finish kernels), with the
 // partial sums kept in the static array above.  Calls no cudaMalloc, cudaFree or any other allocating
 // routine.  The first call on each GPU looks the array's device address up (cudaGetSymbolAddress); make
-// that first call before starting any stream capture.  Asynchronous on the handle's stream.  Only the
+// that first call before starting any stream capture.  The CUDA runtime also loads a kernel's code the first
+// time that kernel is launched, and k_objective is one kernel per (model family, criterion, transformation):
+// so warm up once per such combination you are going to use, not just once per GPU.  Asynchronous on the
+// handle's stream.  Only the
 // draws held by this handle are summed: no collective is issued even when a communicator is attached.
 extern "C" int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const double *d_points,
                                            const double *d_weights, double *d_fx)
 {
     if (!h) { kst_set_error("NULL problem handle"); return KST_EINVAL; }
     if (!d_points || !d_weights || !d_fx) { kst_set_error("objective_batch_noalloc: NULL buffer"); return KST_EINVAL; }
-    if (S < 1 || K < 1 || K * h->m > KST_MAX_ROWS) {
-        kst_set_error("objective_batch_noalloc: need S >= 1, K >= 1, K*m <= %d (S=%d K=%d m=%d)", KST_MAX_ROWS, S, K, h->m);
-        return KST_EINVAL;
-    }
+    int rc = kst_objective_check(h, S, K, "objective_batch_noalloc");
+    if (rc) return rc;
     if (S > KST_NOALLOC_MAX_SWARM) {
         kst_set_error("objective_batch_noalloc: swarm of %d particles exceeds the fixed limit of %d; "
                       "use kst_objective_batch_device, which allocates its scratch", S, KST_NOALLOC_MAX_SWARM);
@@ -350,7 +365,7 @@ extern "C" int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const d
     }
     KST_CUDA(cudaSetDevice(h->device));
     double *scratch = nullptr;
-    int rc = kst_noalloc_scratch_ptr(h->device, &scratch);
+    rc = kst_noalloc_scratch_ptr(h->device, &scratch);
     if (rc) return rc;
     int n_blk = 1, tile_p = KST_TILE_P;
     const int tiles = kst_objective_grid(h, S, &n_blk, &tile_p);

@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
                 kst_fisher<MF, CL>(M, rows_addr, na, sw, dcv, tab);
                 if (REG) {
 #pragma unroll
-                    for (int i = 0; i < KstPacked<R>::N; i++) M[i] += __ldg(prm.reg + (size_t)((unsigned)i * ld + (unsigned)j));
+                    for (int i = 0; i < KstPacked<R>::N; i++) M[i] += __ldg(prm.reg + ((size_t)i * ld + (size_t)j));
                 }
                 if (UNI) {
                     double det;

@@ -120,7 +120,10 @@ class DesignProblem:
 
     `device` / `comm` are engine options with no counterpart in the reference: the GPU to use and
     an optional (nranks, rank, unique_id) triple when the prior sample passed in is one shard of a
-    sample split over several processes.
+    sample split over several processes.  unique_id is the 128-byte NCCL id rank 0 made and every rank
+    received, or a callable that does that exchange and returns a fresh id on every call: an id serves
+    exactly one communicator, and efficiency / shannon_information on a non-D problem build a second
+    handle (the same problem under DCriterion) that needs its own.
     """
 
     def __init__(self, *, criterion, region, model, covariate_parameterization, prior_knowledge,
@@ -146,7 +149,8 @@ class DesignProblem:
             if isinstance(self.na, RegularizedFisherMatrix):
                 h.set_regularization(self.na.R)
             if self.comm is not None:
-                h.comm_init(*self.comm)
+                nranks, rank, uid = self.comm
+                h.comm_init(nranks, rank, uid() if callable(uid) else uid)
             self._handle_cache = h
         return self._handle_cache
 
@@ -201,6 +205,9 @@ def _as_doptimality_problem(dp):  # src/designproblem.jl:320-331
     if isinstance(dp.dc, DCriterion):
         return dp
     if getattr(dp, "_dopt", None) is None:
+        if dp.comm is not None and not callable(dp.comm[2]):
+            raise ValueError("the D-optimality twin of a multi-rank problem needs a communicator of its own: pass "
+                             "comm=(nranks, rank, make_unique_id) with a callable that returns a fresh broadcast id")
         dp._dopt = DesignProblem(criterion=DCriterion(), region=dp.dr, model=dp.m, covariate_parameterization=dp.cp,
                                  prior_knowledge=dp.pk, transformation=dp.trafo, normal_approximation=dp.na,
                                  device=dp.device, comm=dp.comm)

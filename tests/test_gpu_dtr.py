@@ -48,7 +48,7 @@ def test_dtr_objective_vs_oracle(case, crit):
     got, want = h.objective_batch(pts, w), o.objective_batch(pts, w, nthreads=8)
     pw = np.full(len(theta), 1.0 / len(theta))
     rf.assert_parity(got, want, lambda i: rf.objective(5, [1.0], pts[i], w[i], theta, pw, crit=crit, m=m, cov=cov),
-                     rtol=RTOL)
+                     rtol=RTOL, cond_fn=lambda i: rf.cond_max(5, [1.0], pts[i], w[i], theta, m, cov))
     assert np.isfinite(got).mean() >= 0.9
     M = h.informationmatrix(pts[0], w[0], 3)
     np.testing.assert_allclose(M, o.informationmatrix(pts[0], w[0], 3), rtol=1e-9, atol=1e-14 * np.abs(M).max())
@@ -65,7 +65,8 @@ def test_dtr_delta_method_and_gateaux():
         pts, w = wl.jittered_swarm_nd(6, 3, lb, ub, seed=5)
         got, want = h.objective_batch(pts, w), o.objective_batch(pts, w)
         rf.assert_parity(got, want, lambda i: rf.objective(5, [1.0], pts[i], w[i], theta, pw, crit=crit, dt=dt, m=m,
-                                                           cov=cov), rtol=RTOL)
+                                                           cov=cov), rtol=RTOL,
+                         cond_fn=lambda i: rf.cond_max(5, [1.0], pts[i], w[i], theta, m, cov))
     for case in ("copyboth", "equidistant"):
         h, o, cov, m, lb, ub = _pair(case, theta)
         at_p, at_w = wl.jittered_swarm_nd(1, 6 if m == 1 else 3, lb, ub, seed=9)
@@ -107,7 +108,7 @@ def test_dtr_maximum_unit_size():
     pts, w = wl.jittered_swarm_nd(9, 8, [0.0], [100.0], seed=11)
     got, want = h.objective_batch(pts, w), o.objective_batch(pts, w, nthreads=8)
     rf.assert_parity(got, want, lambda i: rf.objective(5, [1.0], pts[i], w[i], theta, pw, m=16, cov=(4, times)),
-                     rtol=RTOL)
+                     rtol=RTOL, cond_fn=lambda i: rf.cond_max(5, [1.0], pts[i], w[i], theta, 16, (4, times)))
     M = h.informationmatrix(pts[0], w[0], 5)
     np.testing.assert_allclose(M, o.informationmatrix(pts[0], w[0], 5), rtol=1e-9, atol=1e-14 * np.abs(M).max())
     dirs = np.linspace(0.0, 100.0, 300)

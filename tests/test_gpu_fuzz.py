@@ -20,14 +20,6 @@ FAMILIES = {   # name: (model id, model params, prior, ub, log_lo, r)
 }
 
 
-def _well_conditioned(o, pts_i, w_i, N, limit=1e6):
-    for j in range(0, N, max(1, N // 48)):
-        M = o.informationmatrix(pts_i, w_i, j)
-        if not np.all(np.isfinite(M)) or np.linalg.cond(M) > limit:
-            return False
-    return True
-
-
 def _orthonormal_rows(n, t, r, seed):
     rng = np.random.default_rng(seed)
     q = np.linalg.qr(rng.normal(size=(n, r, r)))[0]
@@ -65,17 +57,24 @@ def test_random_shapes_against_oracle(seed):
     h = kb.ProblemHandle(model, mp, th, pw, crit, dt, (0.0,), (ub,))
     o = ko.Problem(model, mp, th, pw, crit=crit, dt=dt)
     got, want = h.objective_batch(pts, w), o.objective_batch(pts, w)
-    assert np.array_equal(np.isnan(got), np.isnan(want))
     fin = np.isfinite(want) & np.isfinite(got)
     assert fin.mean() >= 0.5, (name, N, S, K, crit, t)
-    # the 1e-10 bar is a statement about designs double arithmetic can resolve: leave out particles whose information
-    # matrix has a condition number beyond 1e6 (saturated designs with a nearly redundant point), where the
-    # reference's own Cholesky route is only good to ~1e-9 as well (tools/fuzz_debug.py prints both errors)
-    fin &= np.array([_well_conditioned(o, pts[i], w[i], N) if fin[i] else False for i in range(S)])
+    # every particle goes through assert_parity: Inf / NaN classes must agree (unless the scaled condition number is
+    # beyond 1e12, where the side of "singular" a double lands on is rounding luck), the 1e-10 bar holds outright for
+    # cond < 1e6 (against the oracle or, where the oracle's own rounding is the larger error, the 80-bit referee), and
+    # beyond that the engine may be at most 8 x as far from the referee as the reference arithmetic itself
+    cond = {}
+
+    def cond_fn(i):
+        if i not in cond:
+            cond[i] = rf.cond_max(model, mp, pts[i], w[i], th)
+        return cond[i]
+
+    rf.assert_parity(got, want, lambda i: rf.objective(model, mp, pts[i], w[i], th, pw, crit=crit, dt=dt), rtol=RTOL,
+                     cond_fn=cond_fn)
+    fin &= np.array([cond_fn(i) < 1e6 if fin[i] else False for i in range(S)])
     if not fin.any():
         return
-    rf.assert_parity(got[fin], want[fin],
-                     lambda i: rf.objective(model, mp, pts[fin][i], w[fin][i], th, pw, crit=crit, dt=dt), rtol=RTOL)
     # Gateaux derivative at the first regular particle
     s0 = int(np.flatnonzero(fin)[0])
     dirs = np.linspace(ub * 0.01, ub, 37)
@@ -118,13 +117,8 @@ def test_random_shapes_vector_units(seed):
     h = kb.ProblemHandle(model, mp, th, pw, crit, dt, lb, ub, m=m, cp_id=cp, cp_params=cpp)
     o = ko.Problem(model, omp, th, pw, crit=crit, dt=dt, m=m, d=len(lb), cp_id=cp, cp_params=cpp)
     got, want = h.objective_batch(pts, w), o.objective_batch(pts, w)
-    assert np.array_equal(np.isnan(got), np.isnan(want))
-    fin = np.isfinite(want) & np.isfinite(got)
-    if not fin.any():
-        return
-    rf.assert_parity(got[fin], want[fin],
-                     lambda i: rf.objective(model, mp, pts[fin][i], w[fin][i], th, pw, crit=crit, dt=dt, m=m, cov=cov),
-                     rtol=RTOL)
+    rf.assert_parity(got, want, lambda i: rf.objective(model, mp, pts[i], w[i], th, pw, crit=crit, dt=dt, m=m, cov=cov),
+                     rtol=RTOL, cond_fn=lambda i: rf.cond_max(model, mp, pts[i], w[i], th, m, cov))
 
 
 @pytest.mark.parametrize("seed", range(int(os.environ.get("KST_FUZZ_CASES", "24")) // 2))
