@@ -66,7 +66,7 @@ def test_dtr_delta_method_and_gateaux():
         got, want = h.objective_batch(pts, w), o.objective_batch(pts, w)
         rf.assert_parity(got, want, lambda i: rf.objective(5, [1.0], pts[i], w[i], theta, pw, crit=crit, dt=dt, m=m,
                                                            cov=cov), rtol=RTOL,
-                         cond_fn=lambda i: rf.cond_max(5, [1.0], pts[i], w[i], theta, m, cov))
+                         cond_fn=lambda i: rf.cond_max(5, [1.0], pts[i], w[i], theta, m, cov, dt=dt))
     for case in ("copyboth", "equidistant"):
         h, o, cov, m, lb, ub = _pair(case, theta)
         at_p, at_w = wl.jittered_swarm_nd(1, 6 if m == 1 else 3, lb, ub, seed=9)

@@ -67,7 +67,7 @@ def test_random_shapes_against_oracle(seed):
 
     def cond_fn(i):
         if i not in cond:
-            cond[i] = rf.cond_max(model, mp, pts[i], w[i], th)
+            cond[i] = rf.cond_max(model, mp, pts[i], w[i], th, dt=dt)
         return cond[i]
 
     rf.assert_parity(got, want, lambda i: rf.objective(model, mp, pts[i], w[i], th, pw, crit=crit, dt=dt), rtol=RTOL,
@@ -118,7 +118,7 @@ def test_random_shapes_vector_units(seed):
     o = ko.Problem(model, omp, th, pw, crit=crit, dt=dt, m=m, d=len(lb), cp_id=cp, cp_params=cpp)
     got, want = h.objective_batch(pts, w), o.objective_batch(pts, w)
     rf.assert_parity(got, want, lambda i: rf.objective(model, mp, pts[i], w[i], th, pw, crit=crit, dt=dt, m=m, cov=cov),
-                     rtol=RTOL, cond_fn=lambda i: rf.cond_max(model, mp, pts[i], w[i], th, m, cov))
+                     rtol=RTOL, cond_fn=lambda i: rf.cond_max(model, mp, pts[i], w[i], th, m, cov, dt=dt))
 
 
 @pytest.mark.parametrize("seed", range(int(os.environ.get("KST_FUZZ_CASES", "24")) // 2))

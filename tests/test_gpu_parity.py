@@ -110,7 +110,7 @@ def _parity(c, h, o, pts, w, crit, dt, m, pw=None):
     pw = np.full(len(c["theta"]), 1.0 / len(c["theta"])) if pw is None else pw
     rf.assert_parity(got, want, lambda i: rf.objective(c["model"], c["mp"], pts[i], w[i], c["theta"], pw, crit=crit,
                                                        dt=dt, m=m), rtol=RTOL,
-                     cond_fn=lambda i: rf.cond_max(c["model"], c["mp"], pts[i], w[i], c["theta"], m))
+                     cond_fn=lambda i: rf.cond_max(c["model"], c["mp"], pts[i], w[i], c["theta"], m, dt=dt))
     return got, want
 
 
@@ -130,7 +130,7 @@ def test_objective_batch_vs_oracle(cfg, n, S):
     # these well-separated designs are all well conditioned (scaled cond(M) < 1e6), so assert_parity held every one
     # of them to the north-star bar outright: within 1e-10 of the oracle, or of the 80-bit referee where the oracle's
     # own rounding is the larger error -- no slack rule, no skipped element
-    conds = np.array([rf.cond_max(c["model"], c["mp"], pts[i], w[i], c["theta"], m) for i in range(S)])
+    conds = np.array([rf.cond_max(c["model"], c["mp"], pts[i], w[i], c["theta"], m, dt=dt) for i in range(S)])
     assert conds.max() < 1e6 and rf.last_report["slack"] == 0 and rf.last_report["singular_luck"] == 0, rf.last_report
     assert np.isfinite(want).all() and np.isfinite(got).all()
     # the reference's own random initialiser (i.i.d. points): the same rule wherever cond < 1e6, the referee with a

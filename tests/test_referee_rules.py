@@ -38,8 +38,10 @@ def test_ill_conditioned_designs_get_a_slack_of_eight():
     assert rf.last_report["slack"] == 1
     with pytest.raises(AssertionError):
         rf.assert_parity([1.0 + 1e-7], [1.0], lambda i: 1.0 + 5e-9, **ill)      # 9.5e-8 > 8 x 5e-9
-    with pytest.raises(AssertionError):                                          # the oracle is fine: no excuse
-        rf.assert_parity([1.0 + 1e-9], [1.0], lambda i: 1.0, **ill)
+    rf.assert_parity([1.0 + 1e-9], [1.0], lambda i: 1.0, **ill)                  # oracle exact by luck: inside the
+    assert rf.last_report["cond_bound"] == 1                                     # cond * 2^-53 = 1.1e-8 bound
+    with pytest.raises(AssertionError):                                          # beyond it: no excuse
+        rf.assert_parity([1.0 + 5e-8], [1.0], lambda i: 1.0, **ill)
 
 
 def test_scaled_condition_number():
@@ -49,3 +51,19 @@ def test_scaled_condition_number():
     near = rf.cond_max(1, [1.0], [[0.0], [2.5], [2.5 + 1e-7]], [1 / 3] * 3, th)
     assert good < 1e4 and near > 1e12
     assert rf.cond_max(1, [1.0], [[2.5]], [1.0], th) > 1e12 or np.isinf(rf.cond_max(1, [1.0], [[2.5]], [1.0], th))
+
+
+def test_cond_bound_rule_and_transformed_matrix():
+    ill = dict(cond_fn=lambda i: 1e9)       # cond * 2^-53 = 1.1e-7 relative
+    rf.assert_parity([1.0 + 5e-9], [1.0], lambda i: 1.0 + 2e-10, **ill)        # oracle lucky (2e-10), engine 4.8e-9
+    assert rf.last_report["cond_bound"] == 1
+    with pytest.raises(AssertionError):
+        rf.assert_parity([1.0 + 5e-7], [1.0], lambda i: 1.0 + 2e-10, **ill)    # beyond the forward error bound
+    # a dense DeltaMethod Jacobian on a compartment-model design: M is harmless once scaled, DT M^-1 DT' is close to
+    # rank one because the columns of M^-1 differ by many orders of magnitude
+    th = np.array([[4.3, 0.06, 21.8]])
+    pts, w = [[3.0], [4.4], [13.7]], [0.3, 0.3, 0.4]
+    q = np.linalg.qr(np.random.default_rng(0).normal(size=(3, 3)))[0]
+    plain = rf.cond_max(4, [0.1], pts, w, th, m=3)
+    with_dt = rf.cond_max(4, [0.1], pts, w, th, m=3, dt=q[None, :2, :])
+    assert plain < 1e3 and with_dt > 1e4 * plain
