@@ -207,7 +207,7 @@ int kst_ensure_partials(kst_problem *h, size_t n)
     return KST_OK;
 }
 
-static int ensure_stage(kst_problem *h, size_t particles, size_t rows)
+int kst_ensure_stage(kst_problem *h, size_t particles, size_t rows)
 {
     if (particles > h->stage_cap_particles) {
         if (h->stage_fx) KST_CUDA(cudaFree(h->stage_fx));
@@ -256,7 +256,7 @@ extern "C" int kst_objective_batch(kst_problem *h, int S, int K, const double *p
     KST_CHECK_HANDLE(h);
     if (!points || !weights || !fx) { kst_set_error("objective_batch: NULL buffer"); return KST_EINVAL; }
     if (S < 1 || K < 1) { kst_set_error("objective_batch: need S >= 1 and K >= 1"); return KST_EINVAL; }
-    int rc = ensure_stage(h, (size_t)S, (size_t)S * K);
+    int rc = kst_ensure_stage(h, (size_t)S, (size_t)S * K);
     if (rc) return rc;
     KST_CUDA(cudaMemcpyAsync(h->stage_pts, points, sizeof(double) * S * K * h->d, cudaMemcpyHostToDevice, h->stream));
     KST_CUDA(cudaMemcpyAsync(h->stage_w, weights, sizeof(double) * S * K, cudaMemcpyHostToDevice, h->stream));
@@ -316,7 +316,7 @@ extern "C" int kst_informationmatrix(kst_problem *h, int K, const double *points
 {
     KST_CHECK_HANDLE(h);
     if (!points || !weights || !M || K < 1) { kst_set_error("informationmatrix: bad arguments"); return KST_EINVAL; }
-    int rc = ensure_stage(h, (size_t)(h->r * h->r), (size_t)K);
+    int rc = kst_ensure_stage(h, (size_t)(h->r * h->r), (size_t)K);
     if (rc) return rc;
     KST_CUDA(cudaMemcpyAsync(h->stage_pts, points, sizeof(double) * K * h->d, cudaMemcpyHostToDevice, h->stream));
     KST_CUDA(cudaMemcpyAsync(h->stage_w, weights, sizeof(double) * K, cudaMemcpyHostToDevice, h->stream));
@@ -334,7 +334,7 @@ extern "C" int kst_gateaux_prepare(kst_problem *h, int K, const double *points, 
 {
     KST_CHECK_HANDLE(h);
     if (!points || !weights || K < 1) { kst_set_error("gateaux_prepare: bad arguments"); return KST_EINVAL; }
-    int rc = ensure_stage(h, 1, (size_t)K);
+    int rc = kst_ensure_stage(h, 1, (size_t)K);
     if (rc) return rc;
     KST_CUDA(cudaMemcpyAsync(h->stage_pts, points, sizeof(double) * K * h->d, cudaMemcpyHostToDevice, h->stream));
     KST_CUDA(cudaMemcpyAsync(h->stage_w, weights, sizeof(double) * K, cudaMemcpyHostToDevice, h->stream));
@@ -413,14 +413,19 @@ extern "C" int kst_gateaux_eval(kst_problem *h, int64_t G, const double *dirs, d
 static int pso_evaluate(kst_problem *h)
 {
     KstPso &p = h->pso;
+    const int gd = p.mode == KST_PSO_MODE_GATEAUX;
     int rc;
-    if (p.mode == KST_PSO_MODE_OBJECTIVE && h->nranks <= 1) {
+    if (h->nranks <= 1) {
         // one GPU: the finish step rides along in k_pso_best, which follows every evaluation of the swarm
-        rc = kst_launch_objective(h, p.S, p.K, p.x_pts, p.x_w, p.fx, &p.pending_n_blk);
-    } else if (p.mode == KST_PSO_MODE_OBJECTIVE) {
+        rc = kst_launch_objective(h, p.S, p.K, p.x_pts, p.x_w, p.fx, &p.pending_n_blk, gd);
+        kst_objective_finish_terms(h, gd, &p.pending_offset, &p.pending_nan);
+    } else if (!gd) {
         rc = kst_objective_allreduce(h, p.S, p.K, p.x_pts, p.x_w, p.fx);
     } else {
-        rc = kst_launch_gateaux_eval(h, p.S, p.x_pts, p.fx);
+        // Gateaux mode: the swarm's one-point directions go through the evaluation kernel with the Gateaux integrand
+        // as the per-draw value (lanes along draws), not through the grid kernel (one thread per direction), which
+        // is laid out for thousands of directions
+        rc = kst_launch_objective(h, p.S, p.K, p.x_pts, p.x_w, p.fx, nullptr, 1);
         if (rc) return rc;
         rc = kst_allreduce_sum(h, p.fx, (size_t)p.S);
     }
@@ -428,12 +433,12 @@ static int pso_evaluate(kst_problem *h)
     return rc;
 }
 
-extern "C" int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, const double *proto_points,
-                            const double *proto_weights, int P, const int *fixw, const int *fixp, uint64_t seed, int mode,
-                            int *status)
+// Pso constructor checks (src/pso.jl:35-43), prototype checks (src/pso.jl:89-91, check_compatible
+// src/designmeasure-abstractpoint.jl:60-71), swarm allocation, upload, k_pso_init: everything of optimizer_state
+// (src/pso.jl:83-125) up to the first evaluation.
+static int pso_setup(kst_problem *h, int S, int K, double c1, double c2, const double *proto_points,
+                     const double *proto_weights, int P, const int *fixw, const int *fixp, uint64_t seed, int mode)
 {
-    KST_CHECK_HANDLE(h);
-    // Pso constructor checks, src/pso.jl:35-43; prototypes check, src/pso.jl:89-91
     if (S <= 1) { kst_set_error("swarmsize must be at least 2"); return KST_EINVAL; }
     if (c1 < 0 || c2 < 0 || c1 + c2 <= 4) { kst_set_error("c1 and c2 must be non-negative and, c1 + c2 > 4"); return KST_EINVAL; }
     if (P < 1 || S < P) { kst_set_error("swarmsize must be >= number of prototype particles"); return KST_EINVAL; }
@@ -442,7 +447,6 @@ extern "C" int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, 
         if (K != 1) { kst_set_error("derivative only implemented for one-point directions"); return KST_EINVAL; }
         if (!h->g_ready) { kst_set_error("pso_init(gateaux) before gateaux_prepare"); return KST_ESTATE; }
     } else if (mode != KST_PSO_MODE_OBJECTIVE) { kst_set_error("unknown pso mode %d", mode); return KST_EINVAL; }
-    // check_compatible (src/designmeasure-abstractpoint.jl:60-71)
     for (int i = 0; i < P * K; i++)
         for (int j = 0; j < h->d; j++) {
             const double x = proto_points[(size_t)i * h->d + j];
@@ -451,21 +455,30 @@ extern "C" int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, 
     int rc = kst_pso_alloc(h, S, K);
     if (rc) return rc;
     KstPso &p = h->pso;
-    p.mode = mode; p.c1 = c1; p.c2 = c2; p.seed = seed; p.iter = 0; p.n_eval = 0;
+    p.mode = mode; p.c1 = c1; p.c2 = c2; p.seed = seed; p.iter = 0; p.n_eval = 0; p.pending_n_blk = 0;
     // "fixing all weights but one is equivalent to fixing them all" (src/designmeasure-abstractpoint.jl:51-56)
     int fw[KST_MAX_ROWS], nfix = 0;
     for (int k = 0; k < K; k++) { fw[k] = fixw[k] != 0; nfix += fw[k]; }
     if (nfix == K - 1)
         for (int k = 0; k < K; k++) fw[k] = 1;
+    // (a copy from pageable host memory is staged before cudaMemcpyAsync returns: the stack buffer may go away)
     KST_CUDA(cudaMemcpyAsync(p.fixw, fw, sizeof(int) * K, cudaMemcpyHostToDevice, h->stream));
     KST_CUDA(cudaMemcpyAsync(p.fixp, fixp, sizeof(int) * K, cudaMemcpyHostToDevice, h->stream));
-    rc = ensure_stage(h, 1, (size_t)P * K);
+    rc = kst_ensure_stage(h, 1, (size_t)P * K);
     if (rc) return rc;
     KST_CUDA(cudaMemcpyAsync(h->stage_pts, proto_points, sizeof(double) * P * K * h->d, cudaMemcpyHostToDevice, h->stream));
     KST_CUDA(cudaMemcpyAsync(h->stage_w, proto_weights, sizeof(double) * P * K, cudaMemcpyHostToDevice, h->stream));
-    KST_CUDA(cudaStreamSynchronize(h->stream));  // fw is a stack buffer
-    rc = kst_launch_pso_init(h, h->stage_pts, h->stage_w, P);
+    return kst_launch_pso_init(h, h->stage_pts, h->stage_w, P);
+}
+
+extern "C" int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, const double *proto_points,
+                            const double *proto_weights, int P, const int *fixw, const int *fixp, uint64_t seed, int mode,
+                            int *status)
+{
+    KST_CHECK_HANDLE(h);
+    int rc = pso_setup(h, S, K, c1, c2, proto_points, proto_weights, P, fixw, fixp, seed, mode);
     if (rc) return rc;
+    KstPso &p = h->pso;
     rc = pso_evaluate(h);
     if (rc) return rc;
     rc = kst_launch_pso_best(h, 1, -1);
@@ -478,6 +491,22 @@ extern "C" int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, 
     return KST_OK;
 }
 
+// n_iters times tick! on the three-launch path (move, evaluation, best update), trace slots slot0, slot0 + 1, ...
+static int pso_ticks_unfused(kst_problem *h, int n_iters, int slot0)
+{
+    KstPso &p = h->pso;
+    for (int it = 0; it < n_iters; it++) {
+        int rc = kst_launch_pso_move(h);
+        if (rc) return rc;
+        rc = pso_evaluate(h);
+        if (rc) return rc;
+        rc = kst_launch_pso_best(h, 0, slot0 + it);
+        if (rc) return rc;
+        p.iter++;
+    }
+    return KST_OK;
+}
+
 extern "C" int kst_pso_run(kst_problem *h, int n_iters, double *trace_fx, double *trace_points, double *trace_weights)
 {
     KST_CHECK_HANDLE(h);
@@ -485,24 +514,13 @@ extern "C" int kst_pso_run(kst_problem *h, int n_iters, double *trace_fx, double
     if (p.iter < 1) { kst_set_error("pso_run before pso_init"); return KST_ESTATE; }
     if (n_iters < 0) { kst_set_error("pso_run: n_iters < 0"); return KST_EINVAL; }
     if (n_iters == 0) return KST_OK;
-    if (n_iters > p.tr_cap) {
-        if (p.tr_fx) { KST_CUDA(cudaFree(p.tr_fx)); KST_CUDA(cudaFree(p.tr_pts)); KST_CUDA(cudaFree(p.tr_w)); }
-        p.tr_fx = p.tr_pts = p.tr_w = nullptr;
-        p.tr_cap = 0;
-        KST_CUDA(cudaMalloc(&p.tr_fx, sizeof(double) * n_iters));
-        KST_CUDA(cudaMalloc(&p.tr_pts, sizeof(double) * n_iters * p.K * h->d));
-        KST_CUDA(cudaMalloc(&p.tr_w, sizeof(double) * n_iters * p.K));
-        p.tr_cap = n_iters;
-    }
-    for (int it = 0; it < n_iters; it++) {
-        int rc = kst_launch_pso_move(h);
-        if (rc) return rc;
-        rc = pso_evaluate(h);
-        if (rc) return rc;
-        rc = kst_launch_pso_best(h, 0, it);
-        if (rc) return rc;
-        p.iter++;
-    }
+    int rc = kst_pso_ensure_trace(h, n_iters);
+    if (rc) return rc;
+    // small problems: the whole run in one cooperative launch (kst_pso_fused.cuh); otherwise three launches per tick
+    rc = kst_launch_pso_fused(h, n_iters, 0, 0, 1, nullptr, nullptr);
+    if (rc == 1) rc = pso_ticks_unfused(h, n_iters, 0);
+    else if (rc == KST_OK) { p.iter += n_iters; p.n_eval += (int64_t)p.S * n_iters; }
+    if (rc) return rc;
     if (trace_fx) KST_CUDA(cudaMemcpyAsync(trace_fx, p.tr_fx, sizeof(double) * n_iters, cudaMemcpyDeviceToHost, h->stream));
     if (trace_points)
         KST_CUDA(cudaMemcpyAsync(trace_points, p.tr_pts, sizeof(double) * n_iters * p.K * h->d, cudaMemcpyDeviceToHost, h->stream));
@@ -510,6 +528,74 @@ extern "C" int kst_pso_run(kst_problem *h, int n_iters, double *trace_fx, double
         KST_CUDA(cudaMemcpyAsync(trace_weights, p.tr_w, sizeof(double) * n_iters * p.K, cudaMemcpyDeviceToHost, h->stream));
     // without trace buffers nothing has to reach the host: the iterations stay queued on the handle's stream
     if (trace_fx || trace_points || trace_weights) KST_CUDA(cudaStreamSynchronize(h->stream));
+    return KST_OK;
+}
+
+// Enqueues a whole optimize() (src/optimize.jl:42-70) -- optimizer_state, then iterations - 1 ticks -- without a host
+// synchronisation.  Afterwards tr_fx / tr_pts / tr_w hold the `iterations` trace entries (entry 0 = initial state),
+// h->d_flag the status word and, when want_snapshot, p.snap the packed state after the initial evaluation.
+int kst_pso_optimize_enqueue(kst_problem *h, int S, int K, int iterations, double c1, double c2, const double *proto_points,
+                             const double *proto_weights, int P, const int *fixw, const int *fixp, uint64_t seed, int mode,
+                             int want_snapshot)
+{
+    if (iterations < 1) { kst_set_error("number of iterations must be positive"); return KST_EINVAL; }
+    int rc = pso_setup(h, S, K, c1, c2, proto_points, proto_weights, P, fixw, fixp, seed, mode);
+    if (rc) return rc;
+    KstPso &p = h->pso;
+    rc = kst_pso_ensure_trace(h, iterations);
+    if (rc) return rc;
+    p.iter = 1;  // the first move is iteration 1 (key of its random numbers), as after kst_pso_init
+    rc = kst_launch_pso_fused(h, iterations, 1, 0, 1, h->d_flag, want_snapshot ? p.snap : nullptr);
+    if (rc == KST_OK) {
+        p.iter = iterations;
+        p.n_eval = (int64_t)S * iterations;
+        return KST_OK;
+    }
+    if (rc != 1) return rc;
+    p.iter = 0;
+    rc = pso_evaluate(h);
+    if (rc) return rc;
+    rc = kst_launch_pso_best(h, 1, 0);
+    if (rc) return rc;
+    p.iter = 1;
+    if (want_snapshot) {
+        // the same packed layout the persistent kernel writes (KstFusedParams::snap), gathered with device copies
+        const size_t np = (size_t)S * K * h->d, nw = (size_t)S * K;
+        struct { const double *src; size_t n; } parts[] = {{p.x_pts, np}, {p.x_w, nw}, {p.p_pts, np}, {p.p_w, nw}, {p.v_pts, np},
+                                                           {p.v_w, nw}, {p.g_pts, (size_t)K * h->d}, {p.g_w, (size_t)K},
+                                                           {p.fx, (size_t)S}, {p.fp, (size_t)S}, {p.fg, 1}};
+        double *dst = p.snap;
+        for (auto &q : parts) {
+            KST_CUDA(cudaMemcpyAsync(dst, q.src, sizeof(double) * q.n, cudaMemcpyDeviceToDevice, h->stream));
+            dst += q.n;
+        }
+    }
+    return pso_ticks_unfused(h, iterations - 1, 1);
+}
+
+extern "C" int kst_pso_optimize(kst_problem *h, int S, int K, int iterations, double c1, double c2,
+                                const double *proto_points, const double *proto_weights, int P, const int *fixw,
+                                const int *fixp, uint64_t seed, int mode, int *status, double *trace_fx,
+                                double *trace_points, double *trace_weights, double *state0)
+{
+    KST_CHECK_HANDLE(h);
+    int rc = kst_pso_optimize_enqueue(h, S, K, iterations, c1, c2, proto_points, proto_weights, P, fixw, fixp, seed, mode,
+                                      state0 != nullptr);
+    if (rc) return rc;
+    KstPso &p = h->pso;
+    int st = 0;
+    KST_CUDA(cudaMemcpyAsync(&st, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (trace_fx) KST_CUDA(cudaMemcpyAsync(trace_fx, p.tr_fx, sizeof(double) * iterations, cudaMemcpyDeviceToHost, h->stream));
+    if (trace_points)
+        KST_CUDA(cudaMemcpyAsync(trace_points, p.tr_pts, sizeof(double) * iterations * K * h->d, cudaMemcpyDeviceToHost, h->stream));
+    if (trace_weights)
+        KST_CUDA(cudaMemcpyAsync(trace_weights, p.tr_w, sizeof(double) * iterations * K, cudaMemcpyDeviceToHost, h->stream));
+    if (state0) {
+        const size_t n = 3 * (size_t)S * K * (h->d + 1) + (size_t)K * (h->d + 1) + 2 * (size_t)S + 1;
+        KST_CUDA(cudaMemcpyAsync(state0, p.snap, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
+    }
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    if (status) *status = st;
     return KST_OK;
 }
 

@@ -56,7 +56,9 @@ void kst_set_error(const char *fmt, ...);
 
 struct KstPso {
     int S = 0, K = 0, mode = 0, iter = 0;
-    int pending_n_blk = 0;  // > 0: fx still sits in h->partials as per-CTA sums, k_pso_best finishes it
+    int pending_n_blk = 0;  // > 0: fx still sits in h->partials as per-CTA sums, k_pso_best finishes it ...
+    double pending_offset = 0.0;  // ... adding this
+    int pending_nan = 0;          // ... or filling NaN (Gateaux mode at a singular design)
     double c1 = 0, c2 = 0;
     uint64_t seed = 0;
     int64_t n_eval = 0;
@@ -68,6 +70,12 @@ struct KstPso {
     // per-run trace buffers (device), grown on demand
     double *tr_fx = nullptr, *tr_pts = nullptr, *tr_w = nullptr;
     int tr_cap = 0;
+    // persistent swarm kernel (kst_pso_fused.cuh): published positions [2][S][K*d] / [2][S][K], grid barrier counter
+    // and how far it has counted, packed snapshot of the state after the initial evaluation
+    double *x2_pts = nullptr, *x2_w = nullptr, *snap = nullptr;
+    unsigned long long *bar = nullptr;
+    unsigned long long bar_count = 0;
+    int fused_off = 0;  // this swarm does not fit the persistent kernel: do not ask again
 };
 
 struct kst_problem {
@@ -134,18 +142,30 @@ struct kst_problem {
 int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const double *d_dt);
 // defer_n_blk != nullptr: the per-CTA partial sums stay in h->partials ([S][*defer_n_blk]) and the caller finishes them
 // (kst_api.cu fuses that step into the peer-memory all-reduce)
+// gd = 1: the Gateaux derivative of the prepared design in the swarm's one-point directions (K = 1) instead of the
+// objective: same kernel body, the draw's "criterion" is tr_U[A_j M(delta, theta_j)]
 int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, const double *d_w,
-                         double *d_fx, int *defer_n_blk = nullptr);
+                         double *d_fx, int *defer_n_blk = nullptr, int gd = 0);
+void kst_objective_finish_terms(const kst_problem *h, int gd, double *offset, int *nan_fill);
 int kst_launch_infomatrix(kst_problem *h, int K, const double *d_pts, const double *d_w,
                           int64_t draw, double *d_M);
 int kst_objective_grid(const kst_problem *h, int S, int *n_blk, int *tile_p);
+// n_steps swarm evaluations (ticks; the first one optimizer_state's initial evaluation when first_is_init) in one
+// cooperative launch.  Returns 1 when the problem does not fit the persistent kernel (nothing was launched).
+// Trace slot tr_slot0 + i receives (fg, g) after evaluation i when with_trace; snap: see KstFusedParams.
+int kst_launch_pso_fused(kst_problem *h, int n_steps, int first_is_init, int tr_slot0, int with_trace, int *d_status,
+                         double *d_snap);
 int kst_sum_fixed(kst_problem *h, const double *d_x, int64_t n, double *host_out);
+int kst_sum_fixed_enqueue(kst_problem *h, const double *d_x, int64_t n);
 // kst_gateaux.cu
 int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const double *d_w);
 int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, double *d_out);
 // kst_pso.cu
 int kst_pso_alloc(kst_problem *h, int S, int K);
 void kst_pso_free(kst_problem *h);
+int kst_pso_ensure_trace(kst_problem *h, int n);
+struct KstPsoDev;
+void kst_pso_make_dev(const kst_problem *h, KstPsoDev *out);
 int kst_launch_pso_init(kst_problem *h, const double *d_proto_pts, const double *d_proto_w, int P);
 int kst_launch_pso_move(kst_problem *h);
 int kst_launch_pso_best(kst_problem *h, int init, int trace_slot);
@@ -155,3 +175,7 @@ int kst_objective_allreduce(kst_problem *h, int S, int K, const double *d_pts, c
 void kst_comm_release(kst_problem *h);
 // kst_api.cu
 int kst_ensure_partials(kst_problem *h, size_t n);
+int kst_ensure_stage(kst_problem *h, size_t particles, size_t rows);
+int kst_pso_optimize_enqueue(kst_problem *h, int S, int K, int iterations, double c1, double c2, const double *proto_points,
+                             const double *proto_weights, int P, const int *fixw, const int *fixp, uint64_t seed, int mode,
+                             int want_snapshot);

@@ -526,12 +526,14 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
                                                            h->t, d_pts, d_w, K, h->mp, h->gA, h->gAp, h->gtrB, wtrB, h->d_flag);
     });
     KST_CUDA(cudaGetLastError());
-    int rc = kst_sum_fixed(h, wtrB, h->N, &h->g_offset);
+    // one round trip for both results: the singularity flag (offset 0 of d_flag) and the summed constant (offset 8)
+    int rc = kst_sum_fixed_enqueue(h, wtrB, h->N);
     if (rc) return rc;
-    int flag = 0;
-    KST_CUDA(cudaMemcpyAsync(&flag, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    struct { int flag, pad; double sum; } back;
+    KST_CUDA(cudaMemcpyAsync(&back, h->d_flag, 16, cudaMemcpyDeviceToHost, h->stream));
     KST_CUDA(cudaStreamSynchronize(h->stream));
-    h->g_singular = flag;
+    h->g_offset = back.sum;
+    h->g_singular = back.flag;
     h->g_ready = 1;
     return KST_OK;
 }

@@ -1,5 +1,8 @@
-// explicit instantiations of the objective evaluation kernels (see kst_objective_kernel.cuh)
-#include "kst_objective_kernel.cuh"
+// explicit instantiations of the objective evaluation kernels (kst_objective_kernel.cuh) and of the persistent
+// swarm kernel built on them (kst_pso_fused.cuh)
+#include "kst_pso_fused.cuh"
 
 template int kst_obj_launch<KstLinLogReg<1>>(kst_problem *, const KstObjParams &, dim3, int);
+template int kst_fused_launch<KstLinLogReg<1>>(kst_problem *, KstFusedParams &, dim3);
 template int kst_obj_launch<KstLinLogReg<2>>(kst_problem *, const KstObjParams &, dim3, int);
+template int kst_fused_launch<KstLinLogReg<2>>(kst_problem *, KstFusedParams &, dim3);

@@ -11,14 +11,17 @@
 // matrix, its LDL' factor and everything after live in FP64 registers.  Per particle one
 // fixed-order block reduction; per-CTA partial sums go to scratch [S][n_blk] and are summed in
 // fixed order by k_obj_finish, so results are bit-reproducible run to run.
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
 
-#include "kst_objective_kernel.cuh"
+#include "kst_pso_fused.cuh"
 
 // the evaluation kernels of every family are compiled in their own translation units
-#define KST_X(MF) extern template int kst_obj_launch<MF>(kst_problem *, const KstObjParams &, dim3, int);
+#define KST_X(MF)                                                                          \
+    extern template int kst_obj_launch<MF>(kst_problem *, const KstObjParams &, dim3, int); \
+    extern template int kst_fused_launch<MF>(kst_problem *, KstFusedParams &, dim3);
 KST_OBJ_FAMILIES(KST_X)
 #undef KST_X
 
@@ -70,14 +73,16 @@ __global__ void k_prep_draws(const double *__restrict__ theta_aos, const double 
 }
 
 
+// nan_fill: Gateaux derivative at a design whose constants could not be computed (gateauxderivative fills NaN,
+// src/designproblem.jl:281-284)
 __global__ void k_obj_finish(const double *__restrict__ partials, int n_blk, double offset,
-                             double *__restrict__ fx, int S)
+                             double *__restrict__ fx, int S, int nan_fill)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= S) return;
     double s = 0.0;
     for (int b = 0; b < n_blk; b++) s += partials[(size_t)p * n_blk + b];
-    fx[p] = s + offset;
+    fx[p] = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : s + offset;
 }
 
 // informationmatrix for one draw (debugging aid of the reference, src/design-common.jl:96-112)
@@ -137,6 +142,14 @@ __global__ void k_sum_fixed(const double *__restrict__ x, int64_t n, double *__r
         __syncthreads();
     }
     if (threadIdx.x == 0) *out = s[0];
+}
+
+// the sum goes to the handle's scratch double (offset 8 of d_flag); the caller copies it out
+int kst_sum_fixed_enqueue(kst_problem *h, const double *d_x, int64_t n)
+{
+    k_sum_fixed<<<1, 1024, 0, h->stream>>>(d_x, n, (double *)((char *)h->d_flag + 8));
+    KST_CUDA(cudaGetLastError());
+    return KST_OK;
 }
 
 int kst_sum_fixed(kst_problem *h, const double *d_x, int64_t n, double *host_out)
@@ -245,21 +258,39 @@ static int kst_objective_check(const kst_problem *h, int S, int K, const char *w
     return KST_OK;
 }
 
+// Kernel arguments of one swarm evaluation.  gd: the Gateaux integrand at the prepared design instead of the criterion.
+void kst_objective_params(const kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *partials,
+                          int tile_p, int gd, KstObjParams *out)
+{
+    KstObjParams &prm = *out;
+    prm.pw = h->pw; prm.dc = h->dc; prm.aux = gd ? h->gAp : h->aux; prm.reg = gd ? nullptr : h->reg; prm.ld = h->ld; prm.N = h->N;
+    prm.pts = d_pts; prm.w = d_w; prm.S = S; prm.K = K; prm.partials = partials; prm.mp = h->mp;
+    prm.w_uniform = h->w_uniform; prm.tile_p = tile_p; prm.gd = gd;
+    for (int c = 0; c < 8; c++) prm.dcmax[c] = h->dcmax[c];
+}
+
+// what the finishing step adds to the fixed-order sum of the per-CTA partial sums
+void kst_objective_finish_terms(const kst_problem *h, int gd, double *offset, int *nan_fill)
+{
+    *offset = gd ? -h->g_offset : h->offset;
+    *nan_fill = gd ? h->g_singular : 0;
+}
+
 int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *d_fx,
-                         int *defer_n_blk)
+                         int *defer_n_blk, int gd)
 {
     {
-        const int rc0 = kst_objective_check(h, S, K, "objective");
+        const int rc0 = kst_objective_check(h, S, K, gd ? "gateaux (swarm)" : "objective");
         if (rc0) return rc0;
     }
+    if (gd && !h->g_ready) { kst_set_error("gateaux evaluation before gateaux_prepare"); return KST_ESTATE; }
+    if (gd && K != 1) { kst_set_error("derivative only implemented for one-point directions"); return KST_EINVAL; }
     int n_blk = 1, tile_p = KST_TILE_P;
     const int tiles = kst_objective_grid(h, S, &n_blk, &tile_p);
     int rc = kst_ensure_partials(h, (size_t)S * n_blk);
     if (rc) return rc;
     KstObjParams prm;
-    prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.reg = h->reg; prm.ld = h->ld; prm.N = h->N;
-    prm.pts = d_pts; prm.w = d_w; prm.S = S; prm.K = K; prm.partials = h->partials; prm.mp = h->mp; prm.w_uniform = h->w_uniform; prm.tile_p = tile_p;
-    for (int c = 0; c < 8; c++) prm.dcmax[c] = h->dcmax[c];
+    kst_objective_params(h, S, K, d_pts, d_w, h->partials, tile_p, gd, &prm);
     const dim3 grid(n_blk, tiles);
     if (h->prof_on) {
         cudaEvent_t e0, e1;
@@ -277,8 +308,48 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
         *defer_n_blk = n_blk;
         return KST_OK;
     }
-    k_obj_finish<<<(S + 127) / 128, 128, 0, h->stream>>>(h->partials, n_blk, h->offset, d_fx, S);
+    double offset;
+    int nan_fill;
+    kst_objective_finish_terms(h, gd, &offset, &nan_fill);
+    k_obj_finish<<<(S + 127) / 128, 128, 0, h->stream>>>(h->partials, n_blk, offset, d_fx, S, nan_fill);
     KST_CUDA(cudaGetLastError());
+    return KST_OK;
+}
+
+// The persistent swarm kernel for the handle's swarm (kst_pso_fused.cuh).  Applicable on one GPU, without a
+// regularisation matrix, when the evaluation grid kst_objective_grid picks fits one wave of resident CTAs.
+int kst_launch_pso_fused(kst_problem *h, int n_steps, int first_is_init, int tr_slot0, int with_trace, int *d_status,
+                         double *d_snap)
+{
+    KstPso &p = h->pso;
+    const int gd = p.mode == KST_PSO_MODE_GATEAUX;
+    const bool disabled = getenv("KST_NO_FUSED") != nullptr;  // A/B switch for tests and measurements (read per call)
+    if (disabled || p.fused_off || h->nranks > 1 || (h->reg && !gd) || p.S > KST_FUSED_MAX_S || n_steps < 1)
+        return KST_FUSED_NOFIT;
+    int rc = kst_objective_check(h, p.S, p.K, "pso (persistent kernel)");
+    if (rc) return rc;
+    int n_blk = 1, tile_p = KST_TILE_P;
+    const int tiles = kst_objective_grid(h, p.S, &n_blk, &tile_p);
+    if ((long long)tiles * n_blk > (long long)h->sm_count * KST_MINB) { p.fused_off = 1; return KST_FUSED_NOFIT; }
+    rc = kst_ensure_partials(h, (size_t)2 * p.S * n_blk);
+    if (rc) return rc;
+    KstFusedParams fp;
+    kst_objective_params(h, p.S, p.K, nullptr, nullptr, nullptr, tile_p, gd, &fp.obj);
+    kst_pso_make_dev(h, &fp.pso);
+    fp.x2_pts = p.x2_pts; fp.x2_w = p.x2_w; fp.partials2 = h->partials;
+    fp.bar = p.bar; fp.bar_base = p.bar_count;
+    fp.n_steps = n_steps; fp.first_is_init = first_is_init; fp.iter0 = (uint32_t)p.iter;
+    fp.c1 = p.c1; fp.c2 = p.c2;
+    const double phi = p.c1 + p.c2;
+    fp.chi = 2 / fabs(2 - phi - sqrt(phi * phi - 4 * phi));  // src/pso.jl:134-135
+    kst_objective_finish_terms(h, gd, &fp.offset, &fp.nan_fill);
+    fp.tr_fx = with_trace ? p.tr_fx : nullptr; fp.tr_pts = with_trace ? p.tr_pts : nullptr; fp.tr_w = with_trace ? p.tr_w : nullptr;
+    fp.tr_slot0 = tr_slot0; fp.status = d_status; fp.snap = d_snap;
+    const dim3 grid(n_blk, tiles);
+    KST_MODEL_SWITCH(h->model_id, rc = kst_fused_launch<MF>(h, fp, grid));
+    if (rc == KST_FUSED_NOFIT) p.fused_off = 1;
+    if (rc) return rc;
+    p.bar_count += (unsigned long long)n_steps * (unsigned long long)(n_blk * tiles);
     return KST_OK;
 }
 
@@ -371,14 +442,12 @@ extern "C" int kst_objective_batch_noalloc(kst_problem *h, int S, int K, const d
     const int tiles = kst_objective_grid(h, S, &n_blk, &tile_p);
     if ((size_t)n_blk * S > KST_NOALLOC_MAX_PARTIALS) n_blk = KST_NOALLOC_MAX_PARTIALS / S;  // >= 64 by the swarm limit
     KstObjParams prm;
-    prm.pw = h->pw; prm.dc = h->dc; prm.aux = h->aux; prm.reg = h->reg; prm.ld = h->ld; prm.N = h->N;
-    prm.pts = d_points; prm.w = d_weights; prm.S = S; prm.K = K; prm.partials = scratch; prm.mp = h->mp; prm.w_uniform = h->w_uniform; prm.tile_p = tile_p;
-    for (int c = 0; c < 8; c++) prm.dcmax[c] = h->dcmax[c];
+    kst_objective_params(h, S, K, d_points, d_weights, scratch, tile_p, 0, &prm);
     const dim3 grid(n_blk, tiles);
     KST_MODEL_SWITCH(h->model_id, rc = kst_obj_launch<MF>(h, prm, grid, K));
     if (rc) return rc;
     KST_CUDA(cudaGetLastError());
-    k_obj_finish<<<(S + 127) / 128, 128, 0, h->stream>>>(scratch, n_blk, h->offset, d_fx, S);
+    k_obj_finish<<<(S + 127) / 128, 128, 0, h->stream>>>(scratch, n_blk, h->offset, d_fx, S, 0);
     KST_CUDA(cudaGetLastError());
     return KST_OK;
 }

@@ -24,7 +24,12 @@ struct KstObjParams {
     int tile_p;             // particles per CTA, 1..KST_TILE_P (small problems use small tiles to fill the SMs)
     double dcmax[8];        // max_j |dc[c][j]| per hoisted constant (Inf / NaN when a draw is not finite): lets a
                             // particle prove that its exp arguments stay inside the exponent range (MF::arg_bound)
+    int gd;                 // 1: evaluate the Gateaux derivative integrand instead of the criterion (CRIT = 3 kernels;
+                            // aux = packed pw_j At_j of the prepared design, [r(r+1)/2][ld])
 };
+
+// criterion ids inside the kernels: the public KST_CRIT_* values plus the Gateaux integrand
+#define KST_KCRIT_GD 3
 
 // ------------------------------------------------------------------------------------------
 // shared-memory particle tile
@@ -43,7 +48,7 @@ struct KstTile {
     __device__ static int *rank(double *s, int rows_max) { return nact(s, rows_max) + KST_TILE_P; }
     // 1 when every exp argument of the particle is provably within +-700 for every draw (no exponent clamp needed)
     __device__ static int *safe(double *s, int rows_max) { return rank(s, rows_max) + KST_TILE_P; }
-    __host__ static size_t bytes(int rows_max)
+    __host__ __device__ static size_t bytes(int rows_max)
     {
         return sizeof(double) * ((size_t)KST_TILE_P * rows_max * RW + 2 * KST_TILE_P + KST_TILE_P * (KST_NT / 32)) +
                sizeof(int) * 3 * KST_TILE_P;
@@ -57,8 +62,10 @@ template <class MF>
 __device__ __forceinline__ void kst_build_tile(double *smem, const double *__restrict__ pts,
                                                const double *__restrict__ w, int p0, int S, int K,
                                                const KstModelParams &mp, int tile_p = KST_TILE_P,
-                                               const double *dcmax = nullptr)
+                                               const double *dcmax = nullptr, int pidx0 = 0)
 {
+    // pidx0: pts / w hold the particles pidx0, pidx0 + 1, ... (the persistent swarm kernel passes its shared-memory
+    // copy of the tile's particles; everyone else the whole swarm, pidx0 = 0)
     const int rows_max = K * mp.m;
     constexpr int RW = KstTile<MF>::RW;
     if ((int)threadIdx.x < tile_p) {
@@ -68,8 +75,8 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
         double sw = 0.0, bound = 0.0;
         if (p < S) {
             for (int k = 0; k < K; k++) {
-                const double *z = pts + ((size_t)p * K + k) * mp.d;
-                const double wk = w[(size_t)p * K + k];
+                const double *z = pts + ((size_t)(p - pidx0) * K + k) * mp.d;
+                const double wk = w[(size_t)(p - pidx0) * K + k];
                 for (int i = 0; i < mp.m; i++) {
                     double pc[MF::NPC], varfac;
                     const bool trivial = MF::prep_row(z, i, mp, pc, varfac);
@@ -175,23 +182,27 @@ struct KstFalse { static constexpr bool value = false; };
 // REG (regularised normal approximation, docs/src/extend-approximation.md:69-79): the per-draw constant matrix Rt_j
 // is added to Mt before the criterion; a design with fewer rows than parameters is then no longer singular and
 // the first pivot is no longer a per-particle constant.
-template <class MF, int CRIT, int T, bool UNI, bool REG = false>
-__global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjParams prm)
+// CRIT = KST_KCRIT_GD (Gateaux integrand, gateauxderivative! src/designproblem.jl:239-258 for a swarm of directions):
+// the "criterion" of a draw is tr_U[A_j M(delta, theta_j)] with the packed, prior-weighted constants of the
+// prepared design in prm.aux; the caller subtracts the summed tr B_j.  A one-point direction is rank deficient by
+// construction, so the structural singularity shortcut does not apply.
+//
+// The body of the evaluation is a device function so that the persistent swarm kernel (kst_pso_fused.cuh) runs the
+// very same code on a tile it keeps in shared memory: the particle tile of CTA (bx, p0 / tile_p) has been built in
+// `smem` (kst_build_tile), `tab` are the staged math tables; the CTA's partial sums for its particles go to
+// partials[(p0 + i) * nbx + bx].
+template <class MF, int CRIT, int T, bool UNI, bool REG>
+__device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, double *smem, KstTab tab, const int p0,
+                                                  const int bx, const int nbx, double *__restrict__ partials)
 {
     constexpr int R = MF::R;
-    extern __shared__ __align__(16) double smem[];
-    __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
     const int rows_max = prm.K * prm.mp.m;
-    const int p0 = blockIdx.y * prm.tile_p;
-    KstTab tab = kst_math_init(s_mathtab);
-    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp, prm.tile_p, prm.dcmax);  // ends with __syncthreads()
-
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int np = min(prm.tile_p, prm.S - p0);
     double *wsum = KstTile<MF>::wsum(smem, rows_max);
     // 32-bit draw indices (the launcher guarantees N + stride < 2^31) and 32-bit shared-space addresses:
     // the loop bookkeeping is a handful of integer instructions
-    const int n = (int)prm.N, stride = (int)gridDim.x * KST_NT, j0 = (int)blockIdx.x * KST_NT + (int)threadIdx.x;
+    const int n = (int)prm.N, stride = nbx * KST_NT, j0 = bx * KST_NT + (int)threadIdx.x;
     unsigned rows_base = (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem));
     // make both shared-space bases opaque: otherwise the compiler rebuilds them from SR_CgaCtaId (a
     // variable-latency S2R/S2UR + LEA) in front of every use instead of keeping them in a register
@@ -210,7 +221,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
         constexpr bool DUAL = MF::FAST_EXP && UNI;  // the unclamped copy of the draw loop only where it pays
         const double inv0 = KstTile<MF>::isumw(smem, rows_max)[p];
         double acc = 0.0;
-        if (!REG && KstTile<MF>::rank(smem, rows_max)[p] < R) {
+        if (!REG && CRIT != KST_KCRIT_GD && KstTile<MF>::rank(smem, rows_max)[p] < R) {
             // fewer live rows than parameters: singular by construction (one-point designs etc.).  The
             // reference reaches the same -Inf through an exactly zero pivot: weighted by the prior weight
             // for log_det! (0 * -Inf = NaN, as there), unweighted where it throws.
@@ -246,7 +257,13 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
 #pragma unroll
                     for (int i = 0; i < KstPacked<R>::N; i++) M[i] += __ldg(prm.reg + ((size_t)i * ld + (size_t)j));
                 }
-                if (UNI) {
+                if (CRIT == KST_KCRIT_GD) {
+                    double q = 0.0;
+#pragma unroll
+                    for (int i = 0; i < KstPacked<R>::N; i++)
+                        q = fma(__ldg(prm.aux + ((size_t)i * ld + (size_t)j)), M[i], q);
+                    acc += q;
+                } else if (UNI) {
                     double det;
                     int signs;
                     kst_det_signs<R, INV0>(M, inv0, det, signs);
@@ -260,7 +277,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
                     }
                 } else {
                     bool exc;
-                    const double val = kst_criterion<R, CRIT, T, INV0>(M, prm.aux + j, prm.ld, exc, inv0, tab);
+                    const double val = kst_criterion<R, (CRIT == KST_KCRIT_GD ? 0 : CRIT), T, INV0>(M, prm.aux + j, prm.ld, exc, inv0, tab);
                     acc += exc ? -KST_INF : pwj * val;
                 }
             }
@@ -284,8 +301,19 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
         double s = 0.0;
 #pragma unroll
         for (int wi = 0; wi < KST_NT / 32; wi++) s += wsum[threadIdx.x * (KST_NT / 32) + wi];
-        prm.partials[(size_t)(p0 + threadIdx.x) * gridDim.x + blockIdx.x] = s;
+        partials[(size_t)(p0 + threadIdx.x) * nbx + bx] = s;
     }
+}
+
+template <class MF, int CRIT, int T, bool UNI, bool REG = false>
+__global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjParams prm)
+{
+    extern __shared__ __align__(16) double smem[];
+    __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
+    const int p0 = blockIdx.y * prm.tile_p;
+    KstTab tab = kst_math_init(s_mathtab);
+    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp, prm.tile_p, prm.dcmax);  // ends with __syncthreads()
+    kst_objective_cta<MF, CRIT, T, UNI, REG>(prm, smem, tab, p0, (int)blockIdx.x, (int)gridDim.x, prm.partials);
 }
 
 // Units with many rows (K * m up to KST_MAX_ROWS): the particle tile plus the static math tables can exceed the
@@ -313,6 +341,11 @@ static int launch_obj_t(kst_problem *h, const KstObjParams &prm, dim3 grid, size
             return KST_OK;                                                                      \
         }                                                                                       \
         break;
+    if (prm.gd) {  // Gateaux integrand of a swarm of one-point directions (CRIT is ignored)
+        KST_OPT_IN((k_objective<MF, KST_KCRIT_GD, 0, false>));
+        k_objective<MF, KST_KCRIT_GD, 0, false><<<grid, KST_NT, smem, h->stream>>>(prm);
+        return KST_OK;
+    }
     if (CRIT == 0 && T == 0 && h->uniform_w && !h->reg) {
         KST_OPT_IN((k_objective<MF, 0, 0, true>));
         k_objective<MF, 0, 0, true><<<grid, KST_NT, smem, h->stream>>>(prm);

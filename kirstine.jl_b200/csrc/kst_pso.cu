@@ -12,41 +12,7 @@
 // which cannot be reproduced outside Julia: parity of *trajectories* with the reference is
 // statistical, parity with the oracle is exact in the random inputs.
 #include "kst_common.cuh"
-
-#define KST_DINF (__longlong_as_double(0x7ff0000000000000LL))
-
-__device__ __forceinline__ void kst_philox(uint64_t seed, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                           uint32_t (&o)[4])
-{
-    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
-#pragma unroll
-    for (int round = 0; round < 10; round++) {
-        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
-        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
-    }
-    o[0] = c0; o[1] = c1; o[2] = c2; o[3] = c3;
-}
-
-__device__ __forceinline__ void kst_uniform2(uint64_t seed, uint32_t iter, uint32_t particle, uint32_t comp,
-                                             uint32_t stream, double &u0, double &u1)
-{
-    uint32_t o[4];
-    kst_philox(seed, iter, particle, comp, stream, o);
-    const uint64_t a = ((uint64_t)o[1] << 32) | o[0], b = ((uint64_t)o[3] << 32) | o[2];
-    u0 = (double)(a >> 11) * 0x1.0p-53;
-    u1 = (double)(b >> 11) * 0x1.0p-53;
-}
-
-struct KstPsoDev {
-    int S, K, d;
-    double *x_pts, *x_w, *p_pts, *p_w, *v_pts, *v_w, *g_pts, *g_w, *fx, *fp, *fg;
-    const int *fixw, *fixp;
-    double lb[KST_MAX_D], ub[KST_MAX_D];
-    uint64_t seed;
-};
+#include "kst_pso_dev.cuh"
 
 // ap_rand!(d, constraints): src/designmeasure-abstractpoint.jl:73-107, random_designpoint!
 // src/designregion.jl:104-110.  Points use u0 of component K + k*d + j, weights -log(1-u0) of
@@ -106,99 +72,15 @@ __global__ void k_pso_init(KstPsoDev s, const double *__restrict__ proto_pts, co
     }
 }
 
-// velocity + constrained move of one particle, operation order exactly as the reference
+// velocity + constrained move, one thread per particle (kst_pso_move_particle, kst_pso_dev.cuh)
 __global__ void k_pso_move(KstPsoDev s, uint32_t iter, double c1, double c2, double chi)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= s.S) return;
     const int K = s.K, d = s.d;
-    double *xp = s.x_pts + (size_t)i * K * d, *xw = s.x_w + (size_t)i * K;
-    const double *pp = s.p_pts + (size_t)i * K * d, *pw = s.p_w + (size_t)i * K;
-    double *vp = s.v_pts + (size_t)i * K * d, *vw = s.v_w + (size_t)i * K;
-
-    // pso_update_velocity!: v = ((v + (p-x) r1 c1) + (g-x) r2 c2) chi, fresh r1, r2 per component
-    // (weights first, then atoms: ap_rand!(v, lb, ub), src/designmeasure-abstractpoint.jl:136-144)
-    for (int c = 0; c < K * (d + 1); c++) {
-        double r1, r2;
-        kst_uniform2(s.seed, iter, i, c, 0, r1, r2);
-        const double x = c < K ? xw[c] : xp[c - K];
-        const double pb = c < K ? pw[c] : pp[c - K];
-        const double gb = c < K ? s.g_w[c] : s.g_pts[c - K];
-        double *v = c < K ? &vw[c] : &vp[c - K];
-        double diffp = pb - x, diffg = gb - x;
-        diffp = __dmul_rn(diffp, r1);
-        diffg = __dmul_rn(diffg, r2);
-        diffp = __dmul_rn(diffp, c1);
-        diffg = __dmul_rn(diffg, c2);
-        double vv = *v;
-        vv = __dadd_rn(vv, diffp);
-        vv = __dadd_rn(vv, diffg);
-        *v = __dmul_rn(vv, chi);
-    }
-
-    // move_handle_fixed! (src/designmeasure-abstractpoint.jl:184-223)
-    double sum_vw_free = 0.0;
-    int n_fixw = 0;
-    for (int k = 0; k < K; k++) n_fixw += s.fixw[k] != 0;
-    for (int k = 0; k < K - 1; k++) {
-        if (s.fixw[k]) vw[k] = 0.0;
-        else sum_vw_free += vw[k];
-    }
-    if (n_fixw != K && s.fixw[K - 1]) {
-        const double mean_free = sum_vw_free / (K - n_fixw);
-        for (int k = 0; k < K - 1; k++)
-            if (!s.fixw[k]) vw[k] -= mean_free;
-    }
-    for (int k = 0; k < K; k++)
-        if (s.fixp[k])
-            for (int j = 0; j < d; j++) vp[k * d + j] = 0.0;
-
-    // move_how_far (:225-248) with move_designpoint_how_far (src/designregion.jl:114-126)
-    double t = 1.0;
-    for (int k = 0; k < K; k++) {
-        double tk = 1.0;
-        for (int j = 0; j < d; j++) {
-            const double x = xp[k * d + j], v = vp[k * d + j];
-            const double probe = __dadd_rn(x, __dmul_rn(tk, v));
-            const double sl = probe > s.ub[j] ? (s.ub[j] - x) / v : tk;
-            const double sr = probe < s.lb[j] ? (s.lb[j] - x) / v : tk;
-            tk = fmin(sl, sr);
-        }
-        t = fmin(t, tk);
-    }
-    for (int k = 0; k < K - 1; k++) {
-        const double sk = __dadd_rn(xw[k], __dmul_rn(t, vw[k])) < 0 ? -xw[k] / vw[k] : t;
-        t = fmin(sk, t);
-    }
-    {
-        const double sum_x = 1.0 - xw[K - 1];
-        double sum_v = 0.0;
-        for (int k = 0; k < K - 1; k++) sum_v += vw[k];
-        const double sk = __dadd_rn(sum_x, __dmul_rn(t, sum_v)) > 1 ? (1 - sum_x) / sum_v : t;
-        t = fmin(sk, t);
-    }
-    if (t < 1e-8) t = 0.0;
-
-    // move_add_v! (:250-285) with move_designpoint! (src/designregion.jl:129-135)
-    for (int k = 0; k < K; k++)
-        for (int j = 0; j < d; j++) {
-            const double x = __dadd_rn(xp[k * d + j], __dmul_rn(t, vp[k * d + j]));
-            xp[k * d + j] = fmin(fmax(x, s.lb[j]), s.ub[j]);
-        }
-    for (int k = 0; k < K; k++) xw[k] = __dadd_rn(xw[k], __dmul_rn(t, vw[k]));
-    double weight_K = 1.0;
-    for (int k = 0; k < K - 1; k++) {
-        xw[k] = fmin(fmax(xw[k], 0.0), 1.0);
-        weight_K -= xw[k];
-    }
-    if (!s.fixw[K - 1]) xw[K - 1] = weight_K;
-    xw[K - 1] = fmax(xw[K - 1], 0.0);
-
-    // stop the particle when the boundary was hit
-    if (t != 1.0) {
-        for (int c = 0; c < K * d; c++) vp[c] = 0.0;
-        for (int k = 0; k < K; k++) vw[k] = 0.0;
-    }
+    kst_pso_move_particle(K, d, s.x_w + (size_t)i * K, s.x_pts + (size_t)i * K * d, s.p_w + (size_t)i * K,
+                          s.p_pts + (size_t)i * K * d, s.v_w + (size_t)i * K, s.v_pts + (size_t)i * K * d, s.g_w, s.g_pts,
+                          s.fixw, s.fixp, s.lb, s.ub, c1, c2, chi, KstRndPhilox{s.seed, iter, (uint32_t)i});
 }
 
 // pso_update_best!: strict '>', sequential semantics => the lowest index attaining the maximum
@@ -208,7 +90,7 @@ __global__ void k_pso_move(KstPsoDev s, uint32_t iter, double c1, double c2, dou
 // sum plus `offset` (what k_obj_finish would have written), computed here to save a launch per iteration.
 __global__ void __launch_bounds__(1024) k_pso_best(KstPsoDev s, int init, double *tr_fx, double *tr_pts, double *tr_w,
                                                    int slot, int *status, const double *__restrict__ partials,
-                                                   int n_blk, double offset)
+                                                   int n_blk, double offset, int nan_fill)
 {
     __shared__ double s_val[1024];
     __shared__ int s_idx[1024];
@@ -225,7 +107,7 @@ __global__ void __launch_bounds__(1024) k_pso_best(KstPsoDev s, int init, double
         if (partials) {
             double acc = 0.0;
             for (int b = 0; b < n_blk; b++) acc += partials[(size_t)i * n_blk + b];
-            f = acc + offset;
+            f = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : acc + offset;
             s.fx[i] = f;
         } else {
             f = s.fx[i];
@@ -285,9 +167,9 @@ __global__ void __launch_bounds__(1024) k_pso_best(KstPsoDev s, int init, double
     if (status && tid == 0 && *status == 0 && !s_notnan) *status = 2;
 }
 
-static KstPsoDev make_dev(const kst_problem *h)
+void kst_pso_make_dev(const kst_problem *h, KstPsoDev *out)
 {
-    KstPsoDev s;
+    KstPsoDev &s = *out;
     const KstPso &p = h->pso;
     s.S = p.S; s.K = p.K; s.d = h->d;
     s.x_pts = p.x_pts; s.x_w = p.x_w; s.p_pts = p.p_pts; s.p_w = p.p_w; s.v_pts = p.v_pts; s.v_w = p.v_w;
@@ -295,6 +177,12 @@ static KstPsoDev make_dev(const kst_problem *h)
     s.fixw = p.fixw; s.fixp = p.fixp;
     for (int j = 0; j < KST_MAX_D; j++) { s.lb[j] = h->lb[j]; s.ub[j] = h->ub[j]; }
     s.seed = p.seed;
+}
+
+static KstPsoDev make_dev(const kst_problem *h)
+{
+    KstPsoDev s;
+    kst_pso_make_dev(h, &s);
     return s;
 }
 
@@ -302,7 +190,7 @@ void kst_pso_free(kst_problem *h)
 {
     KstPso &p = h->pso;
     double **ptrs[] = {&p.x_pts, &p.x_w, &p.p_pts, &p.p_w, &p.v_pts, &p.v_w, &p.g_pts, &p.g_w,
-                       &p.fx, &p.fp, &p.fg, &p.tr_fx, &p.tr_pts, &p.tr_w};
+                       &p.fx, &p.fp, &p.fg, &p.tr_fx, &p.tr_pts, &p.tr_w, &p.x2_pts, &p.x2_w, &p.snap};
     for (auto q : ptrs) {
         if (*q) cudaFree(*q);
         *q = nullptr;
@@ -310,21 +198,57 @@ void kst_pso_free(kst_problem *h)
     if (p.fixw) cudaFree(p.fixw);
     if (p.fixp) cudaFree(p.fixp);
     p.fixw = p.fixp = nullptr;
+    if (p.bar) cudaFree(p.bar);
+    p.bar = nullptr;
+    p.bar_count = 0;
+    p.fused_off = 0;
     p.tr_cap = 0;
     p.S = p.K = 0;
 }
 
+// (Re)allocates the swarm for S particles of K points.  A swarm of the same shape as the previous one is reused as
+// it is: Exchange runs two optimizers per step, and cudaMalloc / cudaFree cost more than their iterations.
 int kst_pso_alloc(kst_problem *h, int S, int K)
 {
-    kst_pso_free(h);
     KstPso &p = h->pso;
+    if (p.S == S && p.K == K && p.x_pts) {
+        p.fused_off = 0;
+        return KST_OK;
+    }
+    // the trace buffers do not depend on the swarm's shape: keep them
+    double *tfx = p.tr_fx, *tpt = p.tr_pts, *tw = p.tr_w;
+    const int tcap = p.tr_cap;
+    p.tr_fx = p.tr_pts = p.tr_w = nullptr;
+    kst_pso_free(h);
+    p.tr_fx = tfx; p.tr_pts = tpt; p.tr_w = tw; p.tr_cap = tcap;
     const size_t np = (size_t)S * K * h->d, nw = (size_t)S * K;
     KST_CUDA(cudaMalloc(&p.x_pts, 8 * np)); KST_CUDA(cudaMalloc(&p.p_pts, 8 * np)); KST_CUDA(cudaMalloc(&p.v_pts, 8 * np));
     KST_CUDA(cudaMalloc(&p.x_w, 8 * nw)); KST_CUDA(cudaMalloc(&p.p_w, 8 * nw)); KST_CUDA(cudaMalloc(&p.v_w, 8 * nw));
     KST_CUDA(cudaMalloc(&p.g_pts, 8 * (size_t)K * h->d)); KST_CUDA(cudaMalloc(&p.g_w, 8 * (size_t)K));
     KST_CUDA(cudaMalloc(&p.fx, 8 * (size_t)S)); KST_CUDA(cudaMalloc(&p.fp, 8 * (size_t)S)); KST_CUDA(cudaMalloc(&p.fg, 8));
     KST_CUDA(cudaMalloc(&p.fixw, sizeof(int) * K)); KST_CUDA(cudaMalloc(&p.fixp, sizeof(int) * K));
+    KST_CUDA(cudaMalloc(&p.x2_pts, 16 * np)); KST_CUDA(cudaMalloc(&p.x2_w, 16 * nw));
+    KST_CUDA(cudaMalloc(&p.snap, 8 * (3 * (np + nw) + (size_t)K * (h->d + 1) + 2 * (size_t)S + 1)));
+    KST_CUDA(cudaMalloc(&p.bar, sizeof(unsigned long long)));
+    KST_CUDA(cudaMemsetAsync(p.bar, 0, sizeof(unsigned long long), h->stream));
+    p.bar_count = 0;
     p.S = S; p.K = K;
+    return KST_OK;
+}
+
+// trace buffers for n entries, sized for the largest design the handle can hold (swarms of any shape reuse them)
+int kst_pso_ensure_trace(kst_problem *h, int n)
+{
+    KstPso &p = h->pso;
+    if (n <= p.tr_cap) return KST_OK;
+    KST_CUDA(cudaStreamSynchronize(h->stream));
+    if (p.tr_fx) { KST_CUDA(cudaFree(p.tr_fx)); KST_CUDA(cudaFree(p.tr_pts)); KST_CUDA(cudaFree(p.tr_w)); }
+    p.tr_fx = p.tr_pts = p.tr_w = nullptr;
+    p.tr_cap = 0;
+    KST_CUDA(cudaMalloc(&p.tr_fx, sizeof(double) * n));
+    KST_CUDA(cudaMalloc(&p.tr_pts, sizeof(double) * n * KST_MAX_ROWS * h->d));
+    KST_CUDA(cudaMalloc(&p.tr_w, sizeof(double) * n * KST_MAX_ROWS));
+    p.tr_cap = n;
     return KST_OK;
 }
 
@@ -353,7 +277,8 @@ int kst_launch_pso_best(kst_problem *h, int init, int trace_slot)
     k_pso_best<<<1, 1024, 0, h->stream>>>(s, init, trace_slot >= 0 ? p.tr_fx : nullptr,
                                            trace_slot >= 0 ? p.tr_pts : nullptr, trace_slot >= 0 ? p.tr_w : nullptr,
                                            trace_slot >= 0 ? trace_slot : 0, init ? h->d_flag : nullptr,
-                                           p.pending_n_blk ? h->partials : nullptr, p.pending_n_blk, h->offset);
+                                           p.pending_n_blk ? h->partials : nullptr, p.pending_n_blk, p.pending_offset,
+                                           p.pending_nan);
     p.pending_n_blk = 0;
     KST_CUDA(cudaGetLastError());
     return KST_OK;

@@ -1,0 +1,160 @@
+// Device-side pieces of the particle swarm shared by the stand-alone kernels (kst_pso.cu) and the persistent swarm
+// kernel (kst_pso_fused.cuh): the counter-based random numbers, the device view of the swarm state, and the
+// velocity update + constrained move of ONE particle.
+//
+// The move must round exactly like the scalar reference arithmetic (src/pso.jl:143-171,
+// src/designmeasure-abstractpoint.jl:164-285, src/designregion.jl:114-135) whatever -fmad setting the including
+// translation unit is compiled with: every operation goes through the __d*_rn intrinsics, which the compiler
+// never contracts into an FMA.
+#pragma once
+#include <stdint.h>
+
+#include "../../include/kirstine_b200.h"
+
+#define KST_DINF (__longlong_as_double(0x7ff0000000000000LL))
+
+__device__ __forceinline__ void kst_philox(uint64_t seed, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                           uint32_t (&o)[4])
+{
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+    for (int round = 0; round < 10; round++) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    o[0] = c0; o[1] = c1; o[2] = c2; o[3] = c3;
+}
+
+__device__ __forceinline__ void kst_uniform2(uint64_t seed, uint32_t iter, uint32_t particle, uint32_t comp,
+                                             uint32_t stream, double &u0, double &u1)
+{
+    uint32_t o[4];
+    kst_philox(seed, iter, particle, comp, stream, o);
+    const uint64_t a = ((uint64_t)o[1] << 32) | o[0], b = ((uint64_t)o[3] << 32) | o[2];
+    u0 = (double)(a >> 11) * 0x1.0p-53;
+    u1 = (double)(b >> 11) * 0x1.0p-53;
+}
+
+struct KstPsoDev {
+    int S, K, d;
+    double *x_pts, *x_w, *p_pts, *p_w, *v_pts, *v_w, *g_pts, *g_w, *fx, *fp, *fg;
+    const int *fixw, *fixp;
+    double lb[KST_MAX_D], ub[KST_MAX_D];
+    uint64_t seed;
+};
+
+// the two uniforms of a velocity component straight from the counter-based generator ...
+struct KstRndPhilox {
+    uint64_t seed;
+    uint32_t iter, particle;
+    __device__ __forceinline__ void operator()(int c, double &r1, double &r2) const
+    {
+        kst_uniform2(seed, iter, particle, (uint32_t)c, 0, r1, r2);
+    }
+};
+// ... or from a table another set of threads has filled with the same numbers
+struct KstRndTable {
+    const double *r;  // [component][2]
+    __device__ __forceinline__ void operator()(int c, double &r1, double &r2) const
+    {
+        r1 = r[2 * c];
+        r2 = r[2 * c + 1];
+    }
+};
+
+// pso_update_velocity! + pso_update_position! for one particle.  x, v are updated in place; p (personal best) and g
+// (global best) are read.  rnd(c, r1, r2) yields the two uniforms of component c (weights first, then atoms:
+// ap_rand!(v, lb, ub), src/designmeasure-abstractpoint.jl:136-144).  All pointers may be global or shared memory.
+template <class RND>
+__device__ __forceinline__ void kst_pso_move_particle(const int K, const int d, double *xw, double *xp, const double *pw,
+                                                      const double *pp, double *vw, double *vp, const double *gw,
+                                                      const double *gp, const int *fixw, const int *fixp,
+                                                      const double *lb, const double *ub, const double c1,
+                                                      const double c2, const double chi, RND rnd)
+{
+    // pso_update_velocity!: v = ((v + (p-x) r1 c1) + (g-x) r2 c2) chi, fresh r1, r2 per component
+    for (int c = 0; c < K * (d + 1); c++) {
+        double r1, r2;
+        rnd(c, r1, r2);
+        const double x = c < K ? xw[c] : xp[c - K];
+        const double pb = c < K ? pw[c] : pp[c - K];
+        const double gb = c < K ? gw[c] : gp[c - K];
+        double *v = c < K ? &vw[c] : &vp[c - K];
+        double diffp = __dsub_rn(pb, x), diffg = __dsub_rn(gb, x);
+        diffp = __dmul_rn(diffp, r1);
+        diffg = __dmul_rn(diffg, r2);
+        diffp = __dmul_rn(diffp, c1);
+        diffg = __dmul_rn(diffg, c2);
+        double vv = *v;
+        vv = __dadd_rn(vv, diffp);
+        vv = __dadd_rn(vv, diffg);
+        *v = __dmul_rn(vv, chi);
+    }
+
+    // move_handle_fixed! (src/designmeasure-abstractpoint.jl:184-223)
+    double sum_vw_free = 0.0;
+    int n_fixw = 0;
+    for (int k = 0; k < K; k++) n_fixw += fixw[k] != 0;
+    for (int k = 0; k < K - 1; k++) {
+        if (fixw[k]) vw[k] = 0.0;
+        else sum_vw_free = __dadd_rn(sum_vw_free, vw[k]);
+    }
+    if (n_fixw != K && fixw[K - 1]) {
+        const double mean_free = __ddiv_rn(sum_vw_free, (double)(K - n_fixw));
+        for (int k = 0; k < K - 1; k++)
+            if (!fixw[k]) vw[k] = __dsub_rn(vw[k], mean_free);
+    }
+    for (int k = 0; k < K; k++)
+        if (fixp[k])
+            for (int j = 0; j < d; j++) vp[k * d + j] = 0.0;
+
+    // move_how_far (:225-248) with move_designpoint_how_far (src/designregion.jl:114-126)
+    double t = 1.0;
+    for (int k = 0; k < K; k++) {
+        double tk = 1.0;
+        for (int j = 0; j < d; j++) {
+            const double x = xp[k * d + j], v = vp[k * d + j];
+            const double probe = __dadd_rn(x, __dmul_rn(tk, v));
+            const double sl = probe > ub[j] ? __ddiv_rn(__dsub_rn(ub[j], x), v) : tk;
+            const double sr = probe < lb[j] ? __ddiv_rn(__dsub_rn(lb[j], x), v) : tk;
+            tk = fmin(sl, sr);
+        }
+        t = fmin(t, tk);
+    }
+    for (int k = 0; k < K - 1; k++) {
+        const double sk = __dadd_rn(xw[k], __dmul_rn(t, vw[k])) < 0 ? __ddiv_rn(-xw[k], vw[k]) : t;
+        t = fmin(sk, t);
+    }
+    {
+        const double sum_x = __dsub_rn(1.0, xw[K - 1]);
+        double sum_v = 0.0;
+        for (int k = 0; k < K - 1; k++) sum_v = __dadd_rn(sum_v, vw[k]);
+        const double sk = __dadd_rn(sum_x, __dmul_rn(t, sum_v)) > 1 ? __ddiv_rn(__dsub_rn(1.0, sum_x), sum_v) : t;
+        t = fmin(sk, t);
+    }
+    if (t < 1e-8) t = 0.0;
+
+    // move_add_v! (:250-285) with move_designpoint! (src/designregion.jl:129-135)
+    for (int k = 0; k < K; k++)
+        for (int j = 0; j < d; j++) {
+            const double x = __dadd_rn(xp[k * d + j], __dmul_rn(t, vp[k * d + j]));
+            xp[k * d + j] = fmin(fmax(x, lb[j]), ub[j]);
+        }
+    for (int k = 0; k < K; k++) xw[k] = __dadd_rn(xw[k], __dmul_rn(t, vw[k]));
+    double weight_K = 1.0;
+    for (int k = 0; k < K - 1; k++) {
+        xw[k] = fmin(fmax(xw[k], 0.0), 1.0);
+        weight_K = __dsub_rn(weight_K, xw[k]);
+    }
+    if (!fixw[K - 1]) xw[K - 1] = weight_K;
+    xw[K - 1] = fmax(xw[K - 1], 0.0);
+
+    // stop the particle when the boundary was hit
+    if (t != 1.0) {
+        for (int c = 0; c < K * d; c++) vp[c] = 0.0;
+        for (int k = 0; k < K; k++) vw[k] = 0.0;
+    }
+}
