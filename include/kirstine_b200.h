@@ -246,6 +246,24 @@ KST_API int kst_pso_get_state(kst_problem *h, double *x_points, double *x_weight
                       double *p_weights, double *g_points, double *g_weights, double *v_points,
                       double *v_weights, double *fx, double *fp, double *fg, int64_t *n_eval);
 
+/*
+ * optimize (src/optimize.jl:42-70) with a Pso optimizer in ONE call: optimizer_state (src/pso.jl:83-125), then
+ * iterations - 1 times tick! (src/pso.jl:127-141), with nothing returning to the host in between.  Arguments as
+ * kst_pso_init.  The traces have `iterations` entries like OptimizationResult.trace_fx / trace_x
+ * (src/optimize.jl:28-40): entry 0 is the initial state, entry i the maximum / maximizer after tick i; any of them
+ * may be NULL.  state0 (or NULL): the PsoState optimize keeps as trace_state[1] (src/optimize.jl:51-53), packed as
+ * x_points[S*K*d], x_weights[S*K], p_points, p_weights, v_points, v_weights, g_points[K*d], g_weights[K], fx[S],
+ * fp[S], fg -- 3*S*K*(d+1) + K*(d+1) + 2*S + 1 doubles.  *status as kst_pso_init (the ticks run even when it is
+ * non-zero; the reference throws instead, so discard the results then).  The swarm stays on the device:
+ * kst_pso_get_state and kst_pso_run continue from it.
+ * Problems whose evaluation grid fits one wave of CTAs run the whole call as one persistent kernel (tables staged
+ * once, one grid barrier per iteration); larger ones use three launches per iteration.  The results are identical.
+ */
+KST_API int kst_pso_optimize(kst_problem *h, int S, int K, int iterations, double c1, double c2,
+                             const double *proto_points, const double *proto_weights, int P, const int *fixw,
+                             const int *fixp, uint64_t seed, int mode, int *status, double *trace_fx,
+                             double *trace_points, double *trace_weights, double *state0);
+
 /* measurement helpers (bench.py): CUDA-event timing of the evaluation kernel on the handle's
  * stream, and a DFMA micro-kernel that measures this GPU's FP64 pipe peak. */
 KST_API int kst_profile_enable(kst_problem *h, int on);

@@ -50,6 +50,8 @@ SIGNATURES = {
     "kst_pso_init": (C.c_int, [_vp, C.c_int, C.c_int, C.c_double, C.c_double, _dp, _dp, C.c_int, _ip, _ip,
                                C.c_uint64, C.c_int, _ip]),
     "kst_pso_run": (C.c_int, [_vp, C.c_int, _dp, _dp, _dp]),
+    "kst_pso_optimize": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, _dp, _dp, C.c_int, _ip, _ip,
+                                   C.c_uint64, C.c_int, _ip, _dp, _dp, _dp, _dp]),
     "kst_pso_get_state": (C.c_int, [_vp] + [_dp] * 11 + [C.POINTER(C.c_int64)]),
     "kst_profile_enable": (C.c_int, [_vp, C.c_int]),
     "kst_profile_read": (C.c_int, [_vp, _dp, C.POINTER(C.c_int64)]),
@@ -260,6 +262,23 @@ class ProblemHandle:
         self._pso_dims = (S, K)
         return st.value
 
+    def pso_optimize(self, S, K, iterations, proto_points, proto_weights, fixw=None, fixp=None, seed=1, c1=2.05, c2=2.05,
+                     mode=PSO_MODE_OBJECTIVE, state0=True):
+        """optimize() in one call: (status, trace_fx[iterations], trace_points, trace_weights, state0 dict or None)."""
+        pw = f64(proto_weights).reshape(-1, K)
+        P = len(pw)
+        pp = f64(proto_points).reshape(P, K, self.d)
+        fw = i32(np.zeros(K) if fixw is None else fixw)
+        fp = i32(np.zeros(K) if fixp is None else fixp)
+        d = self.d
+        tfx, tp, tw = np.empty(iterations), np.empty((iterations, K, d)), np.empty((iterations, K))
+        snap = np.empty(3 * S * K * (d + 1) + K * (d + 1) + 2 * S + 1) if state0 else None
+        st = C.c_int(0)
+        check(lib().kst_pso_optimize(self._h, S, K, iterations, c1, c2, ptr(pp), ptr(pw), P, fw.ctypes.data_as(_ip),
+                                     fp.ctypes.data_as(_ip), seed, mode, C.byref(st), ptr(tfx), ptr(tp), ptr(tw), ptr(snap)))
+        self._pso_dims = (S, K)
+        return st.value, tfx, tp, tw, (unpack_state(snap, S, K, d) if state0 else None)
+
     def pso_run_async(self, n_iters):
         """Enqueue n_iters swarm iterations without copying traces back (no host synchronisation)."""
         check(lib().kst_pso_run(self._h, n_iters, None, None, None))
@@ -295,6 +314,18 @@ class ProblemHandle:
         n = C.c_int64(0)
         check(lib().kst_profile_read(self._h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+
+def unpack_state(snap, S, K, d):
+    """The packed PsoState of kst_pso_optimize / kst_exchange_run as the dict pso_state() returns (n_eval = S)."""
+    out, o = {}, 0
+    for key, shape in (("x_pts", (S, K, d)), ("x_w", (S, K)), ("p_pts", (S, K, d)), ("p_w", (S, K)), ("v_pts", (S, K, d)),
+                       ("v_w", (S, K)), ("g_pts", (K, d)), ("g_w", (K,)), ("fx", (S,)), ("fp", (S,))):
+        n = int(np.prod(shape))
+        out[key] = snap[o:o + n].reshape(shape).copy()
+        o += n
+    out["fg"], out["n_eval"] = float(snap[o]), S
+    return out
 
 
 def fp64_peak_probe(device=0):

@@ -491,6 +491,20 @@ extern "C" int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, 
     return KST_OK;
 }
 
+// after a synchronisation: did a persistent swarm kernel give up at its grid barrier?
+static int pso_check_barrier(kst_problem *h)
+{
+    KstPso &p = h->pso;
+    if (!p.bar || p.bar_count == 0) return KST_OK;
+    unsigned long long err = 0;
+    KST_CUDA(cudaMemcpy(&err, p.bar + 1, sizeof(err), cudaMemcpyDeviceToHost));
+    if (err) {
+        kst_set_error("persistent swarm kernel: grid barrier timed out (results invalid); set KST_NO_FUSED=1");
+        return KST_ECUDA;
+    }
+    return KST_OK;
+}
+
 // n_iters times tick! on the three-launch path (move, evaluation, best update), trace slots slot0, slot0 + 1, ...
 static int pso_ticks_unfused(kst_problem *h, int n_iters, int slot0)
 {
@@ -527,7 +541,10 @@ extern "C" int kst_pso_run(kst_problem *h, int n_iters, double *trace_fx, double
     if (trace_weights)
         KST_CUDA(cudaMemcpyAsync(trace_weights, p.tr_w, sizeof(double) * n_iters * p.K, cudaMemcpyDeviceToHost, h->stream));
     // without trace buffers nothing has to reach the host: the iterations stay queued on the handle's stream
-    if (trace_fx || trace_points || trace_weights) KST_CUDA(cudaStreamSynchronize(h->stream));
+    if (trace_fx || trace_points || trace_weights) {
+        KST_CUDA(cudaStreamSynchronize(h->stream));
+        return pso_check_barrier(h);
+    }
     return KST_OK;
 }
 
@@ -596,7 +613,7 @@ extern "C" int kst_pso_optimize(kst_problem *h, int S, int K, int iterations, do
     }
     KST_CUDA(cudaStreamSynchronize(h->stream));
     if (status) *status = st;
-    return KST_OK;
+    return pso_check_barrier(h);
 }
 
 extern "C" int kst_pso_get_state(kst_problem *h, double *x_points, double *x_weights, double *p_points, double *p_weights,
@@ -615,7 +632,7 @@ extern "C" int kst_pso_get_state(kst_problem *h, double *x_points, double *x_wei
         if (c.dst) KST_CUDA(cudaMemcpyAsync(c.dst, c.src, sizeof(double) * c.n, cudaMemcpyDeviceToHost, h->stream));
     KST_CUDA(cudaStreamSynchronize(h->stream));
     if (n_eval) *n_eval = p.n_eval;
-    return KST_OK;
+    return pso_check_barrier(h);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -229,8 +229,8 @@ int kst_pso_alloc(kst_problem *h, int S, int K)
     KST_CUDA(cudaMalloc(&p.fixw, sizeof(int) * K)); KST_CUDA(cudaMalloc(&p.fixp, sizeof(int) * K));
     KST_CUDA(cudaMalloc(&p.x2_pts, 16 * np)); KST_CUDA(cudaMalloc(&p.x2_w, 16 * nw));
     KST_CUDA(cudaMalloc(&p.snap, 8 * (3 * (np + nw) + (size_t)K * (h->d + 1) + 2 * (size_t)S + 1)));
-    KST_CUDA(cudaMalloc(&p.bar, sizeof(unsigned long long)));
-    KST_CUDA(cudaMemsetAsync(p.bar, 0, sizeof(unsigned long long), h->stream));
+    KST_CUDA(cudaMalloc(&p.bar, 2 * sizeof(unsigned long long)));  // arrival counter, error word
+    KST_CUDA(cudaMemsetAsync(p.bar, 0, 2 * sizeof(unsigned long long), h->stream));
     p.bar_count = 0;
     p.S = S; p.K = K;
     return KST_OK;

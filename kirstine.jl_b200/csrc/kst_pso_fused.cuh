@@ -47,15 +47,26 @@ struct KstFusedParams {
                                   // x_pts, x_w, p_pts, p_w, v_pts, v_w [S..], g_pts, g_w, fx[S], fp[S], fg
 };
 
+// ctr[0] counts arrivals; ctr[1] is an error word: a CTA that waits longer than 5 s gives up (the results are then
+// garbage, the host reports the error) instead of hanging the GPU should the grid ever not be co-resident.
 __device__ __forceinline__ void kst_grid_barrier(unsigned long long *ctr, unsigned long long target)
 {
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(ctr, 1ull);
-        unsigned long long v;
+        unsigned long long v, t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        unsigned spins = 0;
         do {
             asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(ctr) : "memory");
+            if (v < target && (++spins & 1023u) == 0) {
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 5000000000ull) {
+                    atomicExch(ctr + 1, 1ull);
+                    break;
+                }
+            }
         } while (v < target);
         __threadfence();
     }

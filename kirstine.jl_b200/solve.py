@@ -120,6 +120,22 @@ def optimize(h, optimizer, prototypes, fixw, fixp, mode, trace_state=False):
     """optimize (src/optimize.jl:42-70) with the whole swarm resident on the device."""
     t0 = time.time()
     K = numpoints(prototypes[0])
+    if not trace_state:
+        # the whole run in one call: nothing but the traces, the status and the initial state's snapshot come back
+        st, fx, px, pw, s0 = h.pso_optimize(optimizer.swarmsize, K, optimizer.iterations,
+                                            np.stack([p.points for p in prototypes]),
+                                            np.stack([p.weights for p in prototypes]), fixw, fixp, seed=_next_seed(),
+                                            c1=optimizer.c1, c2=optimizer.c2, mode=mode)
+        if st == 1:
+            raise RuntimeError("infinite objective value at best initial point")
+        if st == 2:
+            raise RuntimeError("objective evaluates to NaN on all initial points")
+        t_x = [_wrap_design(px[i], pw[i]) for i in range(optimizer.iterations)]
+        fxm = float(fx[-1])
+        if not math.isfinite(fxm):
+            warnings.warn("maximum is not finite")
+        return OptimizationResult(t_x[-1], fxm, t_x, [float(v) for v in fx], [PsoState(s0)],
+                                  optimizer.swarmsize * optimizer.iterations, time.time() - t0)
     st = h.pso_init(optimizer.swarmsize, K, np.stack([p.points for p in prototypes]),
                     np.stack([p.weights for p in prototypes]), fixw, fixp, seed=_next_seed(), c1=optimizer.c1,
                     c2=optimizer.c2, mode=mode)
