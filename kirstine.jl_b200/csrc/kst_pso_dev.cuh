@@ -46,7 +46,7 @@ struct KstPsoDev {
     uint64_t seed;
 };
 
-// the two uniforms of a velocity component straight from the counter-based generator ...
+// the two uniforms of a velocity component straight from the counter-based generator
 struct KstRndPhilox {
     uint64_t seed;
     uint32_t iter, particle;
@@ -55,15 +55,23 @@ struct KstRndPhilox {
         kst_uniform2(seed, iter, particle, (uint32_t)c, 0, r1, r2);
     }
 };
-// ... or from a table another set of threads has filled with the same numbers
-struct KstRndTable {
-    const double *r;  // [component][2]
-    __device__ __forceinline__ void operator()(int c, double &r1, double &r2) const
-    {
-        r1 = r[2 * c];
-        r2 = r[2 * c + 1];
-    }
-};
+// pso_update_velocity! (src/pso.jl:143-164) for ONE component: v = ((v + (p-x) r1 c1) + (g-x) r2 c2) chi.  Components
+// are independent of each other, so a caller may spread them over threads.
+__device__ __forceinline__ double kst_pso_velocity(double v, double x, double pb, double gb, double r1, double r2,
+                                                   double c1, double c2, double chi)
+{
+    double diffp = __dsub_rn(pb, x), diffg = __dsub_rn(gb, x);
+    diffp = __dmul_rn(diffp, r1);
+    diffg = __dmul_rn(diffg, r2);
+    diffp = __dmul_rn(diffp, c1);
+    diffg = __dmul_rn(diffg, c2);
+    v = __dadd_rn(v, diffp);
+    v = __dadd_rn(v, diffg);
+    return __dmul_rn(v, chi);
+}
+
+__device__ __forceinline__ void kst_pso_position(const int K, const int d, double *xw, double *xp, double *vw, double *vp,
+                                                 const int *fixw, const int *fixp, const double *lb, const double *ub);
 
 // pso_update_velocity! + pso_update_position! for one particle.  x, v are updated in place; p (personal best) and g
 // (global best) are read.  rnd(c, r1, r2) yields the two uniforms of component c (weights first, then atoms:
@@ -75,7 +83,7 @@ __device__ __forceinline__ void kst_pso_move_particle(const int K, const int d, 
                                                       const double *lb, const double *ub, const double c1,
                                                       const double c2, const double chi, RND rnd)
 {
-    // pso_update_velocity!: v = ((v + (p-x) r1 c1) + (g-x) r2 c2) chi, fresh r1, r2 per component
+    // fresh r1, r2 per component
     for (int c = 0; c < K * (d + 1); c++) {
         double r1, r2;
         rnd(c, r1, r2);
@@ -83,17 +91,16 @@ __device__ __forceinline__ void kst_pso_move_particle(const int K, const int d, 
         const double pb = c < K ? pw[c] : pp[c - K];
         const double gb = c < K ? gw[c] : gp[c - K];
         double *v = c < K ? &vw[c] : &vp[c - K];
-        double diffp = __dsub_rn(pb, x), diffg = __dsub_rn(gb, x);
-        diffp = __dmul_rn(diffp, r1);
-        diffg = __dmul_rn(diffg, r2);
-        diffp = __dmul_rn(diffp, c1);
-        diffg = __dmul_rn(diffg, c2);
-        double vv = *v;
-        vv = __dadd_rn(vv, diffp);
-        vv = __dadd_rn(vv, diffg);
-        *v = __dmul_rn(vv, chi);
+        *v = kst_pso_velocity(*v, x, pb, gb, r1, r2, c1, c2, chi);
     }
+    kst_pso_position(K, d, xw, xp, vw, vp, fixw, fixp, lb, ub);
+}
 
+// pso_update_position! (src/pso.jl:166-171) = ap_add!(x, v, constraints) for one particle whose velocity has been
+// updated: fixed components, largest feasible step, move, clamp, stop at the boundary.
+__device__ __forceinline__ void kst_pso_position(const int K, const int d, double *xw, double *xp, double *vw, double *vp,
+                                                 const int *fixw, const int *fixp, const double *lb, const double *ub)
+{
     // move_handle_fixed! (src/designmeasure-abstractpoint.jl:184-223)
     double sum_vw_free = 0.0;
     int n_fixw = 0;

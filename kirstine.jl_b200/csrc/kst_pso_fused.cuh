@@ -74,19 +74,95 @@ __device__ __forceinline__ void kst_grid_barrier(unsigned long long *ctr, unsign
 }
 
 // doubles of swarm state a CTA keeps in shared memory behind the particle tile
-__host__ __device__ inline size_t kst_fused_state_doubles(int S, int K, int d, int tile_p)
+__host__ __device__ inline size_t kst_fused_state_doubles(int S, int K, int d, int m, int tile_p)
 {
     const size_t KC = (size_t)K * (d + 1);
     return 3 * tile_p * KC      // x, v, p of the tile's particles
            + KC                 // g
            + (size_t)S          // personal-best values of the whole swarm
-           + 2 * tile_p * KC    // random numbers of one move
-           + tile_p;            // "improved" flags of the tile (as doubles: keeps everything 8-byte aligned)
+           + tile_p             // "improved" flags of the tile (as doubles: keeps everything 8-byte aligned)
+           + 2 * (size_t)tile_p * K * m;  // per-row scratch of the parallel tile build
 }
 template <class MF>
 __host__ __device__ inline size_t kst_fused_tile_doubles(int rows_max)
 {
     return (KstTile<MF>::bytes(rows_max) + 15) / 16 * 2;
+}
+
+// kst_build_tile (kst_objective_kernel.cuh) with the per-row work -- map_to_covariate!, the covariate-only
+// transcendentals, the square root of the row weight -- spread over one thread per (particle, row); one thread per
+// particle then compacts the rows in order and sums the weights in the reference's order, so the tile is the one
+// kst_build_tile builds, bit for bit.  pts / w: the tile's particles ([np][K][d], [np][K]); s_om / s_bd: scratch
+// of tile_p * K * m doubles each.  In the serial version the K * m logarithms of a sigmoid Emax particle are one
+// thread's dependent chain, which costs more than the evaluation itself on the reference's problem sizes.
+template <class MF>
+__device__ __forceinline__ void kst_build_tile_par(double *smem, const double *pts, const double *w, int np, int K,
+                                                   const KstModelParams &mp, int tile_p, const double *dcmax, double *s_om,
+                                                   double *s_bd)
+{
+    const int m = mp.m, rows_max = K * m;
+    constexpr int RW = KstTile<MF>::RW;
+    double *rows_all = KstTile<MF>::rows(smem);
+    for (int e = threadIdx.x; e < np * rows_max; e += KST_NT) {
+        const int i = e / rows_max, q = e % rows_max, k = q / m, u = q % m;
+        double pc[MF::NPC], varfac;
+        const bool trivial = MF::prep_row(pts + ((size_t)i * K + k) * mp.d, u, mp, pc, varfac);
+        const double om = w[(size_t)i * K + k] * varfac;
+        double sq = 0.0, bound = 0.0;
+        if (om != 0.0 && !trivial) {
+            sq = sqrt(om);
+            if (MF::FAST_EXP) bound = MF::arg_bound(pc, dcmax);
+            MF::post_row(pc, sq);
+        }
+        double *r = rows_all + ((size_t)i * rows_max + q) * RW;
+        r[0] = trivial ? -1.0 : sq;  // sq >= 0 for a live row; zero-weight rows are recognised by om == 0
+#pragma unroll
+        for (int c = 0; c < MF::NPC; c++) r[1 + c] = pc[c];
+        s_om[e] = om;
+        s_bd[e] = bound;
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < tile_p) {
+        const int i = threadIdx.x;
+        double *rows = rows_all + (size_t)i * rows_max * RW;
+        int na = 0, ntriv = 0;
+        double sw = 0.0, bound = 0.0;
+        if (i < np) {
+            for (int q = 0; q < rows_max; q++) {
+                const double om = s_om[i * rows_max + q];
+                sw += om;
+                if (om == 0.0) continue;
+                if (!(rows[q * RW] < 0.0)) {  // live row (a NaN weight stays a live row, as in kst_build_tile)
+                    bound = fmax(bound, s_bd[i * rows_max + q]);
+                    if (na != q) {
+#pragma unroll
+                        for (int c = 0; c < RW; c++) rows[na * RW + c] = rows[q * RW + c];
+                    }
+                    na++;
+                } else {
+                    ntriv++;
+                }
+            }
+        }
+        int rank = na + ((MF::CONST_COL >= 0 && ntriv > 0) ? 1 : 0);
+        if (MF::CONST_COL >= 0 && !(sw > 0.0 && sw < KST_INF)) rank = 0;
+        if (na == 0) {
+            double pc[MF::NPC], vf;
+            const double one = 1.0;
+            MF::prep_row(&one, 1, mp, pc, vf);
+            MF::post_row(pc, 0.0);
+            rows[0] = 0.0;
+#pragma unroll
+            for (int c = 0; c < MF::NPC; c++) rows[1 + c] = pc[c];
+            na = 1;
+        }
+        KstTile<MF>::sumw(smem, rows_max)[i] = sw;
+        KstTile<MF>::isumw(smem, rows_max)[i] = 1.0 / sw;
+        KstTile<MF>::nact(smem, rows_max)[i] = na;
+        KstTile<MF>::rank(smem, rows_max)[i] = rank;
+        KstTile<MF>::safe(smem, rows_max)[i] = (MF::FAST_EXP && dcmax && bound <= 700.0) ? 1 : 0;
+    }
+    __syncthreads();
 }
 
 // number of doubles of the packed state snapshot (KstFusedParams::snap)
@@ -125,8 +201,9 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_pso_fused(const KstFusedPa
     double *sg_w = st;            st += K;
     double *sg_p = st;            st += KD;
     double *s_fp = st;            st += S;
-    double *s_rand = st;          st += 2 * tp * KC;
-    double *s_impr = st;
+    double *s_impr = st;          st += tp;
+    double *s_om = st;            st += tp * rows_max;
+    double *s_bd = st;
 
     // the tile's particles, the global best and every personal-best value
     for (int e = tid; e < np * K; e += KST_NT) {
@@ -150,13 +227,22 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_pso_fused(const KstFusedPa
         if (!is_init) {
             // tick!: velocities and constrained move of the tile's particles (src/pso.jl:127-171)
             const uint32_t iter = fp.iter0 + (uint32_t)(step - (fp.first_is_init ? 1 : 0));
-            for (int e = tid; e < np * KC; e += KST_NT)
-                kst_uniform2(ps.seed, iter, (uint32_t)(p0 + e / KC), (uint32_t)(e % KC), 0, s_rand[2 * e], s_rand[2 * e + 1]);
+            // one thread per (particle, component) for the random numbers and the velocity, then one per particle for
+            // the constrained move (its sums run in the reference's order)
+            for (int e = tid; e < np * KC; e += KST_NT) {
+                const int i = e / KC, c = e % KC;
+                double r1, r2;
+                kst_uniform2(ps.seed, iter, (uint32_t)(p0 + i), (uint32_t)c, 0, r1, r2);
+                const bool isw = c < K;
+                const int o = isw ? i * K + c : i * KD + (c - K);
+                double *v = isw ? sv_w + o : sv_p + o;
+                *v = kst_pso_velocity(*v, isw ? sx_w[o] : sx_p[o], isw ? sp_w[o] : sp_p[o], isw ? sg_w[c] : sg_p[c - K], r1,
+                                      r2, fp.c1, fp.c2, fp.chi);
+            }
             __syncthreads();
             if (tid < np)
-                kst_pso_move_particle(K, d, sx_w + tid * K, sx_p + tid * KD, sp_w + tid * K, sp_p + tid * KD,
-                                      sv_w + tid * K, sv_p + tid * KD, sg_w, sg_p, ps.fixw, ps.fixp, ps.lb, ps.ub, fp.c1,
-                                      fp.c2, fp.chi, KstRndTable{s_rand + 2 * tid * KC});
+                kst_pso_position(K, d, sx_w + tid * K, sx_p + tid * KD, sv_w + tid * K, sv_p + tid * KD, ps.fixw, ps.fixp,
+                                 ps.lb, ps.ub);
             __syncthreads();
         }
         if (writer) {  // the moved positions, for whoever needs the new global best after the barrier
@@ -165,7 +251,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_pso_fused(const KstFusedPa
             for (int e = tid; e < np * KD; e += KST_NT) xp[e] = sx_p[e];
         }
         // pso_evaluate_objective!: this CTA's draw slice for its tile
-        kst_build_tile<MF>(smem, sx_p, sx_w, p0, S, K, prm.mp, tp, prm.dcmax, p0);  // ends with __syncthreads()
+        kst_build_tile_par<MF>(smem, sx_p, sx_w, np, K, prm.mp, tp, prm.dcmax, s_om, s_bd);  // ends with __syncthreads()
         double *pt = fp.partials2 + (size_t)par * S * nbx;
         kst_objective_cta<MF, CRIT, T, UNI, false>(prm, smem, tab, p0, bx, nbx, pt);
         kst_grid_barrier(fp.bar, fp.bar_base + (unsigned long long)(step + 1) * (unsigned long long)(nbx * gridDim.y));
@@ -311,7 +397,7 @@ int kst_fused_launch(kst_problem *h, KstFusedParams &fp, dim3 grid)
 {
     const int K = fp.obj.K;
     const size_t smem = sizeof(double) * (kst_fused_tile_doubles<MF>(K * h->m) +
-                                          kst_fused_state_doubles(fp.obj.S, K, h->d, fp.obj.tile_p));
+                                          kst_fused_state_doubles(fp.obj.S, K, h->d, h->m, fp.obj.tile_p));
     if (fp.obj.gd) return kst_fused_go<MF, KST_KCRIT_GD, 0, false>(h, fp, grid, smem);
     return h->crit == KST_CRIT_D   ? kst_fused_t<MF, 0>(h, fp, grid, smem)
            : h->crit == KST_CRIT_A ? kst_fused_t<MF, 1>(h, fp, grid, smem)
