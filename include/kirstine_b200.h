@@ -42,6 +42,8 @@ extern "C" {
 #define KST_ESTATE (-4)   /* call order violated (e.g. gateaux_eval before gateaux_prepare) */
 #define KST_ENCCL (-5)    /* NCCL unavailable or failed */
 #define KST_ELIMIT (-6)   /* size beyond a documented fixed limit */
+#define KST_ESINGULAR (-7)  /* kst_exchange_run: the reference's SingularException (singular candidate design) */
+#define KST_EOBJECTIVE (-8) /* kst_exchange_run: the reference's ErrorExceptions of optimizer_state (src/pso.jl:119-123) */
 
 /* Registered model families = device functors standing in for the user's jacobianmatrix!,
  * update_model_vcov!, unit_length, dimension (src/user.jl:18-98).  The reference ships no
@@ -263,6 +265,48 @@ KST_API int kst_pso_optimize(kst_problem *h, int S, int K, int iterations, doubl
                              const double *proto_points, const double *proto_weights, int P, const int *fixw,
                              const int *fixp, uint64_t seed, int mode, int *status, double *trace_fx,
                              double *trace_points, double *trace_weights, double *state0);
+
+/*
+ * solve_with(dp, ::Exchange, trace_state = false) (src/solve-exchange.jl:116-179) in one call: `steps` times
+ *   simplify (src/designproblem.jl:185-190) -> gateaux_constants -> optimize the Gateaux derivative over one-point
+ *   directions (prototypes: the candidate's points) -> prepend the direction (mixture, or simplify_merge with distance 0
+ *   when it is already in the support) -> optimize the weights with all points fixed.
+ * Both optimizers are Pso and run on the device (kst_pso_optimize); per step only the singularity flag, the direction
+ * and the new weights return to the host, where the K <= Kmax point bookkeeping is done.
+ *
+ * Exchange (src/solve-exchange.jl:15-69) as a plain struct.  maxweight / maxdist: simplify_args for simplify_drop /
+ * simplify_merge; unique_a / unique_b: the two keyword arguments of the registered covariate parameterizations'
+ * simplify_unique methods (docs/src/dtr.md:229-247: minposdose, minpostime; :498-523: minposdose, minposdelta), ignored
+ * by the others.  seed: the optimizers of step i (0-based) use the 2i-th and (2i+1)-th value of the sequence
+ * s -> s * 6364136223846793005 + 1442695040888963407 (mod 2^64) started at `seed`.
+ */
+typedef struct kst_exchange_options {
+    int steps;
+    int swarm_direction, iters_direction;
+    double c1_direction, c2_direction;
+    int swarm_weight, iters_weight;
+    double c1_weight, c2_weight;
+    double maxweight, maxdist, unique_a, unique_b;
+    uint64_t seed;
+} kst_exchange_options;
+/*
+ *  cand_points[K0*d], cand_weights[K0]  the strategy's candidate
+ *  Kmax        capacity, in design points, of every per-step output slot (a candidate never has more than
+ *              K0 + steps points); Kmax * m <= KST_MAX_ROWS
+ *  K_out, points_out[Kmax*d], weights_out[Kmax]   solution(er): the last weight optimizer's maximizer
+ *  dir_trace_fx[steps*iters_direction], dir_trace_x[steps*iters_direction*d]   trace_fx / trace_x of every direction run
+ *  w_trace_fx[steps*iters_weight]; w_trace_points / w_trace_weights: per step a slot of iters_weight*Kmax*d resp.
+ *              iters_weight*Kmax doubles holding iters_weight designs of w_K[step] points, packed
+ *  dir_state0 / w_state0 (or NULL)  per step the packed initial PsoState (layout: kst_pso_optimize), slots of
+ *              3*S*(d+1) + (d+1) + 2*S + 1 resp. 3*S*Kmax*(d+1) + Kmax*(d+1) + 2*S + 1 doubles
+ *  steps_done  completed steps (== steps on success)
+ * Any trace pointer may be NULL.  Errors: KST_ESINGULAR where the reference throws SingularException,
+ * KST_EOBJECTIVE for optimizer_state's two ErrorExceptions; outputs are then undefined beyond steps_done.
+ */
+KST_API int kst_exchange_run(kst_problem *h, const kst_exchange_options *opt, int K0, const double *cand_points,
+                             const double *cand_weights, int Kmax, int *K_out, double *points_out, double *weights_out,
+                             double *dir_trace_fx, double *dir_trace_x, double *w_trace_fx, double *w_trace_points,
+                             double *w_trace_weights, int *w_K, double *dir_state0, double *w_state0, int *steps_done);
 
 /* measurement helpers (bench.py): CUDA-event timing of the evaluation kernel on the handle's
  * stream, and a DFMA micro-kernel that measures this GPU's FP64 pipe peak. */

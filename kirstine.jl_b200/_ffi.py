@@ -59,6 +59,20 @@ SIGNATURES = {
     "kst_math_selftest": (C.c_int, [C.c_int, C.c_int64, _dp, _dp, _dp, _dp]),
 }
 
+
+
+class ExchangeOptions(C.Structure):
+    """kst_exchange_options (include/kirstine_b200.h)."""
+    _fields_ = [("steps", C.c_int), ("swarm_direction", C.c_int), ("iters_direction", C.c_int),
+                ("c1_direction", C.c_double), ("c2_direction", C.c_double), ("swarm_weight", C.c_int),
+                ("iters_weight", C.c_int), ("c1_weight", C.c_double), ("c2_weight", C.c_double),
+                ("maxweight", C.c_double), ("maxdist", C.c_double), ("unique_a", C.c_double), ("unique_b", C.c_double),
+                ("seed", C.c_uint64)]
+
+
+SIGNATURES["kst_exchange_run"] = (C.c_int, [_vp, C.POINTER(ExchangeOptions), C.c_int, _dp, _dp, C.c_int, _ip, _dp, _dp,
+                                            _dp, _dp, _dp, _dp, _dp, _ip, _dp, _dp, _ip])
+
 _lib = None
 
 
@@ -278,6 +292,41 @@ class ProblemHandle:
                                      fp.ctypes.data_as(_ip), seed, mode, C.byref(st), ptr(tfx), ptr(tp), ptr(tw), ptr(snap)))
         self._pso_dims = (S, K)
         return st.value, tfx, tp, tw, (unpack_state(snap, S, K, d) if state0 else None)
+
+    def exchange_run(self, cand_points, cand_weights, steps, opt_direction, opt_weight, maxweight=0.0, maxdist=0.0,
+                     unique_a=0.0, unique_b=0.0, seed=1, state0=True):
+        """kst_exchange_run.  opt_* = (swarmsize, iterations, c1, c2).  Returns a dict with the final candidate
+        (points, weights) and per step the direction / weight traces (and initial states when state0)."""
+        w0 = f64(cand_weights).ravel()
+        K0, d = len(w0), self.d
+        p0 = f64(cand_points).reshape(K0, d)
+        Kmax = K0 + steps
+        Sd, itd, Sw, itw = opt_direction[0], opt_direction[1], opt_weight[0], opt_weight[1]
+        o = ExchangeOptions(steps, Sd, itd, opt_direction[2], opt_direction[3], Sw, itw, opt_weight[2], opt_weight[3],
+                            maxweight, maxdist, unique_a, unique_b, seed)
+        Kout, done = C.c_int(0), C.c_int(0)
+        pts, w = np.empty((Kmax, d)), np.empty(Kmax)
+        dfx, dx = np.empty((steps, itd)), np.empty((steps, itd, d))
+        wfx, wp, ww = np.empty((steps, itw)), np.empty((steps, itw * Kmax * d)), np.empty((steps, itw * Kmax))
+        wK = np.zeros(steps, dtype=np.int32)
+        nsd = 3 * Sd * (d + 1) + (d + 1) + 2 * Sd + 1
+        nsw = 3 * Sw * Kmax * (d + 1) + Kmax * (d + 1) + 2 * Sw + 1
+        sd = np.empty((steps, nsd)) if state0 else None
+        sw = np.empty((steps, nsw)) if state0 else None
+        check(lib().kst_exchange_run(self._h, C.byref(o), K0, ptr(p0), ptr(w0), Kmax, C.byref(Kout), ptr(pts), ptr(w),
+                                     ptr(dfx), ptr(dx), ptr(wfx), ptr(wp), ptr(ww), wK.ctypes.data_as(_ip), ptr(sd), ptr(sw),
+                                     C.byref(done)))
+        K = Kout.value
+        out = dict(points=pts[:K].copy(), weights=w[:K].copy(), dir_fx=dfx, dir_x=dx, w_fx=wfx, w_K=wK, w_points=[],
+                   w_weights=[], dir_state0=[], w_state0=[])
+        for s_ in range(steps):
+            k = int(wK[s_])
+            out["w_points"].append(wp[s_, :itw * k * d].reshape(itw, k, d).copy())
+            out["w_weights"].append(ww[s_, :itw * k].reshape(itw, k).copy())
+            if state0:
+                out["dir_state0"].append(unpack_state(sd[s_], Sd, 1, d))
+                out["w_state0"].append(unpack_state(sw[s_], Sw, k, d))
+        return out
 
     def pso_run_async(self, n_iters):
         """Enqueue n_iters swarm iterations without copying traces back (no host synchronisation)."""

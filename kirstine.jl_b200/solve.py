@@ -8,6 +8,7 @@ import numpy as np
 
 from . import _ffi
 from .designmeasure import DesignMeasure, mixture, numpoints, one_point_design, simplify_merge, sort_points
+from .models import CovariateParameterization
 from .problem import objective, simplify
 
 # ------------------------------------------------------------------------------------------------
@@ -224,7 +225,66 @@ def _solve_with_direct(dp, strategy, trace_state):  # src/solve-directmaximizati
     return DirectMaximizationResult(or_)
 
 
+def _exchange_unique_args(dp, simplify_args):
+    """The keyword arguments a registered covariate parameterization's simplify_unique takes, as the two doubles of
+    kst_exchange_options; None when the arguments cannot be expressed that way (the caller then steps in Python)."""
+    from .models import CopyBoth, EquidistantTimes
+    extra = {k: v for k, v in simplify_args.items() if k not in ("maxweight", "maxdist")}
+    if isinstance(dp.cp, CopyBoth):
+        names = ("minposdose", "minpostime")
+    elif isinstance(dp.cp, EquidistantTimes):
+        names = ("minposdose", "minposdelta")
+    else:
+        return (0.0, 0.0) if not extra and type(dp.cp).simplify_unique is CovariateParameterization.simplify_unique else None
+    if any(k not in names for k in extra):
+        return None
+    return float(extra.get(names[0], 0)), float(extra.get(names[1], 0))
+
+
+def _solve_with_exchange_device(dp, strategy, ua_ub):
+    """The whole Exchange loop behind kst_exchange_run (one C-ABI call, both optimizers on the device)."""
+    candidate = strategy.candidate
+    _check_compatible(candidate, dp.dr)
+    od, ow = strategy.optimizer_direction, strategy.optimizer_weight
+    seed0 = _seed_counter[0]
+    for _ in range(2 * strategy.steps):     # the call consumes the same seeds as 2 * steps optimize() calls would
+        _next_seed()
+    t0 = time.time()
+    try:
+        r = dp.handle().exchange_run(candidate.points, candidate.weights, strategy.steps,
+                                     (od.swarmsize, od.iterations, od.c1, od.c2), (ow.swarmsize, ow.iterations, ow.c1, ow.c2),
+                                     maxweight=strategy.simplify_args.get("maxweight", 0),
+                                     maxdist=strategy.simplify_args.get("maxdist", 0), unique_a=ua_ub[0], unique_b=ua_ub[1],
+                                     seed=seed0)
+    except _ffi.EngineError as exc:
+        if exc.code == -7:
+            raise ArithmeticError("SingularException") from exc
+        if exc.code == -8:
+            raise RuntimeError(str(exc).split(": ", 1)[-1]) from exc
+        raise
+    secs = (time.time() - t0) / (2 * strategy.steps)
+    ors_d, ors_w = [], []
+    for s_ in range(strategy.steps):
+        tx = [_wrap_design(r["dir_x"][s_, i].reshape(1, -1), [1.0]) for i in range(od.iterations)]
+        fx = [float(v) for v in r["dir_fx"][s_]]
+        ors_d.append(OptimizationResult(tx[-1], fx[-1], tx, fx, [PsoState(r["dir_state0"][s_])],
+                                        od.swarmsize * od.iterations, secs))
+        tx = [_wrap_design(r["w_points"][s_][i], r["w_weights"][s_][i]) for i in range(ow.iterations)]
+        fx = [float(v) for v in r["w_fx"][s_]]
+        if not math.isfinite(fx[-1]):
+            warnings.warn("maximum is not finite")
+        ors_w.append(OptimizationResult(tx[-1], fx[-1], tx, fx, [PsoState(r["w_state0"][s_])],
+                                        ow.swarmsize * ow.iterations, secs))
+    return ExchangeResult(ors_d, ors_w)
+
+
 def _solve_with_exchange(dp, strategy, trace_state):  # src/solve-exchange.jl:116-179
+    if not trace_state and isinstance(strategy.optimizer_direction, Pso) and isinstance(strategy.optimizer_weight, Pso):
+        ua_ub = _exchange_unique_args(dp, strategy.simplify_args)
+        if ua_ub is not None:
+            return _solve_with_exchange_device(dp, strategy, ua_ub)
+    # trace_state = True (every iteration's swarm is wanted on the host) or a simplify_unique the library does not
+    # know: the same loop, one C-ABI call per optimizer run
     candidate = strategy.candidate
     _check_compatible(candidate, dp.dr)
     h = dp.handle()

@@ -178,30 +178,6 @@ def test_public_evaluators_semantics():  # test/designproblem.jl:75-167
     np.testing.assert_allclose(M, np.array([[16, 6, -6], [6, 3, -3], [-6, -3, 3]]) / 16, rtol=1e-14)
 
 
-def test_exchange_strategy():  # test/solve-exchange.jl:69-88 + src/solve-exchange.jl:116-179
-    prior = kb.PriorSample([kb.TPCParameter(*t) for t in wl.tpc_prior(50, seed=1)])
-    dp = kb.DesignProblem(criterion=kb.DCriterion(), region=kb.DesignInterval(time=(0, 48)), model=kb.TPCModel(sigma=1),
-                          covariate_parameterization=kb.CopyTime(), prior_knowledge=prior)
-    kb.seed(1357)
-    cand = kb.DesignMeasure(([0.5], 0.4), ([3.0], 0.3), ([30.0], 0.3))
-    str_ = kb.Exchange(optimizer_direction=kb.Pso(iterations=20, swarmsize=25),
-                       optimizer_weight=kb.Pso(iterations=20, swarmsize=25), steps=6, candidate=cand,
-                       simplify_args=dict(maxweight=1e-4, maxdist=2e-3))
-    d, r = kb.solve(dp, str_, maxweight=1e-3, maxdist=1e-2)
-    assert len(r.ord) == len(r.orw) == 6
-    assert all(np.all(np.diff(o.trace_fx) >= 0) for o in r.ord + r.orw)
-    assert all(kb.numpoints(o.maximizer) == 1 for o in r.ord)
-    assert kb.objective(d, dp) > kb.objective(cand, dp)
-    # the Gateaux derivative at the result is (nearly) non-positive on a grid: equivalence theorem
-    gd = kb.gateauxderivative(d, [kb.one_point_design([t]) for t in np.exp(np.linspace(np.log(0.05), np.log(48), 200))], dp)
-    assert gd.max() < 0.5      # small swarms and six steps only: D-efficiency >= exp(-max gd / r) ~ 0.85
-    # compares well with direct maximisation on the same problem
-    kb.seed(2468)
-    dm, _ = kb.solve(dp, kb.DirectMaximization(optimizer=kb.Pso(iterations=100, swarmsize=50),
-                                               prototype=kb.DesignMeasure(([0.3], 1 / 3), ([2.0], 1 / 3), ([20.0], 1 / 3))))
-    assert kb.efficiency(d, dm, dp) > 0.97
-
-
 def test_gateauxderivative_grid_export(tmp_path):
     """Headless form of plot_gateauxderivative (src/plot.jl:103-187; sizes as checked in test/plot.jl:17-60)."""
     import kirstine_b200 as kb
