@@ -479,12 +479,14 @@ extern "C" int kst_pso_init(kst_problem *h, int S, int K, double c1, double c2, 
     int rc = pso_setup(h, S, K, c1, c2, proto_points, proto_weights, P, fixw, fixp, seed, mode);
     if (rc) return rc;
     KstPso &p = h->pso;
+    rc = kst_pso_ensure_trace(h, 1);
+    if (rc) return rc;
     rc = pso_evaluate(h);
     if (rc) return rc;
     rc = kst_launch_pso_best(h, 1, -1);
     if (rc) return rc;
     int st = 0;
-    KST_CUDA(cudaMemcpyAsync(&st, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    KST_CUDA(cudaMemcpyAsync(&st, p.d_status, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     KST_CUDA(cudaStreamSynchronize(h->stream));
     p.iter = 1;
     if (status) *status = st;
@@ -535,14 +537,14 @@ extern "C" int kst_pso_run(kst_problem *h, int n_iters, double *trace_fx, double
     if (rc == 1) rc = pso_ticks_unfused(h, n_iters, 0);
     else if (rc == KST_OK) { p.iter += n_iters; p.n_eval += (int64_t)p.S * n_iters; }
     if (rc) return rc;
-    if (trace_fx) KST_CUDA(cudaMemcpyAsync(trace_fx, p.tr_fx, sizeof(double) * n_iters, cudaMemcpyDeviceToHost, h->stream));
-    if (trace_points)
-        KST_CUDA(cudaMemcpyAsync(trace_points, p.tr_pts, sizeof(double) * n_iters * p.K * h->d, cudaMemcpyDeviceToHost, h->stream));
-    if (trace_weights)
-        KST_CUDA(cudaMemcpyAsync(trace_weights, p.tr_w, sizeof(double) * n_iters * p.K, cudaMemcpyDeviceToHost, h->stream));
     // without trace buffers nothing has to reach the host: the iterations stay queued on the handle's stream
     if (trace_fx || trace_points || trace_weights) {
-        KST_CUDA(cudaStreamSynchronize(h->stream));
+        const double *fx, *pts, *w;
+        rc = kst_pso_fetch(h, 0, nullptr, &fx, &pts, &w, nullptr);
+        if (rc) return rc;
+        if (trace_fx) memcpy(trace_fx, fx, sizeof(double) * n_iters);
+        if (trace_points) memcpy(trace_points, pts, sizeof(double) * n_iters * p.K * h->d);
+        if (trace_weights) memcpy(trace_weights, w, sizeof(double) * n_iters * p.K);
         return pso_check_barrier(h);
     }
     return KST_OK;
@@ -562,7 +564,7 @@ int kst_pso_optimize_enqueue(kst_problem *h, int S, int K, int iterations, doubl
     rc = kst_pso_ensure_trace(h, iterations);
     if (rc) return rc;
     p.iter = 1;  // the first move is iteration 1 (key of its random numbers), as after kst_pso_init
-    rc = kst_launch_pso_fused(h, iterations, 1, 0, 1, h->d_flag, want_snapshot ? p.snap : nullptr);
+    rc = kst_launch_pso_fused(h, iterations, 1, 0, 1, p.d_status, want_snapshot ? p.snap : nullptr);
     if (rc == KST_OK) {
         p.iter = iterations;
         p.n_eval = (int64_t)S * iterations;
@@ -599,19 +601,14 @@ extern "C" int kst_pso_optimize(kst_problem *h, int S, int K, int iterations, do
     int rc = kst_pso_optimize_enqueue(h, S, K, iterations, c1, c2, proto_points, proto_weights, P, fixw, fixp, seed, mode,
                                       state0 != nullptr);
     if (rc) return rc;
-    KstPso &p = h->pso;
     int st = 0;
-    KST_CUDA(cudaMemcpyAsync(&st, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    if (trace_fx) KST_CUDA(cudaMemcpyAsync(trace_fx, p.tr_fx, sizeof(double) * iterations, cudaMemcpyDeviceToHost, h->stream));
-    if (trace_points)
-        KST_CUDA(cudaMemcpyAsync(trace_points, p.tr_pts, sizeof(double) * iterations * K * h->d, cudaMemcpyDeviceToHost, h->stream));
-    if (trace_weights)
-        KST_CUDA(cudaMemcpyAsync(trace_weights, p.tr_w, sizeof(double) * iterations * K, cudaMemcpyDeviceToHost, h->stream));
-    if (state0) {
-        const size_t n = 3 * (size_t)S * K * (h->d + 1) + (size_t)K * (h->d + 1) + 2 * (size_t)S + 1;
-        KST_CUDA(cudaMemcpyAsync(state0, p.snap, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
-    }
-    KST_CUDA(cudaStreamSynchronize(h->stream));
+    const double *fx, *pts, *w, *snap;
+    rc = kst_pso_fetch(h, state0 != nullptr, &st, &fx, &pts, &w, &snap);
+    if (rc) return rc;
+    if (trace_fx) memcpy(trace_fx, fx, sizeof(double) * iterations);
+    if (trace_points) memcpy(trace_points, pts, sizeof(double) * iterations * K * h->d);
+    if (trace_weights) memcpy(trace_weights, w, sizeof(double) * iterations * K);
+    if (state0) memcpy(state0, snap, sizeof(double) * (3 * (size_t)S * K * (h->d + 1) + (size_t)K * (h->d + 1) + 2 * (size_t)S + 1));
     if (status) *status = st;
     return pso_check_barrier(h);
 }

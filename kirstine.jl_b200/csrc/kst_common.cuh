@@ -62,20 +62,26 @@ struct KstPso {
     double c1 = 0, c2 = 0;
     uint64_t seed = 0;
     int64_t n_eval = 0;
-    // device state: points are [S][K][d], weights [S][K]
+    // device state: points are [S][K][d], weights [S][K]; all carved out of `arena` (kst_pso_alloc)
     double *x_pts = nullptr, *x_w = nullptr, *p_pts = nullptr, *p_w = nullptr, *v_pts = nullptr,
            *v_w = nullptr, *g_pts = nullptr, *g_w = nullptr, *fx = nullptr, *fp = nullptr,
            *fg = nullptr;
     int *fixw = nullptr, *fixp = nullptr;
-    // per-run trace buffers (device), grown on demand
-    double *tr_fx = nullptr, *tr_pts = nullptr, *tr_w = nullptr;
-    int tr_cap = 0;
     // persistent swarm kernel (kst_pso_fused.cuh): published positions [2][S][K*d] / [2][S][K], grid barrier counter
-    // and how far it has counted, packed snapshot of the state after the initial evaluation
-    double *x2_pts = nullptr, *x2_w = nullptr, *snap = nullptr;
+    // (+ error word) and how far it has counted
+    double *x2_pts = nullptr, *x2_w = nullptr;
     unsigned long long *bar = nullptr;
     unsigned long long bar_count = 0;
     int fused_off = 0;  // this swarm does not fit the persistent kernel: do not ask again
+    double *arena = nullptr;
+    size_t arena_cap = 0;  // doubles
+    // what a run sends back, carved out of `out` (device) and mirrored in `h_out` (pinned host) by
+    // kst_pso_ensure_trace: status word, trace of tr_n entries, packed snapshot of the initial state
+    int *d_status = nullptr;
+    double *tr_fx = nullptr, *tr_pts = nullptr, *tr_w = nullptr, *snap = nullptr;
+    int tr_n = 0;
+    double *out = nullptr, *h_out = nullptr;
+    size_t out_cap = 0;    // doubles
 };
 
 struct kst_problem {
@@ -164,6 +170,8 @@ int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, dou
 int kst_pso_alloc(kst_problem *h, int S, int K);
 void kst_pso_free(kst_problem *h);
 int kst_pso_ensure_trace(kst_problem *h, int n);
+int kst_pso_fetch(kst_problem *h, int with_snap, int *status, const double **tr_fx, const double **tr_pts,
+                  const double **tr_w, const double **snap);
 struct KstPsoDev;
 void kst_pso_make_dev(const kst_problem *h, KstPsoDev *out);
 int kst_launch_pso_init(kst_problem *h, const double *d_proto_pts, const double *d_proto_w, int P);

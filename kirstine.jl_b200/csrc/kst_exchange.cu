@@ -161,11 +161,10 @@ extern "C" int kst_exchange_run(kst_problem *h, const kst_exchange_options *opt,
         return s;
     };
     std::vector<int> zeros(KST_MAX_ROWS, 0), ones(KST_MAX_ROWS, 1);
-    std::vector<double> protos, proto_w, tr_fx(itd > itw ? itd : itw), tr_x((size_t)(itd > itw ? itd : itw) * Kmax * d),
-        tr_w((size_t)(itd > itw ? itd : itw) * Kmax);
+    std::vector<double> protos, proto_w;
+    const double *tr_fx, *tr_x, *tr_w, *snap;  // into the handle's pinned mirror of the last run's output block
     const size_t snap_d = 3 * (size_t)Sd * (d + 1) + (size_t)(d + 1) + 2 * (size_t)Sd + 1;
     const size_t snap_w = 3 * (size_t)Sw * Kmax * (d + 1) + (size_t)Kmax * (d + 1) + 2 * (size_t)Sw + 1;
-    KstPso &p = h->pso;
     for (int step = 0; step < opt->steps; step++) {
         // simplify the result of the previous iteration
         simplify_unique(h, c, opt->unique_a, opt->unique_b);
@@ -188,17 +187,15 @@ extern "C" int kst_exchange_run(kst_problem *h, const kst_exchange_options *opt,
                                       zeros.data(), zeros.data(), next_seed(), KST_PSO_MODE_GATEAUX, dir_state0 != nullptr);
         if (rc) return rc;
         int st = 0;
-        KST_CUDA(cudaMemcpyAsync(&st, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-        KST_CUDA(cudaMemcpyAsync(tr_fx.data(), p.tr_fx, sizeof(double) * itd, cudaMemcpyDeviceToHost, h->stream));
-        KST_CUDA(cudaMemcpyAsync(tr_x.data(), p.tr_pts, sizeof(double) * itd * d, cudaMemcpyDeviceToHost, h->stream));
-        if (dir_state0)
-            KST_CUDA(cudaMemcpyAsync(dir_state0 + (size_t)step * snap_d, p.snap, sizeof(double) * snap_d, cudaMemcpyDeviceToHost, h->stream));
-        KST_CUDA(cudaStreamSynchronize(h->stream));
+        rc = kst_pso_fetch(h, dir_state0 != nullptr, &st, &tr_fx, &tr_x, &tr_w, &snap);
+        if (rc) return rc;
+        if (dir_state0) memcpy(dir_state0 + (size_t)step * snap_d, snap, sizeof(double) * snap_d);
         if (st == 1) { kst_set_error("infinite objective value at best initial point"); return KST_EOBJECTIVE; }
         if (st == 2) { kst_set_error("objective evaluates to NaN on all initial points"); return KST_EOBJECTIVE; }
-        if (dir_trace_fx) memcpy(dir_trace_fx + (size_t)step * itd, tr_fx.data(), sizeof(double) * itd);
-        if (dir_trace_x) memcpy(dir_trace_x + (size_t)step * itd * d, tr_x.data(), sizeof(double) * itd * d);
-        const double *dir = tr_x.data() + (size_t)(itd - 1) * d;
+        if (dir_trace_fx) memcpy(dir_trace_fx + (size_t)step * itd, tr_fx, sizeof(double) * itd);
+        if (dir_trace_x) memcpy(dir_trace_x + (size_t)step * itd * d, tr_x, sizeof(double) * itd * d);
+        double dir[KST_MAX_D];
+        memcpy(dir, tr_x + (size_t)(itd - 1) * d, sizeof(double) * d);
         // append (prepend) this point to the candidate
         bool in_support = false;
         for (int k = 0; k < c.K && !in_support; k++) in_support = memcmp(dir, &c.pts[k * d], sizeof(double) * d) == 0;
@@ -218,25 +215,21 @@ extern "C" int kst_exchange_run(kst_problem *h, const kst_exchange_options *opt,
         rc = kst_pso_optimize_enqueue(h, Sw, c.K, itw, opt->c1_weight, opt->c2_weight, c.pts.data(), c.w.data(), 1,
                                       zeros.data(), ones.data(), next_seed(), KST_PSO_MODE_OBJECTIVE, w_state0 != nullptr);
         if (rc) return rc;
-        KST_CUDA(cudaMemcpyAsync(&st, h->d_flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-        KST_CUDA(cudaMemcpyAsync(tr_fx.data(), p.tr_fx, sizeof(double) * itw, cudaMemcpyDeviceToHost, h->stream));
-        KST_CUDA(cudaMemcpyAsync(tr_x.data(), p.tr_pts, sizeof(double) * itw * c.K * d, cudaMemcpyDeviceToHost, h->stream));
-        KST_CUDA(cudaMemcpyAsync(tr_w.data(), p.tr_w, sizeof(double) * itw * c.K, cudaMemcpyDeviceToHost, h->stream));
-        if (w_state0) {
-            const size_t n = 3 * (size_t)Sw * c.K * (d + 1) + (size_t)c.K * (d + 1) + 2 * (size_t)Sw + 1;
-            KST_CUDA(cudaMemcpyAsync(w_state0 + (size_t)step * snap_w, p.snap, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
-        }
-        KST_CUDA(cudaStreamSynchronize(h->stream));
+        rc = kst_pso_fetch(h, w_state0 != nullptr, &st, &tr_fx, &tr_x, &tr_w, &snap);
+        if (rc) return rc;
+        if (w_state0)
+            memcpy(w_state0 + (size_t)step * snap_w, snap,
+                   sizeof(double) * (3 * (size_t)Sw * c.K * (d + 1) + (size_t)c.K * (d + 1) + 2 * (size_t)Sw + 1));
         if (st == 1) { kst_set_error("infinite objective value at best initial point"); return KST_EOBJECTIVE; }
         if (st == 2) { kst_set_error("objective evaluates to NaN on all initial points"); return KST_EOBJECTIVE; }
-        if (w_trace_fx) memcpy(w_trace_fx + (size_t)step * itw, tr_fx.data(), sizeof(double) * itw);
+        if (w_trace_fx) memcpy(w_trace_fx + (size_t)step * itw, tr_fx, sizeof(double) * itw);
         // per step the traces are packed with the step's own K (w_K[step]) inside a slot sized for Kmax
-        if (w_trace_points) memcpy(w_trace_points + (size_t)step * itw * Kmax * d, tr_x.data(), sizeof(double) * itw * c.K * d);
-        if (w_trace_weights) memcpy(w_trace_weights + (size_t)step * itw * Kmax, tr_w.data(), sizeof(double) * itw * c.K);
+        if (w_trace_points) memcpy(w_trace_points + (size_t)step * itw * Kmax * d, tr_x, sizeof(double) * itw * c.K * d);
+        if (w_trace_weights) memcpy(w_trace_weights + (size_t)step * itw * Kmax, tr_w, sizeof(double) * itw * c.K);
         if (w_K) w_K[step] = c.K;
         // the maximizer becomes the next candidate (its points are the fixed ones)
-        memcpy(c.w.data(), tr_w.data() + (size_t)(itw - 1) * c.K, sizeof(double) * c.K);
-        memcpy(c.pts.data(), tr_x.data() + (size_t)(itw - 1) * c.K * d, sizeof(double) * c.K * d);
+        memcpy(c.w.data(), tr_w + (size_t)(itw - 1) * c.K, sizeof(double) * c.K);
+        memcpy(c.pts.data(), tr_x + (size_t)(itw - 1) * c.K * d, sizeof(double) * c.K * d);
         if (steps_done) *steps_done = step + 1;
     }
     *K_out = c.K;

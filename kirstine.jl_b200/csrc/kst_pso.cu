@@ -189,66 +189,93 @@ static KstPsoDev make_dev(const kst_problem *h)
 void kst_pso_free(kst_problem *h)
 {
     KstPso &p = h->pso;
-    double **ptrs[] = {&p.x_pts, &p.x_w, &p.p_pts, &p.p_w, &p.v_pts, &p.v_w, &p.g_pts, &p.g_w,
-                       &p.fx, &p.fp, &p.fg, &p.tr_fx, &p.tr_pts, &p.tr_w, &p.x2_pts, &p.x2_w, &p.snap};
-    for (auto q : ptrs) {
-        if (*q) cudaFree(*q);
-        *q = nullptr;
-    }
-    if (p.fixw) cudaFree(p.fixw);
-    if (p.fixp) cudaFree(p.fixp);
-    p.fixw = p.fixp = nullptr;
-    if (p.bar) cudaFree(p.bar);
-    p.bar = nullptr;
-    p.bar_count = 0;
-    p.fused_off = 0;
-    p.tr_cap = 0;
-    p.S = p.K = 0;
+    if (p.arena) cudaFree(p.arena);
+    if (p.out) cudaFree(p.out);
+    if (p.h_out) cudaFreeHost(p.h_out);
+    p = KstPso();
 }
 
-// (Re)allocates the swarm for S particles of K points.  A swarm of the same shape as the previous one is reused as
-// it is: Exchange runs two optimizers per step, and cudaMalloc / cudaFree cost more than their iterations.
+// Carves the swarm for S particles of K points out of ONE device allocation that only ever grows: Exchange alternates
+// between two swarm shapes every step, and a cudaMalloc / cudaFree pair costs more than a short optimizer run.
 int kst_pso_alloc(kst_problem *h, int S, int K)
 {
     KstPso &p = h->pso;
-    if (p.S == S && p.K == K && p.x_pts) {
-        p.fused_off = 0;
-        return KST_OK;
+    const size_t np = (size_t)S * K * h->d, nw = (size_t)S * K, kd = (size_t)K * h->d;
+    // doubles: barrier words (2), x p v (3 np + 3 nw), published positions (2 np + 2 nw), g, fx, fp, fg, fixw / fixp
+    const size_t need = 2 + 5 * (np + nw) + kd + K + 2 * (size_t)S + 1 + (size_t)K + 2;
+    if (need > p.arena_cap) {
+        KST_CUDA(cudaStreamSynchronize(h->stream));
+        if (p.arena) KST_CUDA(cudaFree(p.arena));
+        p.arena = nullptr;
+        p.arena_cap = 0;
+        const size_t cap = need + need / 2;
+        KST_CUDA(cudaMalloc(&p.arena, sizeof(double) * cap));
+        p.arena_cap = cap;
+        KST_CUDA(cudaMemsetAsync(p.arena, 0, 2 * sizeof(double), h->stream));  // arrival counter, error word
+        p.bar_count = 0;
     }
-    // the trace buffers do not depend on the swarm's shape: keep them
-    double *tfx = p.tr_fx, *tpt = p.tr_pts, *tw = p.tr_w;
-    const int tcap = p.tr_cap;
-    p.tr_fx = p.tr_pts = p.tr_w = nullptr;
-    kst_pso_free(h);
-    p.tr_fx = tfx; p.tr_pts = tpt; p.tr_w = tw; p.tr_cap = tcap;
-    const size_t np = (size_t)S * K * h->d, nw = (size_t)S * K;
-    KST_CUDA(cudaMalloc(&p.x_pts, 8 * np)); KST_CUDA(cudaMalloc(&p.p_pts, 8 * np)); KST_CUDA(cudaMalloc(&p.v_pts, 8 * np));
-    KST_CUDA(cudaMalloc(&p.x_w, 8 * nw)); KST_CUDA(cudaMalloc(&p.p_w, 8 * nw)); KST_CUDA(cudaMalloc(&p.v_w, 8 * nw));
-    KST_CUDA(cudaMalloc(&p.g_pts, 8 * (size_t)K * h->d)); KST_CUDA(cudaMalloc(&p.g_w, 8 * (size_t)K));
-    KST_CUDA(cudaMalloc(&p.fx, 8 * (size_t)S)); KST_CUDA(cudaMalloc(&p.fp, 8 * (size_t)S)); KST_CUDA(cudaMalloc(&p.fg, 8));
-    KST_CUDA(cudaMalloc(&p.fixw, sizeof(int) * K)); KST_CUDA(cudaMalloc(&p.fixp, sizeof(int) * K));
-    KST_CUDA(cudaMalloc(&p.x2_pts, 16 * np)); KST_CUDA(cudaMalloc(&p.x2_w, 16 * nw));
-    KST_CUDA(cudaMalloc(&p.snap, 8 * (3 * (np + nw) + (size_t)K * (h->d + 1) + 2 * (size_t)S + 1)));
-    KST_CUDA(cudaMalloc(&p.bar, 2 * sizeof(unsigned long long)));  // arrival counter, error word
-    KST_CUDA(cudaMemsetAsync(p.bar, 0, 2 * sizeof(unsigned long long), h->stream));
-    p.bar_count = 0;
+    double *q = p.arena;
+    p.bar = (unsigned long long *)q; q += 2;
+    p.x_pts = q; q += np; p.p_pts = q; q += np; p.v_pts = q; q += np; p.x2_pts = q; q += 2 * np;
+    p.x_w = q; q += nw; p.p_w = q; q += nw; p.v_w = q; q += nw; p.x2_w = q; q += 2 * nw;
+    p.g_pts = q; q += kd; p.g_w = q; q += K;
+    p.fx = q; q += S; p.fp = q; q += S; p.fg = q; q += 1;
+    p.fixw = (int *)q; p.fixp = p.fixw + K;
+    p.fused_off = 0;
     p.S = S; p.K = K;
+    p.tr_n = 0;  // the output block has to be carved again for this shape
     return KST_OK;
 }
 
-// trace buffers for n entries, sized for the largest design the handle can hold (swarms of any shape reuse them)
+// doubles of the packed PsoState snapshot (layout: KstFusedParams::snap)
+static size_t snapshot_doubles(int S, int K, int d)
+{
+    return 3 * (size_t)S * K * (d + 1) + (size_t)K * (d + 1) + 2 * (size_t)S + 1;
+}
+
+// Carves what a run of n trace entries sends back to the host out of one device block, mirrored by a pinned host
+// block, so that everything returns in ONE copy: [status word | trace_fx n | trace_points n K d | trace_weights n K |
+// snapshot of the initial state].
 int kst_pso_ensure_trace(kst_problem *h, int n)
 {
     KstPso &p = h->pso;
-    if (n <= p.tr_cap) return KST_OK;
+    const size_t kd = (size_t)p.K * h->d;
+    const size_t need = 1 + (size_t)n * (1 + kd + p.K) + snapshot_doubles(p.S, p.K, h->d);
+    if (need > p.out_cap) {
+        KST_CUDA(cudaStreamSynchronize(h->stream));
+        if (p.out) KST_CUDA(cudaFree(p.out));
+        if (p.h_out) KST_CUDA(cudaFreeHost(p.h_out));
+        p.out = p.h_out = nullptr;
+        p.out_cap = 0;
+        const size_t cap = need + need / 2;
+        KST_CUDA(cudaMalloc(&p.out, sizeof(double) * cap));
+        KST_CUDA(cudaHostAlloc(&p.h_out, sizeof(double) * cap, cudaHostAllocDefault));
+        p.out_cap = cap;
+    }
+    p.d_status = (int *)p.out;
+    p.tr_fx = p.out + 1;
+    p.tr_pts = p.tr_fx + n;
+    p.tr_w = p.tr_pts + (size_t)n * kd;
+    p.snap = p.tr_w + (size_t)n * p.K;
+    p.tr_n = n;
+    return KST_OK;
+}
+
+// Brings the output block of the last run back in one copy and waits for it.  The pointers (into the pinned host
+// mirror, valid until the next run) follow the device layout; snap only when with_snap.
+int kst_pso_fetch(kst_problem *h, int with_snap, int *status, const double **tr_fx, const double **tr_pts,
+                  const double **tr_w, const double **snap)
+{
+    KstPso &p = h->pso;
+    const size_t kd = (size_t)p.K * h->d;
+    const size_t n = 1 + (size_t)p.tr_n * (1 + kd + p.K) + (with_snap ? snapshot_doubles(p.S, p.K, h->d) : 0);
+    KST_CUDA(cudaMemcpyAsync(p.h_out, p.out, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
     KST_CUDA(cudaStreamSynchronize(h->stream));
-    if (p.tr_fx) { KST_CUDA(cudaFree(p.tr_fx)); KST_CUDA(cudaFree(p.tr_pts)); KST_CUDA(cudaFree(p.tr_w)); }
-    p.tr_fx = p.tr_pts = p.tr_w = nullptr;
-    p.tr_cap = 0;
-    KST_CUDA(cudaMalloc(&p.tr_fx, sizeof(double) * n));
-    KST_CUDA(cudaMalloc(&p.tr_pts, sizeof(double) * n * KST_MAX_ROWS * h->d));
-    KST_CUDA(cudaMalloc(&p.tr_w, sizeof(double) * n * KST_MAX_ROWS));
-    p.tr_cap = n;
+    if (status) *status = *(const int *)p.h_out;
+    if (tr_fx) *tr_fx = p.h_out + 1;
+    if (tr_pts) *tr_pts = p.h_out + 1 + p.tr_n;
+    if (tr_w) *tr_w = p.h_out + 1 + p.tr_n + (size_t)p.tr_n * kd;
+    if (snap) *snap = p.h_out + 1 + (size_t)p.tr_n * (1 + kd + p.K);
     return KST_OK;
 }
 
@@ -276,7 +303,7 @@ int kst_launch_pso_best(kst_problem *h, int init, int trace_slot)
     KstPso &p = h->pso;
     k_pso_best<<<1, 1024, 0, h->stream>>>(s, init, trace_slot >= 0 ? p.tr_fx : nullptr,
                                            trace_slot >= 0 ? p.tr_pts : nullptr, trace_slot >= 0 ? p.tr_w : nullptr,
-                                           trace_slot >= 0 ? trace_slot : 0, init ? h->d_flag : nullptr,
+                                           trace_slot >= 0 ? trace_slot : 0, init ? p.d_status : nullptr,
                                            p.pending_n_blk ? h->partials : nullptr, p.pending_n_blk, p.pending_offset,
                                            p.pending_nan);
     p.pending_n_blk = 0;
