@@ -68,6 +68,14 @@ extern "C" {
  *   KST_MODEL_SINLOGREG  docs/src/extend-model.md:330-355  predictor a sin(2 pi b (t - c)), theta = (a, b, c) */
 #define KST_MODEL_LINLOGREG 6
 #define KST_MODEL_SINLOGREG 7
+/* A NonlinearRegression whose unit covariance Sigma(c) is NOT diagonal -- what update_model_workspace! /
+ * average_fishermatrix! (src/model-nonlinear-regression.jl:39-49,60-86: potrf! of Sigma(c_k), trsm! of every unit's
+ * Jacobian) allow for any user model, none of the reference's own examples uses, and the other registered families
+ * (diagonal Sigma) do not exercise:
+ *   KST_MODEL_VUAR  mean function, parameters and covariates of KST_MODEL_VU, errors within a unit AR(1)-correlated:
+ *                   Sigma_ij = sigma_squared rho^|i-j| sqrt((1 + t_i)(1 + t_j)); params {sigma_squared, rho}, |rho| < 1;
+ *                   rho = 0 is KST_MODEL_VU.  Covariate parameterization KST_CP_EQUITIME, unit length m <= KST_MAX_UNIT. */
+#define KST_MODEL_VUAR 8
 
 /* covariate parameterizations = map_to_covariate! (src/user.jl:68):
  *   KST_CP_COPY      CopyDose / CopyTime / JustCopy: covariate = design point (src/user.jl:185-216)

@@ -13,6 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("KST_LIB_PATH") or os.path.join(_HERE, "libkirstine_b200.so")
 
 MODEL_EMAX, MODEL_SIGEMAX, MODEL_TPC, MODEL_VU, MODEL_DTR, MODEL_LINLOGREG, MODEL_SINLOGREG = 1, 2, 3, 4, 5, 6, 7
+MODEL_VUAR = 8
 CP_COPY, CP_EQUITIME = 0, 1
 CP_DTR_COPYBOTH, CP_DTR_FIXEDDOSE, CP_DTR_FIXEDTIMES, CP_DTR_EQUIDISTANT, CP_DTR_LOGEQUIDISTANT = 2, 3, 4, 5, 6
 CRIT_D, CRIT_A, CRIT_DEXP = 0, 1, 2

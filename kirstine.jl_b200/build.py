@@ -18,7 +18,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 # per-file extras: the swarm move must round exactly like the scalar reference arithmetic
 EXTRA = {"kst_pso.cu": ["-fmad=false"]}
 SOURCES = ["kst_api.cu", "kst_comm.cu", "kst_objective.cu", "kst_obj_inst_a.cu", "kst_obj_inst_b.cu", "kst_obj_inst_c.cu", "kst_obj_inst_d.cu",
-           "kst_obj_inst_e.cu", "kst_gateaux.cu", "kst_pso.cu", "kst_exchange.cu"]
+           "kst_obj_inst_e.cu", "kst_obj_inst_f.cu", "kst_gateaux.cu", "kst_pso.cu", "kst_exchange.cu"]
 
 
 def _newer(target, deps):

@@ -52,6 +52,7 @@ static int model_dims(int model_id, int d, int *r, int *ndc)
     case KST_MODEL_TPC: *r = KstTpc::R; *ndc = KstTpc::NDC; return 0;
     case KST_MODEL_VU: *r = KstVu::R; *ndc = KstVu::NDC; return 0;
     case KST_MODEL_DTR: *r = KstDtr::R; *ndc = KstDtr::NDC; return 0;
+    case KST_MODEL_VUAR: *r = KstVuAr::R; *ndc = KstVuAr::NDC; return 0;
     }
     return -1;
 }
@@ -64,7 +65,7 @@ extern "C" int kst_problem_destroy(kst_problem *h)
     kst_comm_release(h);
     kst_pso_free(h);
     void *ptrs[] = {h->theta, h->pw, h->dc, h->cs, h->aux, h->reg, h->partials, h->stage_pts, h->stage_w, h->stage_fx,
-                    h->gA, h->gAp, h->gtrB, h->g_wtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials};
+                    h->gA, h->gAp, h->gtrB, h->g_wtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials, h->gd_ones};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
@@ -99,9 +100,13 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
     int want_d = 1, want_ncp = 0;
     bool ok_m = m == 1, ok_cp = cp_id == KST_CP_COPY;
     if (model_id == KST_MODEL_LINLOGREG) want_d = d;  // range checked by model_dims
-    if (model_id == KST_MODEL_VU) {
+    if (model_id == KST_MODEL_VU || model_id == KST_MODEL_VUAR) {
         ok_m = m >= 1 && m <= KST_MAX_UNIT;
         ok_cp = cp_id == KST_CP_EQUITIME;
+        if (model_id == KST_MODEL_VUAR && (n_model_params < 2 || !model_params || !(fabs(model_params[1]) < 1.0) || !(model_params[0] > 0.0))) {
+            kst_set_error("KST_MODEL_VUAR needs model_params = {sigma_squared > 0, rho with |rho| < 1}");
+            return KST_EINVAL;
+        }
     } else if (model_id == KST_MODEL_DTR) {
         ok_m = m >= 1 && m <= KST_MAX_UNIT;
         switch (cp_id) {

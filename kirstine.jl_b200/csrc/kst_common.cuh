@@ -51,6 +51,7 @@ void kst_set_error(const char *fmt, ...);
     case KST_FID_LINLOGREG + 2: { using MF = KstLinLogReg<2>; __VA_ARGS__; } break; \
     case KST_FID_LINLOGREG + 3: { using MF = KstLinLogReg<3>; __VA_ARGS__; } break; \
     case KST_MODEL_SINLOGREG: { using MF = KstSinLogReg; __VA_ARGS__; } break; \
+    case KST_MODEL_VUAR: { using MF = KstVuAr; __VA_ARGS__; } break;     \
     default: kst_set_error("unregistered model id %d", id); return KST_EINVAL; \
     }
 
@@ -126,6 +127,8 @@ struct kst_problem {
     int *d_flag = nullptr;     // 16 bytes: device flag word (singular detection) + one double of scratch at offset 8
     double *gd_dirs = nullptr, *gd_out = nullptr, *gd_partials = nullptr;
     size_t gd_cap = 0, gd_partials_cap = 0;
+    double *gd_ones = nullptr;  // unit weights for directions evaluated through the objective kernel (dense covariance)
+    size_t gd_ones_cap = 0;
 
     KstPso pso;
 

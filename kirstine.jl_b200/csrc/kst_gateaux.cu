@@ -17,8 +17,7 @@
 // per (direction, draw) pair; the next chunk is fetched into registers while the current one is
 // evaluated.  The draw range is split over gridDim.y so that one wave of CTAs fills the GPU (split
 // taken from the kernel's occupancy); partial sums are combined in fixed order.
-#include "kst_common.cuh"
-#include "kst_linalg.cuh"
+#include "kst_objective_kernel.cuh"
 
 #ifndef KST_GD_UNROLL
 #define KST_GD_UNROLL 4
@@ -73,35 +72,50 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
                                   double *__restrict__ gAp, double *__restrict__ gtrB, double *__restrict__ wtrB, int *flag)
 {
     constexpr int R = MF::R, RW = KstRowW<MF>::RW;
-    extern __shared__ __align__(16) double smem[];  // rows[K*m][RW], sw, (na, rank)
+    extern __shared__ __align__(16) double smem[];  // rows[K*m][RW], sw, (na, rank); dense covariance: a KstTile
     __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
     const KstTab tab = kst_math_init(s_mathtab);
     double *rows = smem;
     double *s_sw = smem + (size_t)K * mp.m * RW;
     int *s_na = (int *)(s_sw + 1);
-    if (threadIdx.x == 0) {
-        double sw;
-        int rank;
-        s_na[0] = kst_build_rows<MF>(rows, sw, rank, pts, w, K, mp);
-        s_na[1] = rank;
-        *s_sw = sw;
+    int design_rank;
+    if constexpr (KstDense<MF>::value) {
+        // the design as a one-particle tile of the objective kernel: unit factors and all (ends with __syncthreads())
+        kst_build_tile<MF>(smem, pts, w, 0, 1, K, mp, 1);
+        design_rank = KstTile<MF>::rank(smem, K * mp.m)[0];
+    } else {
+        if (threadIdx.x == 0) {
+            double sw;
+            int rank;
+            s_na[0] = kst_build_rows<MF>(rows, sw, rank, pts, w, K, mp);
+            s_na[1] = rank;
+            *s_sw = sw;
+        }
+        __syncthreads();
+        design_rank = s_na[1];
     }
-    __syncthreads();
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= N) return;
     double dcv[MF::NDC], M[KstPacked<R>::N];
 #pragma unroll
     for (int c = 0; c < MF::NDC; c++) dcv[c] = dc[(size_t)c * ld + j];
+    if constexpr (KstDense<MF>::value) {
+        const int rows_max = K * mp.m;
+        kst_fisher<MF>(M, (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem)), KstTile<MF>::nact(smem, rows_max)[0],
+                       KstTile<MF>::sumw(smem, rows_max)[0], dcv, tab,
+                       (unsigned)__cvta_generic_to_shared(KstTile<MF>::lmat(smem, rows_max)), mp.m);
+    } else {
 #pragma unroll
-    for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
-    const int na = *s_na;
-    for (int i = 0; i < na; i++) {
-        double g[R];
-        MF::row(rows + i * RW + 1, dcv, rows[i * RW], g, tab);
-        kst_accum<R, MF::CONST_COL>(M, g);
+        for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
+        const int na = *s_na;
+        for (int i = 0; i < na; i++) {
+            double g[R];
+            MF::row(rows + i * RW + 1, dcv, rows[i * RW], g, tab);
+            kst_accum<R, MF::CONST_COL>(M, g);
+        }
+        constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
+        if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = *s_sw;
     }
-    constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
-    if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = *s_sw;
     // regularised normal approximation: informationmatrix!(afm, na) adds R (docs/src/extend-approximation.md:69-79)
     double Rt[KstPacked<R>::N];
 #pragma unroll
@@ -112,7 +126,7 @@ __global__ void k_gateaux_prepare(const double *__restrict__ dc, const double *_
 
     double L[R][R], dv[R], dinv[R];
     bool ok = kst_ldlt<R, false>(M, L, dv, dinv, true);
-    ok = ok && (reg || s_na[1] >= R);  // fewer rows than parameters: singular by construction
+    ok = ok && (reg || design_rank >= R);  // fewer rows than parameters: singular by construction
     // Mt^-1 = Li' diag(dinv) Li with Li = L^-1 (unit lower)
     double Li[R][R];
 #pragma unroll
@@ -489,6 +503,12 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
     if (live) partials[g * gridDim.y + blockIdx.y] = acc;
 }
 
+__global__ void k_fill(double *x, double v, int64_t n)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] = v;
+}
+
 __global__ void k_gd_finish(const double *__restrict__ partials, int n_split, double offset, int singular,
                             double *__restrict__ out, int64_t G)
 {
@@ -521,7 +541,10 @@ int kst_launch_gateaux_prepare(kst_problem *h, int K, const double *d_pts, const
     const int nt = 128;
     const unsigned nb = (unsigned)((h->N + nt - 1) / nt);
     KST_MODEL_SWITCH(h->model_id, {
-        const size_t smem = sizeof(double) * ((size_t)K * h->m * KstRowW<MF>::RW + 2);
+        const size_t smem = KstDense<MF>::value ? KstTile<MF>::bytes(K * h->m)
+                                                : sizeof(double) * ((size_t)K * h->m * KstRowW<MF>::RW + 2);
+        if (smem + sizeof(double) * KST_MATH_SMEM > 48 * 1024)
+            KST_CUDA(cudaFuncSetAttribute(k_gateaux_prepare<MF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_gateaux_prepare<MF><<<nb, nt, smem, h->stream>>>(h->dc, h->cs, h->aux, h->pw, h->ld, h->reg, h->N, h->crit, h->trafo,
                                                            h->t, d_pts, d_w, K, h->mp, h->gA, h->gAp, h->gtrB, wtrB, h->d_flag);
     });
@@ -622,6 +645,23 @@ int kst_launch_gateaux_eval(kst_problem *h, int64_t G, const double *d_dirs, dou
     if (G < 1) {
         kst_set_error("gateaux_eval: need G >= 1");
         return KST_EINVAL;
+    }
+    bool dense = false;
+    KST_MODEL_SWITCH(h->model_id, dense = KstDense<MF>::value);
+    if (dense) {
+        // a dense unit covariance couples the rows of a unit: the directions go through the objective kernel with the
+        // Gateaux integrand as the per-draw value (kst_objective_kernel.cuh), which whitens units; weights are 1
+        if (G > 65535 * KST_TILE_P) { kst_set_error("gateaux_eval: at most %d directions per call for this model", 65535 * KST_TILE_P); return KST_ELIMIT; }
+        if ((size_t)G > h->gd_ones_cap) {
+            if (h->gd_ones) KST_CUDA(cudaFree(h->gd_ones));
+            h->gd_ones = nullptr;
+            h->gd_ones_cap = 0;
+            KST_CUDA(cudaMalloc(&h->gd_ones, sizeof(double) * G));
+            h->gd_ones_cap = (size_t)G;
+            k_fill<<<(unsigned)((G + 255) / 256), 256, 0, h->stream>>>(h->gd_ones, 1.0, G);
+            KST_CUDA(cudaGetLastError());
+        }
+        return kst_launch_objective(h, (int)G, 1, d_dirs, h->gd_ones, d_out, nullptr, 1);
     }
     int n_split = 1;
     int rc = KST_OK;

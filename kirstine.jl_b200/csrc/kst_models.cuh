@@ -183,6 +183,55 @@ struct KstVu : KstTpc {
     }
 };
 
+// Trait: the unit covariance Sigma(c) of the family is a dense m x m matrix, i.e. its update_model_vcov!
+// (src/user.jl:85) fills more than the diagonal.  Such a family provides
+//     static void vcov(const double *z, const KstModelParams &mp, double *S)     S: m x m, column-major, full
+// and the kernels do what update_model_workspace! / average_fishermatrix! do with it
+// (src/model-nonlinear-regression.jl:39-49,60-86): Cholesky factor Sigma = U'U once per design point, every unit's
+// Jacobian whitened as U^-T J before the rank-m update.  Families with a diagonal Sigma (all of the reference's own
+// examples) keep the cheaper form: one scalar `varfac` per row folded into the row weight.
+template <class MF>
+struct KstDense {
+    static constexpr bool value = false;
+};
+
+// Vector units with correlated errors: the mean function and covariates of VUMod (test/example-vector.jl:9-50: m
+// measurements at times (i-1) z), unit covariance AR(1)-correlated with the time-dependent variances of VUMod,
+//     Sigma_ij = sigma_squared rho^|i-j| sqrt((1 + t_i)(1 + t_j)),     |rho| < 1.
+// rho = 0 is VUMod itself.  model_params = {sigma_squared, rho}.  Not a model of the reference's tests or docs: it is
+// the registered example of a NonlinearRegression whose Sigma(c) is not diagonal, which the reference supports
+// for every user model through potrf! + trsm!.
+struct KstVuAr : KstTpc {
+    __device__ static void prep_draw(const double *th, const KstModelParams &, double *dc, double *cs)
+    {
+        dc[0] = -th[0];
+        dc[1] = -th[1];
+        cs[0] = th[2];
+        cs[1] = -th[2];
+        cs[2] = 1.0;  // sigma_squared lives in Sigma
+    }
+    __device__ static bool prep_row(const double *z, int i, const KstModelParams &, double *pc, double &varfac)
+    {
+        pc[0] = (double)i * z[0];
+        pc[1] = 0.0;
+        varfac = 1.0;
+        return false;  // no row of a correlated unit can be dropped on its own
+    }
+    __device__ static void vcov(const double *z, const KstModelParams &mp, double *S)
+    {
+        const int m = mp.m;
+        for (int j = 0; j < m; j++)
+            for (int i = 0; i < m; i++) {
+                const double ti = (double)i * z[0], tj = (double)j * z[0];
+                S[i + j * m] = mp.v[0] * pow(mp.v[1], (double)(i > j ? i - j : j - i)) * sqrt((1.0 + ti) * (1.0 + tj));
+            }
+    }
+};
+template <>
+struct KstDense<KstVuAr> {
+    static constexpr bool value = true;
+};
+
 // dose-time-response model: test/example-dtr.jl:27-47, docs/src/dtr.md:87-129.  theta = (a, e, e0, emax, ec50)
 //   A = exp(-a t), B = exp(-e t), C = B - A, rd = e - a, den = dose C a - rd ec50, w = 1/den
 //   row = [-dose ec50 emax (A t a rd + e C) w^2, dose a ec50 emax (B t rd + C) w^2, 1, dose a C w, dose a emax C rd w^2]

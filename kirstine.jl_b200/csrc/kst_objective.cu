@@ -100,7 +100,8 @@ __global__ void k_infomatrix(const double *dc, const double *cs, const double *r
     double dcv[MF::NDC], M[KstPacked<R>::N];
     for (int c = 0; c < MF::NDC; c++) dcv[c] = dc[(size_t)c * ld + j];
     kst_fisher<MF>(M, (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem)), KstTile<MF>::nact(smem, rows_max)[0],
-                   KstTile<MF>::sumw(smem, rows_max)[0], dcv, tab);
+                   KstTile<MF>::sumw(smem, rows_max)[0], dcv, tab,
+                   (unsigned)__cvta_generic_to_shared(KstTile<MF>::lmat(smem, rows_max)), mp.m);
     for (int a = 0; a < R; a++)
         for (int b = a; b < R; b++) {
             const double mt = M[kst_pidx<R>(a, b)] + (reg ? reg[(size_t)kst_pidx<R>(a, b) * ld + j] : 0.0);

@@ -48,12 +48,54 @@ struct KstTile {
     __device__ static int *rank(double *s, int rows_max) { return nact(s, rows_max) + KST_TILE_P; }
     // 1 when every exp argument of the particle is provably within +-700 for every draw (no exponent clamp needed)
     __device__ static int *safe(double *s, int rows_max) { return rank(s, rows_max) + KST_TILE_P; }
+    // Families with a dense unit covariance (KstDense): per particle the packed lower factors L_k = sqrt(w_k) U_k^-T of
+    // its units, m (m + 1) / 2 doubles each, K m (m + 1) / 2 <= rows_max * LW in all
+    static constexpr int LW = (KST_MAX_UNIT + 2) / 2;
+    __host__ __device__ static constexpr size_t base_doubles(int rows_max)
+    {
+        return (size_t)KST_TILE_P * rows_max * RW + 2 * KST_TILE_P + KST_TILE_P * (KST_NT / 32) +
+               (sizeof(int) * 3 * KST_TILE_P + 15) / 16 * 2;
+    }
+    __device__ static double *lmat(double *s, int rows_max) { return s + base_doubles(rows_max); }
     __host__ __device__ static size_t bytes(int rows_max)
     {
-        return sizeof(double) * ((size_t)KST_TILE_P * rows_max * RW + 2 * KST_TILE_P + KST_TILE_P * (KST_NT / 32)) +
-               sizeof(int) * 3 * KST_TILE_P;
+        return sizeof(double) * (base_doubles(rows_max) + (KstDense<MF>::value ? (size_t)KST_TILE_P * rows_max * LW : 0));
     }
 };
+
+// update_model_workspace! for one design point of a dense-covariance family (src/model-nonlinear-regression.jl:39-49):
+// Sigma = U'U (upper Cholesky, the loop order of LAPACK's unblocked potrf), then Lw = sw U^-T packed by rows
+// (Lw[i (i + 1) / 2 + l], l <= i), so that the whitened, weighted Jacobian of the unit is Lw J -- what trsm!('L','U','T','N')
+// followed by the weight of syrk! computes (:79-83).  Returns false when Sigma is not positive definite.
+template <class MF>
+__device__ inline bool kst_unit_factor(const double *z, const KstModelParams &mp, double sw, double *Lw)
+{
+    const int m = mp.m;
+    double U[KST_MAX_UNIT * KST_MAX_UNIT];
+    MF::vcov(z, mp, U);
+    bool ok = true;
+    for (int j = 0; j < m; j++) {
+        double ajj = U[j + j * m];
+        for (int k = 0; k < j; k++) ajj -= U[k + j * m] * U[k + j * m];
+        ok = ok && (ajj > 0.0);
+        ajj = sqrt(ajj);
+        U[j + j * m] = ajj;
+        for (int i = j + 1; i < m; i++) {
+            double v = U[j + i * m];
+            for (int k = 0; k < j; k++) v -= U[k + j * m] * U[k + i * m];
+            U[j + i * m] = v / ajj;
+        }
+    }
+    // column c of L = U^-T by forward substitution with U' (lower): L[i][c] = (delta_ic - sum_{l=c}^{i-1} U[l][i] L[l][c]) / U[i][i]
+    for (int c = 0; c < m; c++)
+        for (int i = c; i < m; i++) {
+            double v = i == c ? 1.0 : 0.0;
+            for (int l = c; l < i; l++) v -= U[l + i * m] * Lw[l * (l + 1) / 2 + c];
+            Lw[i * (i + 1) / 2 + c] = v / U[i + i * m];
+        }
+    for (int i = 0; i < m * (m + 1) / 2; i++) Lw[i] *= sw;
+    return ok;
+}
 
 // One thread per particle of the tile: map design points to rows (map_to_covariate! +
 // update_model_vcov!, src/design-common.jl:51-61, src/model-nonlinear-regression.jl:39-49),
@@ -73,7 +115,31 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
         double *rows = KstTile<MF>::rows(smem) + (size_t)threadIdx.x * rows_max * RW;
         int na = 0, ntriv = 0;
         double sw = 0.0, bound = 0.0;
-        if (p < S) {
+        bool dense_ok = true;
+        if (KstDense<MF>::value && p < S) {
+            // dense unit covariance: whole units are kept or (at weight zero) dropped; every row record carries
+            // weight 1, the unit's factor sqrt(w_k) U_k^-T goes to the L area
+            double *lm = KstTile<MF>::lmat(smem, rows_max) + (size_t)threadIdx.x * rows_max * KstTile<MF>::LW;
+            const int m = mp.m;
+            for (int k = 0; k < K; k++) {
+                const double *z = pts + ((size_t)(p - pidx0) * K + k) * mp.d;
+                const double wk = w[(size_t)(p - pidx0) * K + k];
+                sw += wk;
+                if (wk == 0.0) continue;
+                if constexpr (KstDense<MF>::value)
+                    dense_ok = kst_unit_factor<MF>(z, mp, sqrt(wk), lm + (size_t)(na / m) * (m * (m + 1) / 2)) && dense_ok;
+                for (int i = 0; i < m; i++) {
+                    double pc[MF::NPC], varfac;
+                    MF::prep_row(z, i, mp, pc, varfac);
+                    if (MF::FAST_EXP && dcmax) bound = fmax(bound, MF::arg_bound(pc, dcmax));
+                    MF::post_row(pc, 1.0);
+                    rows[na * RW] = 1.0;
+#pragma unroll
+                    for (int c = 0; c < MF::NPC; c++) rows[na * RW + 1 + c] = pc[c];
+                    na++;
+                }
+            }
+        } else if (p < S) {
             for (int k = 0; k < K; k++) {
                 const double *z = pts + ((size_t)(p - pidx0) * K + k) * mp.d;
                 const double wk = w[(size_t)(p - pidx0) * K + k];
@@ -101,6 +167,23 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
         // the hoisted first pivot must be a positive, finite number; otherwise the design is singular
         // (or its weights are NaN) and every draw takes the rank-deficient path
         if (MF::CONST_COL >= 0 && !(sw > 0.0 && sw < KST_INF)) rank = 0;
+        if (KstDense<MF>::value && !dense_ok) rank = 0;  // a unit covariance that is not positive definite
+        if (na == 0 && KstDense<MF>::value) {
+            // no unit left: one weightless unit (L = 0) keeps the loop shape
+            double *lm = KstTile<MF>::lmat(smem, rows_max) + (size_t)threadIdx.x * rows_max * KstTile<MF>::LW;
+            for (int i = 0; i < mp.m * (mp.m + 1) / 2; i++) lm[i] = 0.0;
+            const double one = 1.0;
+            for (int i = 0; i < mp.m; i++) {
+                double pc[MF::NPC], vf;
+                MF::prep_row(&one, i, mp, pc, vf);
+                MF::post_row(pc, 1.0);
+                rows[i * RW] = 1.0;
+#pragma unroll
+                for (int c = 0; c < MF::NPC; c++) rows[i * RW + 1 + c] = pc[c];
+            }
+            na = mp.m;
+            rank = 0;
+        }
         if (na == 0) {
             // the evaluation loop always runs the first row: give it a weightless, harmless one
             double pc[MF::NPC], vf;
@@ -151,13 +234,43 @@ __device__ __forceinline__ void kst_rows(double *M, unsigned addr, const double 
 // Remainders first (1, 2, 4 rows by the bits of na), then groups of MF::ROWS rows: the FP64 pipe only
 // saturates with about four independent dependency chains per warp (tools/fp64_probe.cu), which the
 // interleaved rows provide; there is no remainder code after the loop.
+// Dense unit covariance (KstDense): `na` rows in units of m; per unit the m Jacobian rows are evaluated, whitened with
+// the unit's packed factor Lw (shared-space address laddr, m (m + 1) / 2 doubles per unit) and accumulated:
+// Mt += (Lw G)'(Lw G) -- average_fishermatrix!'s trsm! + syrk! (src/model-nonlinear-regression.jl:79-83).
 template <class MF, bool CLAMP = true>
 __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na, double sw, const double *dcv,
-                                           KstTab tab)
+                                           KstTab tab, unsigned laddr = 0, int m = 1)
 {
     constexpr int R = MF::R, RW = KstTile<MF>::RW, UN = KST_ROWS_OVERRIDE > 0 ? KST_ROWS_OVERRIDE : MF::ROWS;
 #pragma unroll
     for (int i = 0; i < KstPacked<R>::N; i++) M[i] = 0.0;
+    if constexpr (KstDense<MF>::value) {
+        unsigned ra = rows_addr, la = laddr;
+        for (int u = 0; u < na; u += m) {
+            double x[KST_MAX_UNIT][R];
+            for (int i = 0; i < m; i++) kst_row_at<MF, CLAMP>(ra + (unsigned)(i * RW * 8), dcv, x[i], tab);
+            // last row first: rows l < i are still the raw Jacobian rows when row i needs them
+            for (int i = m - 1; i >= 0; i--) {
+                const unsigned li = la + (unsigned)(i * (i + 1) / 2 * 8);
+                double l;
+                asm("ld.shared.f64 %0, [%1];" : "=d"(l) : "r"(li + (unsigned)(i * 8)));
+                double acc[R];
+#pragma unroll
+                for (int c = 0; c < R; c++) acc[c] = l * x[i][c];
+                for (int k = 0; k < i; k++) {
+                    asm("ld.shared.f64 %0, [%1];" : "=d"(l) : "r"(li + (unsigned)(k * 8)));
+#pragma unroll
+                    for (int c = 0; c < R; c++) acc[c] = fma(l, x[k][c], acc[c]);
+                }
+#pragma unroll
+                for (int c = 0; c < R; c++) x[i][c] = acc[c];
+            }
+            for (int i = 0; i < m; i++) kst_accum<R, -1>(M, x[i]);
+            ra += (unsigned)(m * RW * 8);
+            la += (unsigned)(m * (m + 1) / 2 * 8);
+        }
+        return;
+    }
     unsigned addr = rows_addr;
     int left = na;
     if (UN > 1 && (left & 1)) { kst_rows<MF, 1, CLAMP>(M, addr, dcv, tab); addr += RW * 8; left -= 1; }
@@ -214,6 +327,10 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
 #pragma unroll 1
     for (int p = 0; p < np; p++) {
         const unsigned rows_addr = rows_base + (unsigned)(p * rows_max * KstTile<MF>::RW * 8);
+        const unsigned laddr = KstDense<MF>::value
+                                   ? (unsigned)__cvta_generic_to_shared(KstTile<MF>::lmat(smem, rows_max)) +
+                                         (unsigned)(p * rows_max * KstTile<MF>::LW * 8)
+                                   : 0u;
         const int na = KstTile<MF>::nact(smem, rows_max)[p];
         const double sw = KstTile<MF>::sumw(smem, rows_max)[p];
         // 1 / first pivot, hoisted per particle when the first pivot is the constant-column entry
@@ -252,7 +369,7 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
                     pwn = __ldg(pw + jn);
                 }
                 double M[KstPacked<R>::N];
-                kst_fisher<MF, CL>(M, rows_addr, na, sw, dcv, tab);
+                kst_fisher<MF, CL>(M, rows_addr, na, sw, dcv, tab, laddr, prm.mp.m);
                 if (REG) {
 #pragma unroll
                     for (int i = 0; i < KstPacked<R>::N; i++) M[i] += __ldg(prm.reg + ((size_t)i * ld + (size_t)j));
@@ -374,5 +491,6 @@ int kst_obj_launch(kst_problem *h, const KstObjParams &prm, dim3 grid, int K)
                                    : launch_obj_t<MF, 2>(h, prm, grid, smem);
 }
 #define KST_OBJ_FAMILIES(X) \
-    X(KstEmax) X(KstSigEmax) X(KstTpc) X(KstVu) X(KstDtr) X(KstLinLogReg<1>) X(KstLinLogReg<2>) X(KstLinLogReg<3>) X(KstSinLogReg)
+    X(KstEmax) X(KstSigEmax) X(KstTpc) X(KstVu) X(KstDtr) X(KstLinLogReg<1>) X(KstLinLogReg<2>) X(KstLinLogReg<3>) X(KstSinLogReg) \
+    X(KstVuAr)
 

@@ -251,7 +251,10 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_pso_fused(const KstFusedPa
             for (int e = tid; e < np * KD; e += KST_NT) xp[e] = sx_p[e];
         }
         // pso_evaluate_objective!: this CTA's draw slice for its tile
-        kst_build_tile_par<MF>(smem, sx_p, sx_w, np, K, prm.mp, tp, prm.dcmax, s_om, s_bd);  // ends with __syncthreads()
+        if constexpr (KstDense<MF>::value)  // unit factors: one thread per particle, like everywhere else
+            kst_build_tile<MF>(smem, sx_p, sx_w, p0, S, K, prm.mp, tp, prm.dcmax, p0);
+        else
+            kst_build_tile_par<MF>(smem, sx_p, sx_w, np, K, prm.mp, tp, prm.dcmax, s_om, s_bd);  // ends with __syncthreads()
         double *pt = fp.partials2 + (size_t)par * S * nbx;
         kst_objective_cta<MF, CRIT, T, UNI, false>(prm, smem, tab, p0, bx, nbx, pt);
         kst_grid_barrier(fp.bar, fp.bar_base + (unsigned long long)(step + 1) * (unsigned long long)(nbx * gridDim.y));

@@ -96,6 +96,20 @@ class VUMod(Model):
         return [self.sigma_squared]
 
 
+class VUModAR1(Model):
+    """VUMod (test/example-vector.jl:9-12) with AR(1)-correlated errors within a unit:
+    Sigma_ij = sigma_squared rho^|i-j| sqrt((1 + t_i)(1 + t_j)).  The registered example of a NonlinearRegression whose
+    update_model_vcov! fills a dense matrix (the reference factors any Sigma(c) with potrf! and whitens with trsm!,
+    src/model-nonlinear-regression.jl:39-49,79-83); rho = 0 is VUMod."""
+    model_id, parameter_type = _ffi.MODEL_VUAR, VUParameter
+
+    def __init__(self, sigma_squared, rho, m):
+        self.sigma_squared, self.rho, self.m = float(sigma_squared), float(rho), int(m)
+
+    def _params(self):
+        return [self.sigma_squared, self.rho]
+
+
 class DTRMod(Model):
     """test/example-dtr.jl:4-7, docs/src/dtr.md:87-90: dose-time-response, m measurements per unit."""
     model_id, parameter_type = _ffi.MODEL_DTR, DTRParameter

@@ -8,7 +8,7 @@ import numpy as np
 from . import _ffi
 from .designmeasure import (DesignMeasure, numpoints, one_point_design, simplify_drop, simplify_merge)
 from .models import (DTRMod, EmaxModel, EquidistantTimes, FixedDose, FixedTimes, LinLogReg, LogEquidistantTimes, Model,
-                     SigEmaxModel, SinLogReg, TPCModel, VUMod)
+                     SigEmaxModel, SinLogReg, TPCModel, VUMod, VUModAR1)
 
 # ------------------------------------------------------------------------------------------------
 # criteria, transformations, normal approximation, prior knowledge
@@ -256,7 +256,7 @@ def implied_covariates(d, m, cp):
             out.append({"dose": float(z[0])})
         elif isinstance(m, TPCModel):
             out.append({"time": float(z[0])})
-        elif isinstance(m, VUMod):
+        elif isinstance(m, (VUMod, VUModAR1)):
             out.append({"time": [float(j * z[0]) for j in range(m.m)]})
         elif isinstance(m, DTRMod):
             if isinstance(cp, FixedDose):

@@ -13,7 +13,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "libkirstine_oracle.so")
 
-EMAX, SIGEMAX, TPC, VU, DTR, LINLOGREG, SINLOGREG = 1, 2, 3, 4, 5, 6, 7
+EMAX, SIGEMAX, TPC, VU, DTR, LINLOGREG, SINLOGREG, VUAR = 1, 2, 3, 4, 5, 6, 7, 8
 CP_COPY, CP_EQUITIME = 0, 1
 CP_DTR_COPYBOTH, CP_DTR_FIXEDDOSE, CP_DTR_FIXEDTIMES, CP_DTR_EQUIDISTANT, CP_DTR_LOGEQUIDISTANT = 2, 3, 4, 5, 6
 CRIT_D, CRIT_A, CRIT_DEXP = 0, 1, 2

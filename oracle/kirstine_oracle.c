@@ -34,7 +34,8 @@
 #define KO_MAXC (KO_MAXM + 2)
 #define KO_MAXD 4
 
-enum { KO_EMAX = 1, KO_SIGEMAX = 2, KO_TPC = 3, KO_VU = 4, KO_DTR = 5, KO_LINLOGREG = 6, KO_SINLOGREG = 7 };
+enum { KO_EMAX = 1, KO_SIGEMAX = 2, KO_TPC = 3, KO_VU = 4, KO_DTR = 5, KO_LINLOGREG = 6, KO_SINLOGREG = 7,
+       KO_VUAR = 8 /* VUMod with AR(1)-correlated errors within a unit: a dense Sigma(c), mp = {sigma_squared, rho} */ };
 enum { KO_CP_COPY = 0, KO_CP_EQUITIME = 1, KO_CP_DTR_COPYBOTH = 2, KO_CP_DTR_FIXEDDOSE = 3,
        KO_CP_DTR_FIXEDTIMES = 4, KO_CP_DTR_EQUIDISTANT = 5, KO_CP_DTR_LOGEQUIDISTANT = 6 };
 enum { KO_CRIT_D = 0, KO_CRIT_A = 1, KO_CRIT_DEXP = 2 };
@@ -68,6 +69,7 @@ static void ko_covariate(const ko_problem *p, const double *z, double *c)
 {
     switch (p->model_id) {
     case KO_VU:
+    case KO_VUAR:
         for (int j = 0; j < p->m; j++) c[j] = (double)j * z[0];
         break;
     case KO_DTR: /* docs/src/dtr.md: CopyBoth :197-203, FixedDose :331-339, FixedTimes :401-409,
@@ -122,6 +124,13 @@ static void ko_vcov(const ko_problem *p, const double *c, double *S)
         break;
     case KO_DTR:
         for (int j = 0; j < m; j++) S[IDX(j, j, m)] = p->mp[0] * p->mp[0];
+        break;
+    case KO_VUAR: /* not a reference model: VUMod's variances with AR(1) correlation, to exercise the general
+                   * potrf! + trsm! path of src/model-nonlinear-regression.jl:39-49,79-83 */
+        for (int j = 0; j < m; j++)
+            for (int i = 0; i < m; i++)
+                S[IDX(i, j, m)] = p->mp[0] * pow(p->mp[1], (double)(i > j ? i - j : j - i)) *
+                                  sqrt((1.0 + c[i]) * (1.0 + c[j]));
         break;
     default: S[0] = 1.0; /* logistic regression has no unit covariance */
     }
@@ -190,7 +199,8 @@ void ko_jacobian(const ko_problem *p, const double *c, const double *th, double 
         break;
     }
     case KO_TPC:
-    case KO_VU: {
+    case KO_VU:
+    case KO_VUAR: {
         double a = th[0], e = th[1], s = th[2];
         for (int j = 0; j < m; j++) {
             double t = c[j];

@@ -74,6 +74,22 @@ def rows(model, mp, z, theta, m=1, cov=None):
             var = LD(mp[0]) ** 2 if model == 3 else LD(mp[0]) * (1 + t)
             out.append(g / np.sqrt(var))
         return np.stack(out, axis=1)
+    if model == 8:  # VUMod with AR(1) errors, mp = (sigma_squared, rho): rows whitened with the dense unit covariance
+        a, e, s = th.T
+        t = np.array([LD(i) * z for i in range(m)], dtype=LD)
+        J = np.stack([np.stack([np.exp(-a * ti) * s * ti, -np.exp(-e * ti) * s * ti, np.exp(-e * ti) - np.exp(-a * ti)],
+                               axis=1) for ti in t], axis=1)                       # (N, m, 3)
+        S = np.array([[LD(mp[0]) * LD(mp[1]) ** abs(i - j) * np.sqrt((1 + t[i]) * (1 + t[j])) for j in range(m)]
+                      for i in range(m)], dtype=LD)
+        U = np.zeros((m, m), dtype=LD)                                             # S = U'U
+        for j in range(m):
+            U[j, j] = np.sqrt(S[j, j] - np.sum(U[:j, j] ** 2))
+            for i in range(j + 1, m):
+                U[j, i] = (S[j, i] - np.sum(U[:j, j] * U[:j, i])) / U[j, j]
+        X = np.zeros_like(J)                                                       # U' X = J
+        for i in range(m):
+            X[:, i, :] = (J[:, i, :] - np.einsum("l,nlr->nr", U[:i, i], X[:, :i, :])) / U[i, i]
+        return X
     raise KeyError(model)
 
 
