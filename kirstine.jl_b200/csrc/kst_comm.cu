@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(1024) k_peer_allreduce(double *buf, int count,
         double v;
         if (partials) {
             double s = 0.0;
-            for (int b = 0; b < n_blk; b++) s += partials[(size_t)i * n_blk + b];
+            for (int b = 0; b < n_blk; b++) s += partials[(size_t)b * count + i];
             v = s + offset;
         } else {
             v = buf[i];

@@ -111,7 +111,7 @@ struct kst_problem {
     int uniform_w = 0;         // all prior weights of this handle are the same positive finite number ...
     double w_uniform = 0.0;    // ... namely this one
 
-    // scratch for the objective kernel: partial sums [S][n_blk]
+    // scratch for the objective kernel: partial sums [n_blk][S]
     double *partials = nullptr;
     size_t partials_cap = 0;
     // staging for the host-buffer entry points
@@ -149,7 +149,7 @@ struct kst_problem {
 
 // kst_objective.cu
 int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const double *d_dt);
-// defer_n_blk != nullptr: the per-CTA partial sums stay in h->partials ([S][*defer_n_blk]) and the caller finishes them
+// defer_n_blk != nullptr: the per-CTA partial sums stay in h->partials ([*defer_n_blk][S]) and the caller finishes them
 // (kst_api.cu fuses that step into the peer-memory all-reduce)
 // gd = 1: the Gateaux derivative of the prepared design in the swarm's one-point directions (K = 1) instead of the
 // objective: same kernel body, the draw's "criterion" is tr_U[A_j M(delta, theta_j)]

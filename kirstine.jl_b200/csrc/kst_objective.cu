@@ -9,7 +9,7 @@
 // along draws (coalesced SoA loads of the per-draw constants); all lanes of a warp share the
 // particle, so its compacted row list is read from shared memory as a broadcast.  The r x r
 // matrix, its LDL' factor and everything after live in FP64 registers.  Per particle one
-// fixed-order block reduction; per-CTA partial sums go to scratch [S][n_blk] and are summed in
+// fixed-order block reduction; per-CTA partial sums go to scratch [n_blk][S] and are summed in
 // fixed order by k_obj_finish, so results are bit-reproducible run to run.
 #include <stdlib.h>
 #include <string.h>
@@ -81,7 +81,7 @@ __global__ void k_obj_finish(const double *__restrict__ partials, int n_blk, dou
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= S) return;
     double s = 0.0;
-    for (int b = 0; b < n_blk; b++) s += partials[(size_t)p * n_blk + b];
+    for (int b = 0; b < n_blk; b++) s += partials[(size_t)b * S + p];
     fx[p] = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : s + offset;
 }
 

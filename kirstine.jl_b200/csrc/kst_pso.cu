@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(1024) k_pso_best(KstPsoDev s, int init, double
         double f;
         if (partials) {
             double acc = 0.0;
-            for (int b = 0; b < n_blk; b++) acc += partials[(size_t)i * n_blk + b];
+            for (int b = 0; b < n_blk; b++) acc += partials[(size_t)b * s.S + i];
             f = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : acc + offset;
             s.fx[i] = f;
         } else {

@@ -31,7 +31,7 @@ struct KstFusedParams {
     KstObjParams obj;             // pts / w / partials unused: the tile comes from shared memory
     KstPsoDev pso;                // canonical swarm state: read at the start, written at the end
     double *x2_pts, *x2_w;        // published positions, [2][S][K*d] and [2][S][K]
-    double *partials2;            // [2][S][n_blk]
+    double *partials2;            // [2][n_blk][S]
     unsigned long long *bar;      // grid barrier counter (monotonic over launches)
     unsigned long long bar_base;  // its value when this launch starts
     int n_steps;                  // swarm evaluations in this launch
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_pso_fused(const KstFusedPa
         bool notnan = false;
         for (int i = tid; i < S; i += KST_NT) {
             double acc = 0.0;
-            for (int b = 0; b < nbx; b++) acc += __ldcg(pt + (size_t)i * nbx + b);
+            for (int b = 0; b < nbx; b++) acc += __ldcg(pt + (size_t)b * S + i);
             const double f = fp.nan_fill ? NaN : acc + fp.offset;
             if (leader && (last || (is_init && fp.snap))) ps.fx[i] = f;
             notnan = notnan || (f == f);
