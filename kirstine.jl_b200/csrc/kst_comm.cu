@@ -3,11 +3,13 @@
 // evaluation.  Entry points declared in include/kirstine_b200.h: kst_comm_*.
 #include <dlfcn.h>
 #include <stddef.h>
+#include <math.h>
 #include <string.h>
 
 #include <mutex>
 
 #include "kst_common.cuh"
+#include "kst_pso_dev.cuh"
 
 // ---------------------------------------------------------------------------------------
 // NCCL through dlopen: no link-time dependency, single-GPU users never load it
@@ -133,9 +135,10 @@ __device__ __forceinline__ double kst_ld_peer(const double *p)
 // partials != nullptr fuses the last step of the objective evaluation into the collective: entry i of this rank's
 // vector is the fixed-order sum of partials[i][0..n_blk) plus `offset` (exactly what k_obj_finish computes), so a
 // swarm evaluation on several GPUs is k_objective + this one kernel.
-__global__ void __launch_bounds__(1024) k_peer_allreduce(double *buf, int count, KstPeerPtrs peers, int nranks, int rank,
-                                                         unsigned long long seq, const double *__restrict__ partials,
-                                                         int n_blk, double offset)
+__device__ __forceinline__ void kst_peer_allreduce_cta(double *buf, int count, const KstPeerPtrs &peers, int nranks,
+                                                       int rank, unsigned long long seq,
+                                                       const double *__restrict__ partials, int n_blk, double offset,
+                                                       int nan_fill)
 {
     __shared__ int s_fail;
     const int par = (int)(seq & 1ull);
@@ -145,7 +148,7 @@ __global__ void __launch_bounds__(1024) k_peer_allreduce(double *buf, int count,
         if (partials) {
             double s = 0.0;
             for (int b = 0; b < n_blk; b++) s += partials[(size_t)b * count + i];
-            v = s + offset;
+            v = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : s + offset;
         } else {
             v = buf[i];
         }
@@ -173,6 +176,7 @@ __global__ void __launch_bounds__(1024) k_peer_allreduce(double *buf, int count,
     if (s_fail) {
         if (threadIdx.x == 0) mine->error = 1;
         for (int i = threadIdx.x; i < count; i += blockDim.x) buf[i] = __longlong_as_double(0x7ff8000000000000LL);
+        __syncthreads();
         return;
     }
     for (int i = threadIdx.x; i < count; i += blockDim.x) {
@@ -186,6 +190,66 @@ __global__ void __launch_bounds__(1024) k_peer_allreduce(double *buf, int count,
             if (r < nranks) s += v[r];
         buf[i] = s;
     }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(1024) k_peer_allreduce(double *buf, int count, KstPeerPtrs peers, int nranks, int rank,
+                                                         unsigned long long seq, const double *__restrict__ partials,
+                                                         int n_blk, double offset)
+{
+    kst_peer_allreduce_cta(buf, count, peers, nranks, rank, seq, partials, n_blk, offset, 0);
+}
+
+// The tail of a swarm iteration in ONE single-CTA launch (after the evaluation kernel):
+//   1. fx = fixed-order sum of the evaluation's per-CTA partial sums (+ offset), summed over the ranks through the
+//      peer-memory exchange when there are several (kst_peer_allreduce_cta);
+//   2. pso_update_best! (kst_pso_best_cta);
+//   3. the NEXT iteration's tick! (src/pso.jl:127-141: velocity + constrained move) into the next-position buffers
+//      xn / vn, which the host swaps in when that iteration starts.  x and v themselves stay what the last
+//      evaluation saw, so kst_pso_get_state reads a consistent state at any time.
+// With the move riding along here, an iteration of a swarm too large for the persistent kernel is two launches
+// (evaluation + this) on one GPU and on several, instead of three and four.
+__global__ void __launch_bounds__(1024) k_pso_tail(KstPsoDev s, KstPeerPtrs peers, int nranks, int rank,
+                                                   unsigned long long seq, const double *__restrict__ partials, int n_blk,
+                                                   double offset, int nan_fill, double *tr_fx, double *tr_pts, double *tr_w,
+                                                   int slot, double *xn_pts, double *xn_w, double *vn_pts, double *vn_w,
+                                                   uint32_t next_iter, double c1, double c2, double chi)
+{
+    if (nranks > 1) {
+        kst_peer_allreduce_cta(s.fx, s.S, peers, nranks, rank, seq, partials, n_blk, offset, nan_fill);
+        kst_pso_best_cta(s, 0, tr_fx, tr_pts, tr_w, slot, nullptr, nullptr, 0, 0.0, 0);
+    } else {
+        kst_pso_best_cta(s, 0, tr_fx, tr_pts, tr_w, slot, nullptr, partials, n_blk, offset, nan_fill);
+    }
+    const int K = s.K, d = s.d;
+    for (int i = threadIdx.x; i < s.S; i += blockDim.x) {
+        double *xp = xn_pts + (size_t)i * K * d, *xw = xn_w + (size_t)i * K;
+        double *vp = vn_pts + (size_t)i * K * d, *vw = vn_w + (size_t)i * K;
+        for (int c = 0; c < K * d; c++) { xp[c] = s.x_pts[(size_t)i * K * d + c]; vp[c] = s.v_pts[(size_t)i * K * d + c]; }
+        for (int k = 0; k < K; k++) { xw[k] = s.x_w[(size_t)i * K + k]; vw[k] = s.v_w[(size_t)i * K + k]; }
+        kst_pso_move_particle(K, d, xw, xp, s.p_w + (size_t)i * K, s.p_pts + (size_t)i * K * d, vw, vp, s.g_w, s.g_pts,
+                              s.fixw, s.fixp, s.lb, s.ub, c1, c2, chi, KstRndPhilox{s.seed, next_iter, (uint32_t)i});
+    }
+}
+
+int kst_launch_pso_tail(kst_problem *h, int trace_slot, int n_blk, double offset, int nan_fill)
+{
+    KstPso &p = h->pso;
+    if (h->nranks > 1 && !(h->peer_ready && p.S <= KST_PEER_CAP)) return 1;
+    KstPsoDev s;
+    kst_pso_make_dev(h, &s);
+    KstPeerPtrs pp;
+    for (int r = 0; r < KST_PEER_MAX; r++) pp.blk[r] = (KstPeerBlock *)h->peer_map[r];
+    const double phi = p.c1 + p.c2;
+    const double chi = 2 / fabs(2 - phi - sqrt(phi * phi - 4 * phi));  // src/pso.jl:134-135
+    const unsigned long long seq = h->nranks > 1 ? ++h->peer_seq : 0;
+    k_pso_tail<<<1, 1024, 0, h->stream>>>(s, pp, h->nranks, h->rank, seq, h->partials, n_blk, offset, nan_fill,
+                                           trace_slot >= 0 ? p.tr_fx : nullptr, trace_slot >= 0 ? p.tr_pts : nullptr,
+                                           trace_slot >= 0 ? p.tr_w : nullptr, trace_slot >= 0 ? trace_slot : 0, p.xn_pts,
+                                           p.xn_w, p.vn_pts, p.vn_w, (uint32_t)(p.iter + 1), p.c1, p.c2, chi);
+    KST_CUDA(cudaGetLastError());
+    p.next_ready = 1;
+    return KST_OK;
 }
 
 int kst_allreduce_sum(kst_problem *h, double *d_buf, size_t count)

@@ -2,10 +2,6 @@
 // Included by kst_objective.cu (host entry points, small kernels) and by the kst_obj_inst_*.cu files, each of
 // which instantiates kst_obj_launch for some model families so that the families compile in parallel.
 #pragma once
-#ifndef KST_WARP_BALANCE
-#define KST_WARP_BALANCE 1   // 1: a CTA's (particle, 32-draw group) units are dealt to its warps round robin across the
-                             // particles of the tile; 0: every particle's draws are split over all warps on their own
-#endif
 #ifndef KST_ROWS_OVERRIDE
 #define KST_ROWS_OVERRIDE 0  // tuning: force the row interleave factor (1, 2, 4, 8) for every family
 #endif
@@ -319,22 +315,7 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
     double *wsum = KstTile<MF>::wsum(smem, rows_max);
     // 32-bit draw indices (the launcher guarantees N + stride < 2^31) and 32-bit shared-space addresses:
     // the loop bookkeeping is a handful of integer instructions
-#if KST_WARP_BALANCE
-    // Work split.  The draws of this GPU form groups of 32 consecutive draws (one per lane); CTA bx owns the groups
-    // bx, bx + nbx, ...; its (particle, group) units are dealt to its warps round robin ACROSS the particles of the
-    // tile: a warp that finishes particle p at group index gi carries the remainder gi - gcnt into particle p + 1.
-    // Every warp thus gets the same number of units to within one, whatever the draw count (with the draws of each
-    // particle split over all warps on their own, 125 000 draws on 37 x 256 threads meant 13.2 -> 14 rounds for
-    // every particle: 6 % of the launch idle).
-    constexpr int NW = KST_NT / 32;
-    const int n = (int)prm.N;
-    const int ngroups = (n + 31) >> 5;
-    const int gcnt = bx < ngroups ? (ngroups - bx + nbx - 1) / nbx : 0;   // groups owned by this CTA
-    const int j0 = (bx << 5) + lane, gstride = nbx << 5, stride = gstride * NW;
-    int gi = warp;  // the warp's next group (index among the CTA's groups) in the current particle
-#else
     const int n = (int)prm.N, stride = nbx * KST_NT, j0 = bx * KST_NT + (int)threadIdx.x;
-#endif
     unsigned rows_base = (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem));
     // make both shared-space bases opaque: otherwise the compiler rebuilds them from SR_CgaCtaId (a
     // variable-latency S2R/S2UR + LEA) in front of every use instead of keeping them in a register
@@ -357,40 +338,32 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
         constexpr bool DUAL = MF::FAST_EXP && UNI;  // the unclamped copy of the draw loop only where it pays
         const double inv0 = KstTile<MF>::isumw(smem, rows_max)[p];
         double acc = 0.0;
-#if KST_WARP_BALANCE
-        // this warp's draws of particle p: jb, jb + stride, ... < je (je can lie beyond n in the CTA's last group)
-        const int trips = gi < gcnt ? (gcnt - gi + NW - 1) / NW : 0;
-        const int jb = j0 + gi * gstride, je = jb + trips * stride;
-        gi += trips * NW - gcnt;
-#else
-        const int jb = j0, je = n;
-#endif
         if (!REG && CRIT != KST_KCRIT_GD && KstTile<MF>::rank(smem, rows_max)[p] < R) {
             // fewer live rows than parameters: singular by construction (one-point designs etc.).  The
             // reference reaches the same -Inf through an exactly zero pivot: weighted by the prior weight
             // for log_det! (0 * -Inf = NaN, as there), unweighted where it throws.
             // (Dexp: exp(-Inf / t) = 0 for such a draw.)
-            for (int j = jb; j < je; j += stride)
-                if (j < n) acc += T != 0 ? -KST_INF : (CRIT == 0 ? pw[j] * -KST_INF : (CRIT == 2 ? pw[j] * 0.0 : -KST_INF));
+            for (int j = j0; j < n; j += stride)
+                acc += T != 0 ? -KST_INF : (CRIT == 0 ? pw[j] * -KST_INF : (CRIT == 2 ? pw[j] * 0.0 : -KST_INF));
         } else {
             double run = 1.0;  // UNI: running product of determinants
             // software prefetch: the next draw's constants are requested before this draw's rows are evaluated
             double dcn[MF::NDC], pwn = 0.0;
-            if (jb < je) {  // (a group's lanes beyond n read the padding of the arrays: ld is a multiple of 32)
+            if (j0 < n) {
 #pragma unroll
-                for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jb));
-                pwn = __ldg(pw + jb);
+                for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)j0));
+                pwn = __ldg(pw + j0);
             }
             // the draw loop, compiled twice for the kernels worth it: with and without the exponent clamp inside exp
             auto draws = [&](auto clamp_tag) {
             constexpr bool CL = decltype(clamp_tag)::value;
-            for (int j = jb; j < je; j += stride) {
+            for (int j = j0; j < n; j += stride) {
                 double dcv[MF::NDC];
 #pragma unroll
                 for (int c = 0; c < MF::NDC; c++) dcv[c] = dcn[c];
                 const double pwj = pwn;
                 const int jn = j + stride;
-                if (jn < je) {
+                if (jn < n) {
 #pragma unroll
                     for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
                     pwn = __ldg(pw + jn);
@@ -401,9 +374,6 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
 #pragma unroll
                     for (int i = 0; i < KstPacked<R>::N; i++) M[i] += __ldg(prm.reg + ((size_t)i * ld + (size_t)j));
                 }
-#if KST_WARP_BALANCE
-                if (j >= n) continue;  // only in the last group of the sample: lanes past the end do not count
-#endif
                 if (CRIT == KST_KCRIT_GD) {
                     double q = 0.0;
 #pragma unroll

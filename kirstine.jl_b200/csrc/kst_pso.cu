@@ -83,88 +83,12 @@ __global__ void k_pso_move(KstPsoDev s, uint32_t iter, double c1, double c2, dou
                           s.fixw, s.fixp, s.lb, s.ub, c1, c2, chi, KstRndPhilox{s.seed, iter, (uint32_t)i});
 }
 
-// pso_update_best!: strict '>', sequential semantics => the lowest index attaining the maximum
-// among improved particles becomes the global best iff it beats fg; NaN never wins.
-// status (init only): 1 = fg == +Inf, 2 = all fx NaN.
-// partials != nullptr: the evaluation kernel's per-CTA partial sums are still unfinished; fx[i] is their fixed-order
-// sum plus `offset` (what k_obj_finish would have written), computed here to save a launch per iteration.
+// pso_update_best! as a kernel of its own (kst_pso_best_cta, kst_pso_dev.cuh)
 __global__ void __launch_bounds__(1024) k_pso_best(KstPsoDev s, int init, double *tr_fx, double *tr_pts, double *tr_w,
                                                    int slot, int *status, const double *__restrict__ partials,
                                                    int n_blk, double offset, int nan_fill)
 {
-    __shared__ double s_val[1024];
-    __shared__ int s_idx[1024];
-    __shared__ int s_notnan;
-    const int K = s.K, d = s.d, tid = threadIdx.x;
-    if (tid == 0) s_notnan = 0;
-    __syncthreads();
-    double best = -KST_DINF;
-    int bidx = -1;
-    bool have = false;
-    bool notnan = false;
-    for (int i = tid; i < s.S; i += blockDim.x) {
-        double f;
-        if (partials) {
-            double acc = 0.0;
-            for (int b = 0; b < n_blk; b++) acc += partials[(size_t)b * s.S + i];
-            f = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : acc + offset;
-            s.fx[i] = f;
-        } else {
-            f = s.fx[i];
-        }
-        const double fpi = init ? (-KST_DINF) : s.fp[i];
-        notnan = notnan || (f == f);
-        if (f > fpi) {
-            const double *xp = s.x_pts + (size_t)i * K * d, *xw = s.x_w + (size_t)i * K;
-            double *pp = s.p_pts + (size_t)i * K * d, *pw = s.p_w + (size_t)i * K;
-            for (int c = 0; c < K * d; c++) pp[c] = xp[c];
-            for (int k = 0; k < K; k++) pw[k] = xw[k];
-            s.fp[i] = f;
-            if (!have || f > best) { best = f; bidx = i; have = true; }
-        } else if (init) {
-            s.fp[i] = fpi;
-        }
-    }
-    if (notnan) atomicOr(&s_notnan, 1);
-    s_val[tid] = best;
-    s_idx[tid] = have ? bidx : -1;
-    __syncthreads();
-    for (int o = blockDim.x / 2; o > 0; o >>= 1) {
-        if (tid < o) {
-            const int ia = s_idx[tid], ib = s_idx[tid + o];
-            const double va = s_val[tid], vb = s_val[tid + o];
-            const bool take_b = ib >= 0 && (ia < 0 || vb > va || (vb == va && ib < ia));
-            if (take_b) { s_val[tid] = vb; s_idx[tid] = ib; }
-        }
-        __syncthreads();
-    }
-    const int gi = s_idx[0];
-    const double gv = s_val[0];
-    __shared__ int s_update;
-    if (tid == 0) {
-        const double fg_old = init ? (-KST_DINF) : *s.fg;
-        s_update = (gi >= 0 && gv > fg_old) ? 1 : 0;
-        const double fg_new = s_update ? gv : fg_old;
-        *s.fg = fg_new;
-        if (tr_fx) tr_fx[slot] = fg_new;
-        if (status) {
-            int st = 0;
-            if (fg_new == KST_DINF) st = 1;
-            *status = st;
-        }
-    }
-    __syncthreads();
-    if (s_update) {
-        const double *xp = s.x_pts + (size_t)gi * K * d, *xw = s.x_w + (size_t)gi * K;
-        for (int c = tid; c < K * d; c += blockDim.x) s.g_pts[c] = xp[c];
-        for (int k = tid; k < K; k += blockDim.x) s.g_w[k] = xw[k];
-    }
-    __syncthreads();
-    if (tr_pts)
-        for (int c = tid; c < K * d; c += blockDim.x) tr_pts[(size_t)slot * K * d + c] = s.g_pts[c];
-    if (tr_w)
-        for (int k = tid; k < K; k += blockDim.x) tr_w[(size_t)slot * K + k] = s.g_w[k];
-    if (status && tid == 0 && *status == 0 && !s_notnan) *status = 2;
+    kst_pso_best_cta(s, init, tr_fx, tr_pts, tr_w, slot, status, partials, n_blk, offset, nan_fill);
 }
 
 void kst_pso_make_dev(const kst_problem *h, KstPsoDev *out)
@@ -201,8 +125,9 @@ int kst_pso_alloc(kst_problem *h, int S, int K)
 {
     KstPso &p = h->pso;
     const size_t np = (size_t)S * K * h->d, nw = (size_t)S * K, kd = (size_t)K * h->d;
-    // doubles: barrier words (2), x p v (3 np + 3 nw), published positions (2 np + 2 nw), g, fx, fp, fg, fixw / fixp
-    const size_t need = 2 + 5 * (np + nw) + kd + K + 2 * (size_t)S + 1 + (size_t)K + 2;
+    // doubles: barrier words (2), x p v (3 np + 3 nw), published positions (2 np + 2 nw), next x and v (2 np + 2 nw),
+    // g, fx, fp, fg, fixw / fixp
+    const size_t need = 2 + 7 * (np + nw) + kd + K + 2 * (size_t)S + 1 + (size_t)K + 2;
     if (need > p.arena_cap) {
         KST_CUDA(cudaStreamSynchronize(h->stream));
         if (p.arena) KST_CUDA(cudaFree(p.arena));
@@ -217,7 +142,10 @@ int kst_pso_alloc(kst_problem *h, int S, int K)
     double *q = p.arena;
     p.bar = (unsigned long long *)q; q += 2;
     p.x_pts = q; q += np; p.p_pts = q; q += np; p.v_pts = q; q += np; p.x2_pts = q; q += 2 * np;
+    p.xn_pts = q; q += np; p.vn_pts = q; q += np;
     p.x_w = q; q += nw; p.p_w = q; q += nw; p.v_w = q; q += nw; p.x2_w = q; q += 2 * nw;
+    p.xn_w = q; q += nw; p.vn_w = q; q += nw;
+    p.next_ready = 0;
     p.g_pts = q; q += kd; p.g_w = q; q += K;
     p.fx = q; q += S; p.fp = q; q += S; p.fg = q; q += 1;
     p.fixw = (int *)q; p.fixp = p.fixw + K;

@@ -165,3 +165,90 @@ __device__ __forceinline__ void kst_pso_position(const int K, const int d, doubl
         for (int k = 0; k < K; k++) vw[k] = 0.0;
     }
 }
+
+// pso_update_best!: strict '>', sequential semantics => the lowest index attaining the maximum
+// among improved particles becomes the global best iff it beats fg; NaN never wins.
+// status (init only): 1 = fg == +Inf, 2 = all fx NaN.
+// partials != nullptr: the evaluation kernel's per-CTA partial sums are still unfinished; fx[i] is their fixed-order
+// sum plus `offset` (what k_obj_finish would have written), computed here to save a launch per iteration.
+// One CTA of up to 1024 threads; ends with the CTA synchronised and g, fg, fp, p up to date.
+__device__ __forceinline__ void kst_pso_best_cta(const KstPsoDev &s, int init, double *tr_fx, double *tr_pts, double *tr_w,
+                                                 int slot, int *status, const double *__restrict__ partials,
+                                                 int n_blk, double offset, int nan_fill)
+{
+    __shared__ double s_val[1024];
+    __shared__ int s_idx[1024];
+    __shared__ int s_notnan;
+    const int K = s.K, d = s.d, tid = threadIdx.x;
+    if (tid == 0) s_notnan = 0;
+    __syncthreads();
+    double best = -KST_DINF;
+    int bidx = -1;
+    bool have = false;
+    bool notnan = false;
+    for (int i = tid; i < s.S; i += blockDim.x) {
+        double f;
+        if (partials) {
+            double acc = 0.0;
+            for (int b = 0; b < n_blk; b++) acc += partials[(size_t)b * s.S + i];
+            f = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : acc + offset;
+            s.fx[i] = f;
+        } else {
+            f = s.fx[i];
+        }
+        const double fpi = init ? (-KST_DINF) : s.fp[i];
+        notnan = notnan || (f == f);
+        if (f > fpi) {
+            const double *xp = s.x_pts + (size_t)i * K * d, *xw = s.x_w + (size_t)i * K;
+            double *pp = s.p_pts + (size_t)i * K * d, *pw = s.p_w + (size_t)i * K;
+            for (int c = 0; c < K * d; c++) pp[c] = xp[c];
+            for (int k = 0; k < K; k++) pw[k] = xw[k];
+            s.fp[i] = f;
+            if (!have || f > best) { best = f; bidx = i; have = true; }
+        } else if (init) {
+            s.fp[i] = fpi;
+        }
+    }
+    if (notnan) atomicOr(&s_notnan, 1);
+    s_val[tid] = best;
+    s_idx[tid] = have ? bidx : -1;
+    __syncthreads();
+    for (int o = blockDim.x / 2; o > 0; o >>= 1) {
+        if (tid < o) {
+            const int ia = s_idx[tid], ib = s_idx[tid + o];
+            const double va = s_val[tid], vb = s_val[tid + o];
+            const bool take_b = ib >= 0 && (ia < 0 || vb > va || (vb == va && ib < ia));
+            if (take_b) { s_val[tid] = vb; s_idx[tid] = ib; }
+        }
+        __syncthreads();
+    }
+    const int gi = s_idx[0];
+    const double gv = s_val[0];
+    __shared__ int s_update;
+    if (tid == 0) {
+        const double fg_old = init ? (-KST_DINF) : *s.fg;
+        s_update = (gi >= 0 && gv > fg_old) ? 1 : 0;
+        const double fg_new = s_update ? gv : fg_old;
+        *s.fg = fg_new;
+        if (tr_fx) tr_fx[slot] = fg_new;
+        if (status) {
+            int st = 0;
+            if (fg_new == KST_DINF) st = 1;
+            *status = st;
+        }
+    }
+    __syncthreads();
+    if (s_update) {
+        const double *xp = s.x_pts + (size_t)gi * K * d, *xw = s.x_w + (size_t)gi * K;
+        for (int c = tid; c < K * d; c += blockDim.x) s.g_pts[c] = xp[c];
+        for (int k = tid; k < K; k += blockDim.x) s.g_w[k] = xw[k];
+    }
+    __syncthreads();
+    if (tr_pts)
+        for (int c = tid; c < K * d; c += blockDim.x) tr_pts[(size_t)slot * K * d + c] = s.g_pts[c];
+    if (tr_w)
+        for (int k = tid; k < K; k += blockDim.x) tr_w[(size_t)slot * K + k] = s.g_w[k];
+    if (status && tid == 0 && *status == 0 && !s_notnan) *status = 2;
+    __syncthreads();
+}
+
