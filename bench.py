@@ -516,7 +516,7 @@ def main():
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "draws_total": n_total, "draws_per_gpu": j1 - j0, "swarm": S, "points": K,
-                   "step": "one PSO iteration = two launches: k_objective (all particles x this GPU's draws) + k_pso_tail (finishes the per-CTA partial sums, sums them over the ranks through NVLink peer memory when N > 1, pso_update_best!, and the next iteration's move); with KST_BENCH_COLLECTIVE=nccl: k_pso_move + k_objective + k_obj_finish + ncclAllReduce + k_pso_best",
+                   "step": "one PSO iteration = three launches: k_pso_move, k_objective (all particles x this GPU's draws), and k_pso_best (N = 1) / k_pso_tail (N > 1), which finishes the per-CTA partial sums, sums them over the ranks through NVLink peer memory and does pso_update_best!; with KST_BENCH_COLLECTIVE=nccl: k_pso_move + k_objective + k_obj_finish + ncclAllReduce + k_pso_best",
                    "l2": "flushed between steps (256 MiB write on the same stream, outside the events)",
                    "parallelism": "prior draws sharded over %d GPU(s), swarm replicated" % world,
                    "collective": {"peer": "fused NVLink peer-memory all-reduce kernel (S doubles per step)",
@@ -526,10 +526,10 @@ def main():
                 "d2h_bytes_per_step": int(S * 8), "ms_per_step": e2e_ms / args.steps,
                 "wall_ms_per_step": e2e_wall_ms / args.steps,
                 "call": "kst_objective_batch (host buffers, pinned) = one swarm evaluation"},
-        # own kernels per timed step on each rank: k_objective + k_pso_tail (finish, peer all-reduce, best, next move);
-        # on the NCCL path move, objective, finish and best are separate launches (ncclAllReduce is a library kernel,
-        # not counted)
-        "gpu_launches": int((4 if collective == "nccl" else 2) * args.steps),
+        # own kernels per timed step on each rank: move, objective, best (N = 1) or tail (N > 1: finish + peer
+        # all-reduce + best); on the NCCL path finish and best are separate launches (ncclAllReduce is a library
+        # kernel, not counted)
+        "gpu_launches": int((4 if collective == "nccl" else 3) * args.steps),
         "roofline": roofline,
         "cpu_baseline": cpu,
         "parity_check": parity,

@@ -6,7 +6,6 @@
 #include <string.h>
 
 #include <cmath>
-#include <utility>
 #include <mutex>
 #include <new>
 
@@ -461,7 +460,7 @@ static int pso_setup(kst_problem *h, int S, int K, double c1, double c2, const d
     int rc = kst_pso_alloc(h, S, K);
     if (rc) return rc;
     KstPso &p = h->pso;
-    p.mode = mode; p.c1 = c1; p.c2 = c2; p.seed = seed; p.iter = 0; p.n_eval = 0; p.pending_n_blk = 0; p.next_ready = 0;
+    p.mode = mode; p.c1 = c1; p.c2 = c2; p.seed = seed; p.iter = 0; p.n_eval = 0; p.pending_n_blk = 0;
     // "fixing all weights but one is equivalent to fixing them all" (src/designmeasure-abstractpoint.jl:51-56)
     int fw[KST_MAX_ROWS], nfix = 0;
     for (int k = 0; k < K; k++) { fw[k] = fixw[k] != 0; nfix += fw[k]; }
@@ -518,20 +517,13 @@ static int pso_ticks_unfused(kst_problem *h, int n_iters, int slot0)
 {
     KstPso &p = h->pso;
     const int gd = p.mode == KST_PSO_MODE_GATEAUX;
-    const bool tail = h->nranks <= 1 || (h->peer_ready && p.S <= KST_PEER_CAP);
+    const bool tail = h->nranks > 1 && h->peer_ready && p.S <= KST_PEER_CAP;
     for (int it = 0; it < n_iters; it++) {
-        int rc;
-        if (p.next_ready) {
-            // the previous iteration's tail kernel has already moved the swarm into the next-position buffers
-            std::swap(p.x_pts, p.xn_pts); std::swap(p.x_w, p.xn_w);
-            std::swap(p.v_pts, p.vn_pts); std::swap(p.v_w, p.vn_w);
-            p.next_ready = 0;
-        } else {
-            rc = kst_launch_pso_move(h);
-            if (rc) return rc;
-        }
+        int rc = kst_launch_pso_move(h);
+        if (rc) return rc;
         if (tail) {
-            // evaluation + one tail launch: finish, sum over the ranks, best update, the next iteration's move
+            // several GPUs with a peer exchange: evaluation + ONE launch that finishes the partial sums, sums them over
+            // the ranks and updates the bests
             int n_blk = 0, nan_fill = 0;
             double offset = 0.0;
             rc = kst_launch_objective(h, p.S, p.K, p.x_pts, p.x_w, p.fx, &n_blk, gd);

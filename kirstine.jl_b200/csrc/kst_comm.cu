@@ -200,55 +200,34 @@ __global__ void __launch_bounds__(1024) k_peer_allreduce(double *buf, int count,
     kst_peer_allreduce_cta(buf, count, peers, nranks, rank, seq, partials, n_blk, offset, 0);
 }
 
-// The tail of a swarm iteration in ONE single-CTA launch (after the evaluation kernel):
+// The tail of a swarm iteration on several GPUs in ONE single-CTA launch (after the evaluation kernel):
 //   1. fx = fixed-order sum of the evaluation's per-CTA partial sums (+ offset), summed over the ranks through the
-//      peer-memory exchange when there are several (kst_peer_allreduce_cta);
-//   2. pso_update_best! (kst_pso_best_cta);
-//   3. the NEXT iteration's tick! (src/pso.jl:127-141: velocity + constrained move) into the next-position buffers
-//      xn / vn, which the host swaps in when that iteration starts.  x and v themselves stay what the last
-//      evaluation saw, so kst_pso_get_state reads a consistent state at any time.
-// With the move riding along here, an iteration of a swarm too large for the persistent kernel is two launches
-// (evaluation + this) on one GPU and on several, instead of three and four.
+//      peer-memory exchange (kst_peer_allreduce_cta);
+//   2. pso_update_best! (kst_pso_best_cta).
+// An iteration is then move + evaluation + this: three launches, as on one GPU (where k_pso_best finishes the partial
+// sums).  Folding the next iteration's move in here as well was measured and dropped: one CTA moving 1024 particles
+// is a chain of dependent L2 round trips on a single SM (about 100 us against 40 us for the separate launches).
 __global__ void __launch_bounds__(1024) k_pso_tail(KstPsoDev s, KstPeerPtrs peers, int nranks, int rank,
                                                    unsigned long long seq, const double *__restrict__ partials, int n_blk,
                                                    double offset, int nan_fill, double *tr_fx, double *tr_pts, double *tr_w,
-                                                   int slot, double *xn_pts, double *xn_w, double *vn_pts, double *vn_w,
-                                                   uint32_t next_iter, double c1, double c2, double chi)
+                                                   int slot)
 {
-    if (nranks > 1) {
-        kst_peer_allreduce_cta(s.fx, s.S, peers, nranks, rank, seq, partials, n_blk, offset, nan_fill);
-        kst_pso_best_cta(s, 0, tr_fx, tr_pts, tr_w, slot, nullptr, nullptr, 0, 0.0, 0);
-    } else {
-        kst_pso_best_cta(s, 0, tr_fx, tr_pts, tr_w, slot, nullptr, partials, n_blk, offset, nan_fill);
-    }
-    const int K = s.K, d = s.d;
-    for (int i = threadIdx.x; i < s.S; i += blockDim.x) {
-        double *xp = xn_pts + (size_t)i * K * d, *xw = xn_w + (size_t)i * K;
-        double *vp = vn_pts + (size_t)i * K * d, *vw = vn_w + (size_t)i * K;
-        for (int c = 0; c < K * d; c++) { xp[c] = s.x_pts[(size_t)i * K * d + c]; vp[c] = s.v_pts[(size_t)i * K * d + c]; }
-        for (int k = 0; k < K; k++) { xw[k] = s.x_w[(size_t)i * K + k]; vw[k] = s.v_w[(size_t)i * K + k]; }
-        kst_pso_move_particle(K, d, xw, xp, s.p_w + (size_t)i * K, s.p_pts + (size_t)i * K * d, vw, vp, s.g_w, s.g_pts,
-                              s.fixw, s.fixp, s.lb, s.ub, c1, c2, chi, KstRndPhilox{s.seed, next_iter, (uint32_t)i});
-    }
+    kst_peer_allreduce_cta(s.fx, s.S, peers, nranks, rank, seq, partials, n_blk, offset, nan_fill);
+    kst_pso_best_cta(s, 0, tr_fx, tr_pts, tr_w, slot, nullptr, nullptr, 0, 0.0, 0);
 }
 
 int kst_launch_pso_tail(kst_problem *h, int trace_slot, int n_blk, double offset, int nan_fill)
 {
     KstPso &p = h->pso;
-    if (h->nranks > 1 && !(h->peer_ready && p.S <= KST_PEER_CAP)) return 1;
+    if (h->nranks <= 1 || !(h->peer_ready && p.S <= KST_PEER_CAP)) return 1;
     KstPsoDev s;
     kst_pso_make_dev(h, &s);
     KstPeerPtrs pp;
     for (int r = 0; r < KST_PEER_MAX; r++) pp.blk[r] = (KstPeerBlock *)h->peer_map[r];
-    const double phi = p.c1 + p.c2;
-    const double chi = 2 / fabs(2 - phi - sqrt(phi * phi - 4 * phi));  // src/pso.jl:134-135
-    const unsigned long long seq = h->nranks > 1 ? ++h->peer_seq : 0;
-    k_pso_tail<<<1, 1024, 0, h->stream>>>(s, pp, h->nranks, h->rank, seq, h->partials, n_blk, offset, nan_fill,
+    k_pso_tail<<<1, 1024, 0, h->stream>>>(s, pp, h->nranks, h->rank, ++h->peer_seq, h->partials, n_blk, offset, nan_fill,
                                            trace_slot >= 0 ? p.tr_fx : nullptr, trace_slot >= 0 ? p.tr_pts : nullptr,
-                                           trace_slot >= 0 ? p.tr_w : nullptr, trace_slot >= 0 ? trace_slot : 0, p.xn_pts,
-                                           p.xn_w, p.vn_pts, p.vn_w, (uint32_t)(p.iter + 1), p.c1, p.c2, chi);
+                                           trace_slot >= 0 ? p.tr_w : nullptr, trace_slot >= 0 ? trace_slot : 0);
     KST_CUDA(cudaGetLastError());
-    p.next_ready = 1;
     return KST_OK;
 }
 

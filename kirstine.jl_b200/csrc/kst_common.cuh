@@ -71,10 +71,6 @@ struct KstPso {
     // persistent swarm kernel (kst_pso_fused.cuh): published positions [2][S][K*d] / [2][S][K], grid barrier counter
     // (+ error word) and how far it has counted
     double *x2_pts = nullptr, *x2_w = nullptr;
-    // the swarm's next positions and velocities, written by the tail kernel of an iteration (kst_comm.cu: finish +
-    // all-reduce + best update + move); the next iteration starts by swapping them in instead of launching a move
-    double *xn_pts = nullptr, *xn_w = nullptr, *vn_pts = nullptr, *vn_w = nullptr;
-    int next_ready = 0;
     unsigned long long *bar = nullptr;
     unsigned long long bar_count = 0;
     int fused_off = 0;  // this swarm does not fit the persistent kernel: do not ask again
@@ -187,9 +183,9 @@ int kst_launch_pso_best(kst_problem *h, int init, int trace_slot);
 // kst_comm.cu
 int kst_allreduce_sum(kst_problem *h, double *d_buf, size_t count);
 int kst_objective_allreduce(kst_problem *h, int S, int K, const double *d_pts, const double *d_w, double *d_fx);
-// One launch after the evaluation kernel of a swarm iteration: finish the per-CTA partial sums, sum over the ranks
-// (peer-memory exchange, when the handle has one), pso_update_best!, and the NEXT iteration's move into the swarm's
-// next-position buffers.  Returns 1 when not applicable (several ranks without a peer exchange, or S beyond it).
+// One launch after the evaluation kernel of a swarm iteration on several GPUs: finish the per-CTA partial sums, sum
+// over the ranks through the peer-memory exchange, pso_update_best!.  Returns 1 when not applicable (one GPU, no
+// peer exchange, or S beyond its capacity).
 int kst_launch_pso_tail(kst_problem *h, int trace_slot, int n_blk, double offset, int nan_fill);
 void kst_comm_release(kst_problem *h);
 // kst_api.cu

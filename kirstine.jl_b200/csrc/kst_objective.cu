@@ -351,7 +351,6 @@ int kst_launch_pso_fused(kst_problem *h, int n_steps, int first_is_init, int tr_
     if (rc == KST_FUSED_NOFIT) p.fused_off = 1;
     if (rc) return rc;
     p.bar_count += (unsigned long long)n_steps * (unsigned long long)(n_blk * tiles);
-    p.next_ready = 0;  // the persistent kernel moved the swarm itself, starting from x
     return KST_OK;
 }
 

@@ -125,9 +125,8 @@ int kst_pso_alloc(kst_problem *h, int S, int K)
 {
     KstPso &p = h->pso;
     const size_t np = (size_t)S * K * h->d, nw = (size_t)S * K, kd = (size_t)K * h->d;
-    // doubles: barrier words (2), x p v (3 np + 3 nw), published positions (2 np + 2 nw), next x and v (2 np + 2 nw),
-    // g, fx, fp, fg, fixw / fixp
-    const size_t need = 2 + 7 * (np + nw) + kd + K + 2 * (size_t)S + 1 + (size_t)K + 2;
+    // doubles: barrier words (2), x p v (3 np + 3 nw), published positions (2 np + 2 nw), g, fx, fp, fg, fixw / fixp
+    const size_t need = 2 + 5 * (np + nw) + kd + K + 2 * (size_t)S + 1 + (size_t)K + 2;
     if (need > p.arena_cap) {
         KST_CUDA(cudaStreamSynchronize(h->stream));
         if (p.arena) KST_CUDA(cudaFree(p.arena));
@@ -142,10 +141,7 @@ int kst_pso_alloc(kst_problem *h, int S, int K)
     double *q = p.arena;
     p.bar = (unsigned long long *)q; q += 2;
     p.x_pts = q; q += np; p.p_pts = q; q += np; p.v_pts = q; q += np; p.x2_pts = q; q += 2 * np;
-    p.xn_pts = q; q += np; p.vn_pts = q; q += np;
     p.x_w = q; q += nw; p.p_w = q; q += nw; p.v_w = q; q += nw; p.x2_w = q; q += 2 * nw;
-    p.xn_w = q; q += nw; p.vn_w = q; q += nw;
-    p.next_ready = 0;
     p.g_pts = q; q += kd; p.g_w = q; q += K;
     p.fx = q; q += S; p.fp = q; q += S; p.fg = q; q += 1;
     p.fixw = (int *)q; p.fixp = p.fixw + K;

@@ -50,9 +50,14 @@ def _worker(rank, world, port, out_dir, peer=False):
     st = h.pso_state()
     h.gateaux_prepare(pts[0], w[0])
     gd = h.gateaux_eval(np.linspace(0, 1, 33))
+    # the Exchange strategy's direction swarm (Gateaux mode) and a whole Exchange run on the sharded prior
+    _, gfx, gpx, _, _ = h.pso_optimize(12, 1, 5, pts[0][[1, 4, 6]].reshape(3, 1, 1), np.ones((3, 1)), seed=3,
+                                       mode=kb._ffi.PSO_MODE_GATEAUX, state0=False)
+    ex = h.exchange_run(pts[0], w[0], 2, (12, 4, 2.05, 2.05), (10, 4, 2.05, 2.05), seed=8, state0=False)
     if peer:
         assert h.comm_peer_error() == 0
-    np.savez(os.path.join(out_dir, "r%d.npz" % rank), fx=fx, tfx=tfx, tp=tp, tw=tw, x=st["x_pts"], xw=st["x_w"], gd=gd)
+    np.savez(os.path.join(out_dir, "r%d.npz" % rank), fx=fx, tfx=tfx, tp=tp, tw=tw, x=st["x_pts"], xw=st["x_w"], gd=gd,
+             gfx=gfx, gpx=gpx, exw=ex["weights"], exp=ex["points"], exfx=ex["w_fx"])
     dist.destroy_process_group()
 
 
@@ -80,3 +85,15 @@ def test_two_gpu_sharded_run_matches_single_gpu(tmp_path, peer):
     np.testing.assert_allclose(a["x"], h.pso_state()["x_pts"], rtol=1e-9, atol=1e-12)
     h.gateaux_prepare(pts[0], w[0])
     np.testing.assert_allclose(a["gd"], h.gateaux_eval(np.linspace(0, 1, 33)), rtol=1e-10, atol=1e-12)
+    _, gfx, gpx, _, _ = h.pso_optimize(12, 1, 5, pts[0][[1, 4, 6]].reshape(3, 1, 1), np.ones((3, 1)), seed=3,
+                                       mode=kb._ffi.PSO_MODE_GATEAUX, state0=False)
+    np.testing.assert_allclose(a["gfx"], gfx, rtol=1e-9, atol=1e-10 * np.abs(gfx).max())
+    np.testing.assert_allclose(a["gpx"], gpx, rtol=1e-9)
+    ex = h.exchange_run(pts[0], w[0], 2, (12, 4, 2.05, 2.05), (10, 4, 2.05, 2.05), seed=8, state0=False)
+    np.testing.assert_allclose(a["exfx"], ex["w_fx"], rtol=1e-10)
+    np.testing.assert_allclose(a["exp"], ex["points"], rtol=1e-8)
+    np.testing.assert_allclose(a["exw"], ex["weights"], rtol=1e-7, atol=1e-9)
+    # the sharded result against the CPU oracle on the whole prior
+    import oracle as ko
+    want = ko.Problem(ko.SIGEMAX, [1.0], theta).objective_batch(pts, w, nthreads=8)
+    np.testing.assert_allclose(a["fx"], want, rtol=1e-10)
