@@ -65,7 +65,7 @@ extern "C" int kst_problem_destroy(kst_problem *h)
     kst_comm_release(h);
     kst_pso_free(h);
     void *ptrs[] = {h->theta, h->pw, h->dc, h->cs, h->aux, h->reg, h->partials, h->stage_pts, h->stage_w, h->stage_fx,
-                    h->gA, h->gAp, h->gtrB, h->g_wtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials, h->gd_ones};
+                    h->gA, h->gAp, h->gtrB, h->g_wtrB, h->d_flag, h->gd_dirs, h->gd_out, h->gd_partials, h->gd_ones, h->g_out};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
@@ -156,7 +156,7 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
     h->w_uniform = prior_w[0];
 
     int rc = KST_OK;
-    double *d_theta_aos = nullptr, *d_dt = nullptr;
+    double *d_theta_aos = nullptr, *d_dt = nullptr, *d_scratch = nullptr;
 #define KST_TRY(call)                        \
     do {                                     \
         cudaError_t e__ = (call);            \
@@ -186,15 +186,18 @@ extern "C" int kst_problem_create(int model_id, const double *model_params, int 
         KST_TRY(cudaMalloc(&d_dt, sizeof(double) * N * t * r));
         KST_TRY(cudaMemcpyAsync(d_dt, dt_jm, sizeof(double) * N * t * r, cudaMemcpyHostToDevice, h->stream));
     }
-    rc = kst_launch_prep_draws(h, d_theta_aos, d_dt);
+    KST_TRY(cudaMalloc(&d_scratch, sizeof(double) * (N + 8)));
+    rc = kst_launch_prep_draws(h, d_theta_aos, d_dt, d_scratch);
     if (rc) goto fail;
     KST_TRY(cudaStreamSynchronize(h->stream));
     cudaFree(d_theta_aos);
+    cudaFree(d_scratch);
     if (d_dt) cudaFree(d_dt);
     *out = h;
     return KST_OK;
 fail:
     if (d_theta_aos) cudaFree(d_theta_aos);
+    if (d_scratch) cudaFree(d_scratch);
     if (d_dt) cudaFree(d_dt);
     kst_problem_destroy(h);
     return rc;
@@ -298,15 +301,16 @@ extern "C" int kst_problem_set_regularization(kst_problem *h, const double *R)
     for (int i = 0; i < r * r; i++)
         if (!std::isfinite(R[i])) { kst_set_error("set_regularization: R must be finite"); return KST_EINVAL; }
     if (!h->reg) KST_CUDA(cudaMalloc(&h->reg, sizeof(double) * (size_t)(r * (r + 1) / 2) * h->ld));
-    double *d_R = nullptr;
-    KST_CUDA(cudaMalloc(&d_R, sizeof(double) * r * r));
+    // R travels through the handle's staging buffer (r * r <= 25 doubles)
+    int rcs = kst_ensure_stage(h, (size_t)(r * r), 1);
+    if (rcs) return rcs;
+    double *d_R = h->stage_fx;
     cudaError_t e = cudaMemcpyAsync(d_R, R, sizeof(double) * r * r, cudaMemcpyHostToDevice, h->stream);
     if (e == cudaSuccess) {
         k_prep_reg<<<(unsigned)((h->N + 255) / 256), 256, 0, h->stream>>>(h->cs, d_R, r, h->N, h->ld, h->reg);
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-    cudaFree(d_R);
     if (e != cudaSuccess) {
         cudaFree(h->reg);
         h->reg = nullptr;
@@ -374,13 +378,12 @@ extern "C" int kst_gateaux_constants(kst_problem *h, double *A, double *tr_B)
     KST_CHECK_HANDLE(h);
     if (!h->g_ready) { kst_set_error("gateaux_constants before gateaux_prepare"); return KST_ESTATE; }
     if (A) {
-        double *d_out = nullptr;
-        KST_CUDA(cudaMalloc(&d_out, sizeof(double) * h->N * h->r * h->r));
-        k_unscale_gconst<<<(unsigned)((h->N + 127) / 128), 128, 0, h->stream>>>(h->gA, h->cs, h->ld, h->N, h->r, d_out);
+        // the copy-out buffer belongs to the handle and is allocated on first use (debugging path of the reference)
+        if (!h->g_out) KST_CUDA(cudaMalloc(&h->g_out, sizeof(double) * h->N * h->r * h->r));
+        k_unscale_gconst<<<(unsigned)((h->N + 127) / 128), 128, 0, h->stream>>>(h->gA, h->cs, h->ld, h->N, h->r, h->g_out);
         KST_CUDA(cudaGetLastError());
-        KST_CUDA(cudaMemcpyAsync(A, d_out, sizeof(double) * h->N * h->r * h->r, cudaMemcpyDeviceToHost, h->stream));
+        KST_CUDA(cudaMemcpyAsync(A, h->g_out, sizeof(double) * h->N * h->r * h->r, cudaMemcpyDeviceToHost, h->stream));
         KST_CUDA(cudaStreamSynchronize(h->stream));
-        KST_CUDA(cudaFree(d_out));
     }
     if (tr_B) {
         KST_CUDA(cudaMemcpyAsync(tr_B, h->gtrB, sizeof(double) * h->N, cudaMemcpyDeviceToHost, h->stream));

@@ -127,6 +127,7 @@ struct kst_problem {
     int *d_flag = nullptr;     // 16 bytes: device flag word (singular detection) + one double of scratch at offset 8
     double *gd_dirs = nullptr, *gd_out = nullptr, *gd_partials = nullptr;
     size_t gd_cap = 0, gd_partials_cap = 0;
+    double *g_out = nullptr;    // kst_gateaux_constants: A_j in the reference's scale, [N][r*r]
     double *gd_ones = nullptr;  // unit weights for directions evaluated through the objective kernel (dense covariance)
     size_t gd_ones_cap = 0;
 
@@ -148,7 +149,7 @@ struct kst_problem {
 };
 
 // kst_objective.cu
-int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const double *d_dt);
+int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const double *d_dt, double *d_scratch);
 // defer_n_blk != nullptr: the per-CTA partial sums stay in h->partials ([*defer_n_blk][S]) and the caller finishes them
 // (kst_api.cu fuses that step into the peer-memory all-reduce)
 // gd = 1: the Gateaux derivative of the prepared design in the swarm's one-point directions (K = 1) instead of the

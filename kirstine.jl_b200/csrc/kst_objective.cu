@@ -167,10 +167,10 @@ int kst_sum_fixed(kst_problem *h, const double *d_x, int64_t n, double *host_out
 // host-side dispatch
 // ------------------------------------------------------------------------------------------
 
-int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const double *d_dt)
+// d_scratch: N + 8 doubles owned by the caller (kst_problem_create frees it with its other upload temporaries)
+int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const double *d_dt, double *d_scratch)
 {
-    double *woff = nullptr;
-    KST_CUDA(cudaMalloc(&woff, sizeof(double) * h->N));
+    double *woff = d_scratch;
     const int nt = 256;
     const unsigned nb = (unsigned)((h->N + nt - 1) / nt);
     KST_MODEL_SWITCH(h->model_id,
@@ -179,13 +179,11 @@ int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const doubl
                                                                  h->aux, woff)));
     KST_CUDA(cudaGetLastError());
     int rc = kst_sum_fixed(h, woff, h->N, &h->offset);
-    cudaFree(woff);
     if (rc) return rc;
     // per-problem maxima of the hoisted constants (KstObjParams::dcmax)
     int ndc = 0;
     KST_MODEL_SWITCH(h->model_id, ndc = MF::NDC);
-    unsigned long long *d_max = nullptr, bits[8] = {};
-    KST_CUDA(cudaMalloc(&d_max, sizeof(bits)));
+    unsigned long long *d_max = (unsigned long long *)(d_scratch + h->N), bits[8] = {};
     cudaError_t e = cudaMemsetAsync(d_max, 0, sizeof(bits), h->stream);
     if (e == cudaSuccess) {
         k_absmax<<<h->sm_count * 4, 256, 0, h->stream>>>(h->dc, ndc, h->ld, h->N, d_max);
@@ -193,7 +191,6 @@ int kst_launch_prep_draws(kst_problem *h, const double *d_theta_aos, const doubl
     }
     if (e == cudaSuccess) e = cudaMemcpyAsync(bits, d_max, sizeof(bits), cudaMemcpyDeviceToHost, h->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-    cudaFree(d_max);
     if (e != cudaSuccess) { kst_set_error("prep_draws: %s", cudaGetErrorString(e)); return KST_ECUDA; }
     for (int c = 0; c < 8; c++) memcpy(&h->dcmax[c], &bits[c], sizeof(double));
     return KST_OK;
