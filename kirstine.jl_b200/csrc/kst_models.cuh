@@ -232,6 +232,34 @@ struct KstDense<KstVuAr> {
     static constexpr bool value = true;
 };
 
+// Trait: draws evaluated per thread and pass over a particle's rows in the objective kernel (1 or 2).  Two pay off
+// where the per-draw bookkeeping weighs as much as the rows themselves (few, cheap rows).
+#ifndef KST_NDRAW_EMAX
+#define KST_NDRAW_EMAX 2
+#endif
+#ifndef KST_NDRAW_SIGEMAX
+#define KST_NDRAW_SIGEMAX 1
+#endif
+#ifndef KST_NDRAW_TPC
+#define KST_NDRAW_TPC 1
+#endif
+template <class MF>
+struct KstDraws {
+    static constexpr int value = 1;
+};
+template <>
+struct KstDraws<KstEmax> {
+    static constexpr int value = KST_NDRAW_EMAX;
+};
+template <>
+struct KstDraws<KstSigEmax> {
+    static constexpr int value = KST_NDRAW_SIGEMAX;
+};
+template <>
+struct KstDraws<KstTpc> {
+    static constexpr int value = KST_NDRAW_TPC;
+};
+
 // dose-time-response model: test/example-dtr.jl:27-47, docs/src/dtr.md:87-129.  theta = (a, e, e0, emax, ec50)
 //   A = exp(-a t), B = exp(-e t), C = B - A, rd = e - a, den = dose C a - rd ec50, w = 1/den
 //   row = [-dose ec50 emax (A t a rd + e C) w^2, dose a ec50 emax (B t rd + C) w^2, 1, dose a C w, dose a emax C rd w^2]

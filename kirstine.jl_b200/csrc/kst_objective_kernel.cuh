@@ -230,6 +230,47 @@ __device__ __forceinline__ void kst_rows(double *M, unsigned addr, const double 
     for (int k = 0; k < NR; k++) kst_accum<R, MF::CONST_COL>(M, g[k]);
 }
 
+// Two draws per thread (KstDraws<MF>::value == 2): every row record is loaded once and evaluated for both draws, so
+// the shared-memory load, the loop bookkeeping and the per-draw set-up are paid once per pair.  NR rows x 2 draws
+// give the independent chains.
+template <class MF, int NR, bool CLAMP = true>
+__device__ __forceinline__ void kst_rows2(double *MA, double *MB, unsigned addr, const double *dcA, const double *dcB,
+                                          KstTab tab)
+{
+    constexpr int R = MF::R, RW = KstTile<MF>::RW;
+    double gA[NR][R], gB[NR][R];
+#pragma unroll
+    for (int k = 0; k < NR; k++) {
+        double rw[RW];
+#pragma unroll
+        for (int c = 0; c < RW; c += 2)
+            asm("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(rw[c]), "=d"(rw[c + 1]) : "r"(addr + (unsigned)(k * RW * 8) + 8u * c));
+        MF::template row<CLAMP>(rw + 1, dcA, rw[0], gA[k], tab);
+        MF::template row<CLAMP>(rw + 1, dcB, rw[0], gB[k], tab);
+    }
+#pragma unroll
+    for (int k = 0; k < NR; k++) {
+        kst_accum<R, MF::CONST_COL>(MA, gA[k]);
+        kst_accum<R, MF::CONST_COL>(MB, gB[k]);
+    }
+}
+
+template <class MF, bool CLAMP = true>
+__device__ __forceinline__ void kst_fisher2(double *MA, double *MB, unsigned rows_addr, int na, double sw,
+                                            const double *dcA, const double *dcB, KstTab tab)
+{
+    constexpr int R = MF::R, RW = KstTile<MF>::RW, UN = MF::ROWS >= 2 ? MF::ROWS / 2 : 1;
+#pragma unroll
+    for (int i = 0; i < KstPacked<R>::N; i++) MA[i] = MB[i] = 0.0;
+    unsigned addr = rows_addr;
+    int left = na;
+    if (UN > 1 && (left & 1)) { kst_rows2<MF, 1, CLAMP>(MA, MB, addr, dcA, dcB, tab); addr += RW * 8; left -= 1; }
+#pragma unroll 1
+    for (; left > 0; left -= UN, addr += UN * RW * 8) kst_rows2<MF, UN, CLAMP>(MA, MB, addr, dcA, dcB, tab);
+    constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
+    if (MF::CONST_COL >= 0) MA[kst_pidx<R>(cc, cc)] = MB[kst_pidx<R>(cc, cc)] = sw;
+}
+
 // Mt = sum over the particle's live rows (at least one) of g g'; rows_addr is a shared-space address.
 // Remainders first (1, 2, 4 rows by the bits of na), then groups of MF::ROWS rows: the FP64 pipe only
 // saturates with about four independent dependency chains per warp (tools/fp64_probe.cu), which the
@@ -399,8 +440,88 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
                 }
             }
             };
+            // The same loop over PAIRS of draws (j, j + stride): one pass over the particle's rows serves both.  A thread
+            // with an odd number of draws evaluates its last one twice and counts it once.
+            auto draws2 = [&](auto clamp_tag) {
+            constexpr bool CL = decltype(clamp_tag)::value;
+            double dcm[MF::NDC], pwm = 0.0;  // the pair's second draw, prefetched like the first
+            if (j0 < n) {
+                const int jb = j0 + stride < n ? j0 + stride : j0;
+#pragma unroll
+                for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jb));
+                pwm = __ldg(pw + jb);
+            }
+            for (int j = j0; j < n; j += 2 * stride) {
+                double dcA[MF::NDC], dcB[MF::NDC];
+#pragma unroll
+                for (int c = 0; c < MF::NDC; c++) { dcA[c] = dcn[c]; dcB[c] = dcm[c]; }
+                const double pwA = pwn, pwB = pwm;
+                const int jB = j + stride;
+                const bool liveB = jB < n;
+                const int jn = j + 2 * stride;
+                if (jn < n) {
+                    const int jm = jn + stride < n ? jn + stride : jn;
+#pragma unroll
+                    for (int c = 0; c < MF::NDC; c++) {
+                        dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
+                        dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jm));
+                    }
+                    pwn = __ldg(pw + jn);
+                    pwm = __ldg(pw + jm);
+                }
+                double MA[KstPacked<R>::N], MB[KstPacked<R>::N];
+                kst_fisher2<MF, CL>(MA, MB, rows_addr, na, sw, dcA, dcB, tab);
+                const int jBl = liveB ? jB : j;
+                if (REG) {
+#pragma unroll
+                    for (int i = 0; i < KstPacked<R>::N; i++) {
+                        MA[i] += __ldg(prm.reg + ((size_t)i * ld + (size_t)j));
+                        MB[i] += __ldg(prm.reg + ((size_t)i * ld + (size_t)jBl));
+                    }
+                }
+                if (CRIT == KST_KCRIT_GD) {
+                    double qA = 0.0, qB = 0.0;
+#pragma unroll
+                    for (int i = 0; i < KstPacked<R>::N; i++) {
+                        qA = fma(__ldg(prm.aux + ((size_t)i * ld + (size_t)j)), MA[i], qA);
+                        qB = fma(__ldg(prm.aux + ((size_t)i * ld + (size_t)jBl)), MB[i], qB);
+                    }
+                    acc += qA;
+                    if (liveB) acc += qB;
+                } else if (UNI) {
+                    double detA, detB;
+                    int signsA, signsB;
+                    kst_det_signs<R, INV0>(MA, inv0, detA, signsA);
+                    kst_det_signs<R, INV0>(MB, inv0, detB, signsB);
+                    if (!liveB) { detB = 1.0; signsB = 0; }
+                    const double pn = run * detA * detB;
+                    const unsigned key = ((unsigned)(signsA | signsB) & 0x80000000u) | (unsigned)__double2hiint(pn);
+                    if (((key >> 20) - 423u) < 1200u) {
+                        run = pn;
+                    } else {
+                        acc += kst_log(run, tab) + kst_log_checked(detA, signsA, tab);
+                        if (liveB) acc += kst_log_checked(detB, signsB, tab);
+                        run = 1.0;
+                    }
+                } else {
+                    bool excA, excB;
+                    const double vA = kst_criterion<R, (CRIT == KST_KCRIT_GD ? 0 : CRIT), T, INV0>(MA, prm.aux + j, prm.ld, excA, inv0, tab);
+                    const double vB = kst_criterion<R, (CRIT == KST_KCRIT_GD ? 0 : CRIT), T, INV0>(MB, prm.aux + jBl, prm.ld, excB, inv0, tab);
+                    acc += excA ? -KST_INF : pwA * vA;
+                    if (liveB) acc += excB ? -KST_INF : pwB * vB;
+                }
+            }
+            };
             // uniform over the warp: all lanes work on the same particle
-            if constexpr (DUAL) {
+            constexpr bool PAIRS = KstDraws<MF>::value == 2 && !KstDense<MF>::value;
+            if constexpr (PAIRS) {
+                if constexpr (DUAL) {
+                    if (KstTile<MF>::safe(smem, rows_max)[p]) draws2(KstFalse{});
+                    else draws2(KstTrue{});
+                } else {
+                    draws2(KstTrue{});
+                }
+            } else if constexpr (DUAL) {
                 if (KstTile<MF>::safe(smem, rows_max)[p]) draws(KstFalse{});
                 else draws(KstTrue{});
             } else {
