@@ -238,10 +238,10 @@ struct KstDense<KstVuAr> {
 #define KST_NDRAW_EMAX 2
 #endif
 #ifndef KST_NDRAW_SIGEMAX
-#define KST_NDRAW_SIGEMAX 1
+#define KST_NDRAW_SIGEMAX 2
 #endif
 #ifndef KST_NDRAW_TPC
-#define KST_NDRAW_TPC 1
+#define KST_NDRAW_TPC 2
 #endif
 template <class MF>
 struct KstDraws {

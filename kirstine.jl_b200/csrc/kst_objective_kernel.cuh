@@ -233,7 +233,13 @@ __device__ __forceinline__ void kst_rows(double *M, unsigned addr, const double 
 // Two draws per thread (KstDraws<MF>::value == 2): every row record is loaded once and evaluated for both draws, so
 // the shared-memory load, the loop bookkeeping and the per-draw set-up are paid once per pair.  NR rows x 2 draws
 // give the independent chains.
-template <class MF, int NR, bool CLAMP = true>
+#ifndef KST_F2_INIT
+#define KST_F2_INIT 0   // 1: the first row block of a pair of draws initialises the accumulators instead of adding to zeros
+#endif
+#ifndef KST_F2_ROWS
+#define KST_F2_ROWS 0   // > 0: rows per block in the two-draw loop (default: half the family's ROWS)
+#endif
+template <class MF, int NR, bool CLAMP = true, bool INIT = false>
 __device__ __forceinline__ void kst_rows2(double *MA, double *MB, unsigned addr, const double *dcA, const double *dcB,
                                           KstTab tab)
 {
@@ -250,8 +256,13 @@ __device__ __forceinline__ void kst_rows2(double *MA, double *MB, unsigned addr,
     }
 #pragma unroll
     for (int k = 0; k < NR; k++) {
-        kst_accum<R, MF::CONST_COL>(MA, gA[k]);
-        kst_accum<R, MF::CONST_COL>(MB, gB[k]);
+        if (INIT && k == 0) {
+            kst_accum_init<R, MF::CONST_COL>(MA, gA[k]);
+            kst_accum_init<R, MF::CONST_COL>(MB, gB[k]);
+        } else {
+            kst_accum<R, MF::CONST_COL>(MA, gA[k]);
+            kst_accum<R, MF::CONST_COL>(MB, gB[k]);
+        }
     }
 }
 
@@ -259,12 +270,22 @@ template <class MF, bool CLAMP = true>
 __device__ __forceinline__ void kst_fisher2(double *MA, double *MB, unsigned rows_addr, int na, double sw,
                                             const double *dcA, const double *dcB, KstTab tab)
 {
-    constexpr int R = MF::R, RW = KstTile<MF>::RW, UN = MF::ROWS >= 2 ? MF::ROWS / 2 : 1;
-#pragma unroll
-    for (int i = 0; i < KstPacked<R>::N; i++) MA[i] = MB[i] = 0.0;
+    constexpr int R = MF::R, RW = KstTile<MF>::RW, UN = KST_F2_ROWS > 0 ? KST_F2_ROWS : (MF::ROWS >= 4 ? MF::ROWS / 2 : MF::ROWS);  // two rows x two draws
+    static_assert(UN == 1 || UN == 2 || UN == 4, "rows per block");
     unsigned addr = rows_addr;
     int left = na;
+#if KST_F2_INIT
+    // the first block (the odd row when there is one, else a full block; na >= 1) sets the accumulators
+    if (UN > 1 && (left & 1)) { kst_rows2<MF, 1, CLAMP, true>(MA, MB, addr, dcA, dcB, tab); addr += RW * 8; left -= 1; }
+    else if (UN > 2 && (left & 2)) { kst_rows2<MF, 2, CLAMP, true>(MA, MB, addr, dcA, dcB, tab); addr += 2 * RW * 8; left -= 2; }
+    else { kst_rows2<MF, UN, CLAMP, true>(MA, MB, addr, dcA, dcB, tab); addr += UN * RW * 8; left -= UN; }
+    if (UN > 2 && (left & 2)) { kst_rows2<MF, 2, CLAMP>(MA, MB, addr, dcA, dcB, tab); addr += 2 * RW * 8; left -= 2; }
+#else
+#pragma unroll
+    for (int i = 0; i < KstPacked<R>::N; i++) MA[i] = MB[i] = 0.0;
     if (UN > 1 && (left & 1)) { kst_rows2<MF, 1, CLAMP>(MA, MB, addr, dcA, dcB, tab); addr += RW * 8; left -= 1; }
+    if (UN > 2 && (left & 2)) { kst_rows2<MF, 2, CLAMP>(MA, MB, addr, dcA, dcB, tab); addr += 2 * RW * 8; left -= 2; }
+#endif
 #pragma unroll 1
     for (; left > 0; left -= UN, addr += UN * RW * 8) kst_rows2<MF, UN, CLAMP>(MA, MB, addr, dcA, dcB, tab);
     constexpr int cc = MF::CONST_COL >= 0 ? MF::CONST_COL : 0;
