@@ -417,9 +417,9 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
                 pwn = __ldg(pw + j0);
             }
             // the draw loop, compiled twice for the kernels worth it: with and without the exponent clamp inside exp
-            auto draws = [&](auto clamp_tag) {
+            auto draws = [&](auto clamp_tag, const int jstart) {
             constexpr bool CL = decltype(clamp_tag)::value;
-            for (int j = j0; j < n; j += stride) {
+            for (int j = jstart; j < n; j += stride) {
                 double dcv[MF::NDC];
 #pragma unroll
                 for (int c = 0; c < MF::NDC; c++) dcv[c] = dcn[c];
@@ -461,34 +461,34 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
                 }
             }
             };
-            // The same loop over PAIRS of draws (j, j + stride): one pass over the particle's rows serves both.  A thread
-            // with an odd number of draws evaluates its last one twice and counts it once.
-            auto draws2 = [&](auto clamp_tag) {
+            // The same loop over PAIRS of draws (j, j + stride): one pass over the particle's rows serves both.  Returns
+            // the first draw it has not done: a thread with an odd number of draws leaves its last one to `draws`.
+            auto draws2 = [&](auto clamp_tag) -> int {
             constexpr bool CL = decltype(clamp_tag)::value;
+            constexpr bool liveB = true;
             double dcm[MF::NDC], pwm = 0.0;  // the pair's second draw, prefetched like the first
-            if (j0 < n) {
-                const int jb = j0 + stride < n ? j0 + stride : j0;
+            if (j0 + stride < n) {
 #pragma unroll
-                for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jb));
-                pwm = __ldg(pw + jb);
+                for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)(j0 + stride)));
+                pwm = __ldg(pw + j0 + stride);
             }
-            for (int j = j0; j < n; j += 2 * stride) {
+            int j = j0;
+            for (; j + stride < n; j += 2 * stride) {
                 double dcA[MF::NDC], dcB[MF::NDC];
 #pragma unroll
                 for (int c = 0; c < MF::NDC; c++) { dcA[c] = dcn[c]; dcB[c] = dcm[c]; }
                 const double pwA = pwn, pwB = pwm;
                 const int jB = j + stride;
-                const bool liveB = jB < n;
                 const int jn = j + 2 * stride;
                 if (jn < n) {
-                    const int jm = jn + stride < n ? jn + stride : jn;
 #pragma unroll
-                    for (int c = 0; c < MF::NDC; c++) {
-                        dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
-                        dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jm));
-                    }
+                    for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
                     pwn = __ldg(pw + jn);
-                    pwm = __ldg(pw + jm);
+                    if (jn + stride < n) {
+#pragma unroll
+                        for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)(jn + stride)));
+                        pwm = __ldg(pw + jn + stride);
+                    }
                 }
                 double MA[KstPacked<R>::N], MB[KstPacked<R>::N];
                 kst_fisher2<MF, CL>(MA, MB, rows_addr, na, sw, dcA, dcB, tab);
@@ -514,8 +514,7 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
                     int signsA, signsB;
                     kst_det_signs<R, INV0>(MA, inv0, detA, signsA);
                     kst_det_signs<R, INV0>(MB, inv0, detB, signsB);
-                    if (!liveB) { detB = 1.0; signsB = 0; }
-                    const double pn = run * detA * detB;
+                        const double pn = run * detA * detB;
                     const unsigned key = ((unsigned)(signsA | signsB) & 0x80000000u) | (unsigned)__double2hiint(pn);
                     if (((key >> 20) - 423u) < 1200u) {
                         run = pn;
@@ -532,21 +531,22 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
                     if (liveB) acc += excB ? -KST_INF : pwB * vB;
                 }
             }
+            return j;
             };
             // uniform over the warp: all lanes work on the same particle
             constexpr bool PAIRS = KstDraws<MF>::value == 2 && !KstDense<MF>::value;
             if constexpr (PAIRS) {
                 if constexpr (DUAL) {
-                    if (KstTile<MF>::safe(smem, rows_max)[p]) draws2(KstFalse{});
-                    else draws2(KstTrue{});
+                    if (KstTile<MF>::safe(smem, rows_max)[p]) draws(KstFalse{}, draws2(KstFalse{}));
+                    else draws(KstTrue{}, draws2(KstTrue{}));
                 } else {
-                    draws2(KstTrue{});
+                    draws(KstTrue{}, draws2(KstTrue{}));
                 }
             } else if constexpr (DUAL) {
-                if (KstTile<MF>::safe(smem, rows_max)[p]) draws(KstFalse{});
-                else draws(KstTrue{});
+                if (KstTile<MF>::safe(smem, rows_max)[p]) draws(KstFalse{}, j0);
+                else draws(KstTrue{}, j0);
             } else {
-                draws(KstTrue{});
+                draws(KstTrue{}, j0);
             }
             if (UNI) acc = prm.w_uniform * (acc + kst_log(run, tab));
         }
