@@ -232,34 +232,6 @@ struct KstDense<KstVuAr> {
     static constexpr bool value = true;
 };
 
-// Trait: draws evaluated per thread and pass over a particle's rows in the objective kernel (1 or 2).  Two pay off
-// where the per-draw bookkeeping weighs as much as the rows themselves (few, cheap rows).
-#ifndef KST_NDRAW_EMAX
-#define KST_NDRAW_EMAX 2
-#endif
-#ifndef KST_NDRAW_SIGEMAX
-#define KST_NDRAW_SIGEMAX 2
-#endif
-#ifndef KST_NDRAW_TPC
-#define KST_NDRAW_TPC 2
-#endif
-template <class MF>
-struct KstDraws {
-    static constexpr int value = 1;
-};
-template <>
-struct KstDraws<KstEmax> {
-    static constexpr int value = KST_NDRAW_EMAX;
-};
-template <>
-struct KstDraws<KstSigEmax> {
-    static constexpr int value = KST_NDRAW_SIGEMAX;
-};
-template <>
-struct KstDraws<KstTpc> {
-    static constexpr int value = KST_NDRAW_TPC;
-};
-
 // dose-time-response model: test/example-dtr.jl:27-47, docs/src/dtr.md:87-129.  theta = (a, e, e0, emax, ec50)
 //   A = exp(-a t), B = exp(-e t), C = B - A, rd = e - a, den = dose C a - rd ec50, w = 1/den
 //   row = [-dose ec50 emax (A t a rd + e C) w^2, dose a ec50 emax (B t rd + C) w^2, 1, dose a C w, dose a emax C rd w^2]
@@ -418,4 +390,45 @@ struct KstSinLogReg {
         g[1] = sc * u;
         g[2] = sc;
     }
+};
+
+// Trait: draws evaluated per thread and pass over a particle's rows in the objective kernel (1 or 2).  Two pay off
+// where the per-draw bookkeeping weighs as much as the rows themselves (few, cheap rows).
+#ifndef KST_NDRAW_EMAX
+#define KST_NDRAW_EMAX 2
+#endif
+#ifndef KST_NDRAW_SIGEMAX
+#define KST_NDRAW_SIGEMAX 2
+#endif
+#ifndef KST_NDRAW_TPC
+#define KST_NDRAW_TPC 2
+#endif
+template <class MF>
+struct KstDraws {
+    static constexpr int value = 1;
+};
+template <>
+struct KstDraws<KstEmax> {
+    static constexpr int value = KST_NDRAW_EMAX;
+};
+template <>
+struct KstDraws<KstSigEmax> {
+    static constexpr int value = KST_NDRAW_SIGEMAX;
+};
+template <>
+struct KstDraws<KstTpc> {
+    static constexpr int value = KST_NDRAW_TPC;
+};
+// (the dose-time-response family, r = 5, stays at one draw: two sets of 15 accumulators spill; measured -11 %)
+template <>
+struct KstDraws<KstVu> {
+    static constexpr int value = 2;
+};
+template <int C>
+struct KstDraws<KstLinLogReg<C>> {
+    static constexpr int value = 2;
+};
+template <>
+struct KstDraws<KstSinLogReg> {
+    static constexpr int value = 2;
 };

@@ -189,14 +189,16 @@ def _cond_scaled(M):
     return out
 
 
-def cond_max(model, mp, pts, w, theta, m=1, cov=None, sample=48, dt=None):
+def cond_max(model, mp, pts, w, theta, m=1, cov=None, sample=4096, dt=None):
     """Largest 2-norm condition number of the design's information matrix over a strided sample of the prior draws,
     from the extended-precision matrices, after scaling to unit diagonal (Cholesky-based log det / inverse are
     invariant under diagonal scaling, so this is the number their accuracy depends on; the raw matrices of the
     compartment models carry column scales like exp(-a t) that say nothing about the design).  With a DeltaMethod
     transformation (dt: (N, t, r) Jacobians) the criterion is taken on DT M^-1 DT', whose own scaled condition number
     counts as well: a dense DT mixes the widely different scales of M^-1 and the t x t matrix can be close to rank
-    one although M is harmless.  Inf when a matrix is not finite or has a non-positive diagonal entry."""
+    one although M is harmless.  Inf when a matrix is not finite or has a non-positive diagonal entry.
+    The sample covers every draw of the test-sized priors (<= 4096): one ill-conditioned draw can carry the whole
+    error of a prior-averaged A criterion (found by the fuzz test at a draw a 48-draw sample had missed)."""
     th = np.asarray(theta, dtype=np.float64)
     step = max(1, len(th) // sample)
     th = th[::step]
