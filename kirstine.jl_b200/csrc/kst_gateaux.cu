@@ -408,7 +408,12 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
     constexpr int MRR = MR > 0 ? MR : 1;
     extern __shared__ __align__(16) double smem[];
     __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
+#if KST_EXP_BIG && KST_TMA_TABLES
+    __shared__ __align__(8) unsigned long long s_mbar;
+    const KstTab tab = kst_math_init_async(s_mathtab, &s_mbar);  // waited for after the row set-up below
+#else
     const KstTab tab = kst_math_init(s_mathtab);  // visible after the first __syncthreads() of the chunk loop
+#endif
     double *s_draw = smem;                                  // [KST_GD_CHUNK][NSP]
     double *s_rows = smem + (size_t)NSP * KST_GD_CHUNK;     // [m][RW][KST_GD_NT]   (MR == 0 only)
     const int m = MR > 0 ? MR : mp.m;
@@ -454,6 +459,9 @@ __global__ void __launch_bounds__(KST_GD_NT) k_gateaux_eval(const double *__rest
         if (__syncthreads_or(sq != 0.0)) live_mask |= 1u << i;
     }
 
+#if KST_EXP_BIG && KST_TMA_TABLES
+    kst_math_wait(&s_mbar);  // (m >= 1: at least one CTA-wide barrier lies behind us)
+#endif
     // this CTA's draw range
     const int64_t per = (N + gridDim.y - 1) / gridDim.y;
     const int64_t j0 = per * blockIdx.y, j1 = min(N, j0 + per);

@@ -205,6 +205,82 @@ __device__ __forceinline__ void kst_build_tile(double *smem, const double *__res
     __syncthreads();
 }
 
+// kst_build_tile with the per-row work -- map_to_covariate!, the covariate-only
+// transcendentals, the square root of the row weight -- spread over one thread per (particle, row); one thread per
+// particle then compacts the rows in order and sums the weights in the reference's order, so the tile is the one
+// kst_build_tile builds, bit for bit.  pts / w: the tile's particles ([np][K][d], [np][K]); s_om / s_bd: scratch
+// of tile_p * K * m doubles each.  In the serial version the K * m logarithms of a sigmoid Emax particle are one
+// thread's dependent chain, which costs more than the evaluation itself on the reference's problem sizes.
+template <class MF>
+__device__ __forceinline__ void kst_build_tile_par(double *smem, const double *pts, const double *w, int np, int K,
+                                                   const KstModelParams &mp, int tile_p, const double *dcmax, double *s_om,
+                                                   double *s_bd)
+{
+    const int m = mp.m, rows_max = K * m;
+    constexpr int RW = KstTile<MF>::RW;
+    double *rows_all = KstTile<MF>::rows(smem);
+    for (int e = threadIdx.x; e < np * rows_max; e += KST_NT) {
+        const int i = e / rows_max, q = e % rows_max, k = q / m, u = q % m;
+        double pc[MF::NPC], varfac;
+        const bool trivial = MF::prep_row(pts + ((size_t)i * K + k) * mp.d, u, mp, pc, varfac);
+        const double om = w[(size_t)i * K + k] * varfac;
+        double sq = 0.0, bound = 0.0;
+        if (om != 0.0 && !trivial) {
+            sq = sqrt(om);
+            if (MF::FAST_EXP) bound = MF::arg_bound(pc, dcmax);
+            MF::post_row(pc, sq);
+        }
+        double *r = rows_all + ((size_t)i * rows_max + q) * RW;
+        r[0] = trivial ? -1.0 : sq;  // sq >= 0 for a live row; zero-weight rows are recognised by om == 0
+#pragma unroll
+        for (int c = 0; c < MF::NPC; c++) r[1 + c] = pc[c];
+        s_om[e] = om;
+        s_bd[e] = bound;
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < tile_p) {
+        const int i = threadIdx.x;
+        double *rows = rows_all + (size_t)i * rows_max * RW;
+        int na = 0, ntriv = 0;
+        double sw = 0.0, bound = 0.0;
+        if (i < np) {
+            for (int q = 0; q < rows_max; q++) {
+                const double om = s_om[i * rows_max + q];
+                sw += om;
+                if (om == 0.0) continue;
+                if (!(rows[q * RW] < 0.0)) {  // live row (a NaN weight stays a live row, as in kst_build_tile)
+                    bound = fmax(bound, s_bd[i * rows_max + q]);
+                    if (na != q) {
+#pragma unroll
+                        for (int c = 0; c < RW; c++) rows[na * RW + c] = rows[q * RW + c];
+                    }
+                    na++;
+                } else {
+                    ntriv++;
+                }
+            }
+        }
+        int rank = na + ((MF::CONST_COL >= 0 && ntriv > 0) ? 1 : 0);
+        if (MF::CONST_COL >= 0 && !(sw > 0.0 && sw < KST_INF)) rank = 0;
+        if (na == 0) {
+            double pc[MF::NPC], vf;
+            const double one = 1.0;
+            MF::prep_row(&one, 1, mp, pc, vf);
+            MF::post_row(pc, 0.0);
+            rows[0] = 0.0;
+#pragma unroll
+            for (int c = 0; c < MF::NPC; c++) rows[1 + c] = pc[c];
+            na = 1;
+        }
+        KstTile<MF>::sumw(smem, rows_max)[i] = sw;
+        KstTile<MF>::isumw(smem, rows_max)[i] = 1.0 / sw;
+        KstTile<MF>::nact(smem, rows_max)[i] = na;
+        KstTile<MF>::rank(smem, rows_max)[i] = rank;
+        KstTile<MF>::safe(smem, rows_max)[i] = (MF::FAST_EXP && dcmax && bound <= 700.0) ? 1 : 0;
+    }
+    __syncthreads();
+}
+
 // one row record (RW doubles at a 32-bit shared-space address) -> weighted row g
 template <class MF, bool CLAMP = true>
 __device__ __forceinline__ void kst_row_at(unsigned addr, const double *dcv, double *g, KstTab tab)
@@ -385,6 +461,7 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
     const double *__restrict__ pw = prm.pw;
     const double *__restrict__ dc = prm.dc;
     const unsigned ld = (unsigned)prm.ld;
+    constexpr bool PAIRS = KstDraws<MF>::value == 2 && !KstDense<MF>::value;
 
 #pragma unroll 1
     for (int p = 0; p < np; p++) {
@@ -410,11 +487,19 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
         } else {
             double run = 1.0;  // UNI: running product of determinants
             // software prefetch: the next draw's constants are requested before this draw's rows are evaluated
-            double dcn[MF::NDC], pwn = 0.0;
+            // (asking for the thread's first draws again at the end of a particle, so that the next particle starts
+            // without a load, measured no gain: +-0.2 %)
+            double dcn[MF::NDC], pwn = 0.0;   // next draw of the thread
+            double dcm[MF::NDC], pwm = 0.0;   // PAIRS: the pair's second draw
             if (j0 < n) {
 #pragma unroll
                 for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)j0));
                 pwn = __ldg(pw + j0);
+            }
+            if (PAIRS && j0 + stride < n) {
+#pragma unroll
+                for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)(j0 + stride)));
+                pwm = __ldg(pw + j0 + stride);
             }
             // the draw loop, compiled twice for the kernels worth it: with and without the exponent clamp inside exp
             auto draws = [&](auto clamp_tag, const int jstart) {
@@ -466,12 +551,6 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
             auto draws2 = [&](auto clamp_tag) -> int {
             constexpr bool CL = decltype(clamp_tag)::value;
             constexpr bool liveB = true;
-            double dcm[MF::NDC], pwm = 0.0;  // the pair's second draw, prefetched like the first
-            if (j0 + stride < n) {
-#pragma unroll
-                for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)(j0 + stride)));
-                pwm = __ldg(pw + j0 + stride);
-            }
             int j = j0;
             for (; j + stride < n; j += 2 * stride) {
                 double dcA[MF::NDC], dcB[MF::NDC];
@@ -534,7 +613,6 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
             return j;
             };
             // uniform over the warp: all lanes work on the same particle
-            constexpr bool PAIRS = KstDraws<MF>::value == 2 && !KstDense<MF>::value;
             if constexpr (PAIRS) {
                 if constexpr (DUAL) {
                     if (KstTile<MF>::safe(smem, rows_max)[p]) draws(KstFalse{}, draws2(KstFalse{}));
@@ -570,8 +648,18 @@ __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjPara
     extern __shared__ __align__(16) double smem[];
     __shared__ __align__(16) double s_mathtab[KST_MATH_SMEM];
     const int p0 = blockIdx.y * prm.tile_p;
+#if KST_EXP_BIG && KST_TMA_TABLES
+    // the math tables arrive by one asynchronous bulk copy while the CTA builds its particle tile
+    __shared__ __align__(8) unsigned long long s_mbar;
+    KstTab tab = kst_math_init_async(s_mathtab, &s_mbar);
+    // (one thread per particle: the per-row builder of the persistent swarm kernel, kst_build_tile_par, was measured
+    // here too: -0.6 % at 125 000 draws, +-0 at 10^6, +2 % on the mid-size configs)
+    kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp, prm.tile_p, prm.dcmax);  // ends with __syncthreads()
+    kst_math_wait(&s_mbar);
+#else
     KstTab tab = kst_math_init(s_mathtab);
     kst_build_tile<MF>(smem, prm.pts, prm.w, p0, prm.S, prm.K, prm.mp, prm.tile_p, prm.dcmax);  // ends with __syncthreads()
+#endif
     kst_objective_cta<MF, CRIT, T, UNI, REG>(prm, smem, tab, p0, (int)blockIdx.x, (int)gridDim.x, prm.partials);
 }
 

@@ -89,82 +89,6 @@ __host__ __device__ inline size_t kst_fused_tile_doubles(int rows_max)
     return (KstTile<MF>::bytes(rows_max) + 15) / 16 * 2;
 }
 
-// kst_build_tile (kst_objective_kernel.cuh) with the per-row work -- map_to_covariate!, the covariate-only
-// transcendentals, the square root of the row weight -- spread over one thread per (particle, row); one thread per
-// particle then compacts the rows in order and sums the weights in the reference's order, so the tile is the one
-// kst_build_tile builds, bit for bit.  pts / w: the tile's particles ([np][K][d], [np][K]); s_om / s_bd: scratch
-// of tile_p * K * m doubles each.  In the serial version the K * m logarithms of a sigmoid Emax particle are one
-// thread's dependent chain, which costs more than the evaluation itself on the reference's problem sizes.
-template <class MF>
-__device__ __forceinline__ void kst_build_tile_par(double *smem, const double *pts, const double *w, int np, int K,
-                                                   const KstModelParams &mp, int tile_p, const double *dcmax, double *s_om,
-                                                   double *s_bd)
-{
-    const int m = mp.m, rows_max = K * m;
-    constexpr int RW = KstTile<MF>::RW;
-    double *rows_all = KstTile<MF>::rows(smem);
-    for (int e = threadIdx.x; e < np * rows_max; e += KST_NT) {
-        const int i = e / rows_max, q = e % rows_max, k = q / m, u = q % m;
-        double pc[MF::NPC], varfac;
-        const bool trivial = MF::prep_row(pts + ((size_t)i * K + k) * mp.d, u, mp, pc, varfac);
-        const double om = w[(size_t)i * K + k] * varfac;
-        double sq = 0.0, bound = 0.0;
-        if (om != 0.0 && !trivial) {
-            sq = sqrt(om);
-            if (MF::FAST_EXP) bound = MF::arg_bound(pc, dcmax);
-            MF::post_row(pc, sq);
-        }
-        double *r = rows_all + ((size_t)i * rows_max + q) * RW;
-        r[0] = trivial ? -1.0 : sq;  // sq >= 0 for a live row; zero-weight rows are recognised by om == 0
-#pragma unroll
-        for (int c = 0; c < MF::NPC; c++) r[1 + c] = pc[c];
-        s_om[e] = om;
-        s_bd[e] = bound;
-    }
-    __syncthreads();
-    if ((int)threadIdx.x < tile_p) {
-        const int i = threadIdx.x;
-        double *rows = rows_all + (size_t)i * rows_max * RW;
-        int na = 0, ntriv = 0;
-        double sw = 0.0, bound = 0.0;
-        if (i < np) {
-            for (int q = 0; q < rows_max; q++) {
-                const double om = s_om[i * rows_max + q];
-                sw += om;
-                if (om == 0.0) continue;
-                if (!(rows[q * RW] < 0.0)) {  // live row (a NaN weight stays a live row, as in kst_build_tile)
-                    bound = fmax(bound, s_bd[i * rows_max + q]);
-                    if (na != q) {
-#pragma unroll
-                        for (int c = 0; c < RW; c++) rows[na * RW + c] = rows[q * RW + c];
-                    }
-                    na++;
-                } else {
-                    ntriv++;
-                }
-            }
-        }
-        int rank = na + ((MF::CONST_COL >= 0 && ntriv > 0) ? 1 : 0);
-        if (MF::CONST_COL >= 0 && !(sw > 0.0 && sw < KST_INF)) rank = 0;
-        if (na == 0) {
-            double pc[MF::NPC], vf;
-            const double one = 1.0;
-            MF::prep_row(&one, 1, mp, pc, vf);
-            MF::post_row(pc, 0.0);
-            rows[0] = 0.0;
-#pragma unroll
-            for (int c = 0; c < MF::NPC; c++) rows[1 + c] = pc[c];
-            na = 1;
-        }
-        KstTile<MF>::sumw(smem, rows_max)[i] = sw;
-        KstTile<MF>::isumw(smem, rows_max)[i] = 1.0 / sw;
-        KstTile<MF>::nact(smem, rows_max)[i] = na;
-        KstTile<MF>::rank(smem, rows_max)[i] = rank;
-        KstTile<MF>::safe(smem, rows_max)[i] = (MF::FAST_EXP && dcmax && bound <= 700.0) ? 1 : 0;
-    }
-    __syncthreads();
-}
-
 // number of doubles of the packed state snapshot (KstFusedParams::snap)
 __host__ __device__ inline size_t kst_snapshot_doubles(int S, int K, int d)
 {
