@@ -2,6 +2,10 @@
 // Included by kst_objective.cu (host entry points, small kernels) and by the kst_obj_inst_*.cu files, each of
 // which instantiates kst_obj_launch for some model families so that the families compile in parallel.
 #pragma once
+#ifndef KST_DRAW_OUTER
+#define KST_DRAW_OUTER 1     // 1: a thread takes a pair of draws through ALL particles of the tile before moving on
+                             // (per-particle sums in shared memory); 0: particle by particle, draws inside
+#endif
 #ifndef KST_ROWS_OVERRIDE
 #define KST_ROWS_OVERRIDE 0  // tuning: force the row interleave factor (1, 2, 4, 8) for every family
 #endif
@@ -57,9 +61,15 @@ struct KstTile {
                (sizeof(int) * 3 * KST_TILE_P + 15) / 16 * 2;
     }
     __device__ static double *lmat(double *s, int rows_max) { return s + base_doubles(rows_max); }
+    // per-thread accumulators of the draw-outer evaluation loop: sum and running determinant product of every particle
+    // of the tile, [2][KST_TILE_P][KST_NT] doubles behind everything else
+    __host__ __device__ static size_t acc_offset(int rows_max)
+    {
+        return base_doubles(rows_max) + (KstDense<MF>::value ? (size_t)KST_TILE_P * rows_max * LW : 0);
+    }
     __host__ __device__ static size_t bytes(int rows_max)
     {
-        return sizeof(double) * (base_doubles(rows_max) + (KstDense<MF>::value ? (size_t)KST_TILE_P * rows_max * LW : 0));
+        return sizeof(double) * (acc_offset(rows_max) + (KST_DRAW_OUTER ? 2 * (size_t)KST_TILE_P * KST_NT : 0));
     }
 };
 
@@ -420,6 +430,8 @@ __device__ __forceinline__ void kst_fisher(double *M, unsigned rows_addr, int na
     if (MF::CONST_COL >= 0) M[kst_pidx<R>(cc, cc)] = sw;
 }
 
+template <int V>
+struct KstInt { static constexpr int value = V; };
 struct KstTrue { static constexpr bool value = true; };
 struct KstFalse { static constexpr bool value = false; };
 
@@ -442,6 +454,194 @@ struct KstFalse { static constexpr bool value = false; };
 // very same code on a tile it keeps in shared memory: the particle tile of CTA (bx, p0 / tile_p) has been built in
 // `smem` (kst_build_tile), `tab` are the staged math tables; the CTA's partial sums for its particles go to
 // partials[bx * S + p0 + i].
+#if KST_DRAW_OUTER
+// Loop order: DRAWS OUTSIDE, PARTICLES INSIDE.  A thread takes its draws in pairs (j, j + stride) -- one draw at a time
+// for the families without the two-draw row pass, and for an odd last draw -- and carries each pair through every
+// particle of the tile before it moves to the next pair: the draw's constants are fetched once per pair instead of
+// once per (particle, pair), the prefetch, loop and pipeline start-up of a draw loop are paid once per tile instead
+// of once per particle, and there is no reduction (with its dependent shuffles and logarithm) between particles.
+// The price: the per-particle running sum and determinant product live in per-thread shared-memory slots
+// (sacc / srun [particle][thread], conflict free) instead of registers: one load and one store per (particle, pair).
+// Every thread still adds its draws of a particle in ascending order and the cross-thread reduction is unchanged, so
+// the results are bit for bit those of the particle-outer order.
+template <class MF, int CRIT, int T, bool UNI, bool REG>
+__device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, double *smem, KstTab tab, const int p0,
+                                                  const int bx, const int nbx, double *__restrict__ partials)
+{
+    constexpr int R = MF::R, RW = KstTile<MF>::RW;
+    const int rows_max = prm.K * prm.mp.m;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int np = min(prm.tile_p, prm.S - p0);
+    double *wsum = KstTile<MF>::wsum(smem, rows_max);
+    const int n = (int)prm.N, stride = nbx * KST_NT, j0 = bx * KST_NT + (int)threadIdx.x;
+    unsigned rows_base = (unsigned)__cvta_generic_to_shared(KstTile<MF>::rows(smem));
+    unsigned lbase = KstDense<MF>::value ? (unsigned)__cvta_generic_to_shared(KstTile<MF>::lmat(smem, rows_max)) : 0u;
+    // shared-space bases opaque to the compiler (see kst_math.cuh: otherwise rebuilt from SR_CgaCtaId before every use)
+    asm volatile("" : "+r"(tab), "+r"(rows_base));
+    const double *__restrict__ pw = prm.pw;
+    const double *__restrict__ dc = prm.dc;
+    const unsigned ld = (unsigned)prm.ld;
+    constexpr bool INV0 = MF::CONST_COL == 0 && !REG;  // 1 / first pivot hoisted per particle
+    constexpr bool DUAL = MF::FAST_EXP && UNI;          // unclamped copy of the row code only where it pays
+    constexpr bool PAIRS = KstDraws<MF>::value == 2 && !KstDense<MF>::value;
+    const int *s_na = KstTile<MF>::nact(smem, rows_max), *s_rank = KstTile<MF>::rank(smem, rows_max);
+    const int *s_safe = KstTile<MF>::safe(smem, rows_max);
+    const double *s_sw = KstTile<MF>::sumw(smem, rows_max), *s_isw = KstTile<MF>::isumw(smem, rows_max);
+    double *sacc = smem + KstTile<MF>::acc_offset(rows_max) + threadIdx.x;   // [p * KST_NT]
+    double *srun = sacc + KST_TILE_P * KST_NT;
+    for (int p = 0; p < np; p++) {
+        sacc[p * KST_NT] = 0.0;
+        if (UNI) srun[p * KST_NT] = 1.0;
+    }
+
+    // one particle, one draw (ND = 1) or one pair of draws (ND = 2): Mt, criterion, the thread's running sums
+    auto eval = [&](auto clamp_tag, auto nd_tag, const int p, const int jA, const int jB, const double *dcA,
+                    const double *dcB, const double pwA, const double pwB) {
+        constexpr bool CL = decltype(clamp_tag)::value;
+        constexpr int ND = decltype(nd_tag)::value;
+        const unsigned rows_addr = rows_base + (unsigned)(p * rows_max * RW * 8);
+        const int na = s_na[p];
+        const double sw = s_sw[p], inv0 = s_isw[p];
+        double MA[KstPacked<R>::N], MB[KstPacked<R>::N];
+        if constexpr (ND == 2) {
+            kst_fisher2<MF, CL>(MA, MB, rows_addr, na, sw, dcA, dcB, tab);
+        } else {
+            kst_fisher<MF, CL>(MA, rows_addr, na, sw, dcA, tab, lbase + (unsigned)(p * rows_max * KstTile<MF>::LW * 8), prm.mp.m);
+        }
+        if (REG) {
+#pragma unroll
+            for (int i = 0; i < KstPacked<R>::N; i++) {
+                MA[i] += __ldg(prm.reg + ((size_t)i * ld + (size_t)jA));
+                if (ND == 2) MB[i] += __ldg(prm.reg + ((size_t)i * ld + (size_t)jB));
+            }
+        }
+        double acc = sacc[p * KST_NT];
+        if (CRIT == KST_KCRIT_GD) {
+            double qA = 0.0, qB = 0.0;
+#pragma unroll
+            for (int i = 0; i < KstPacked<R>::N; i++) {
+                qA = fma(__ldg(prm.aux + ((size_t)i * ld + (size_t)jA)), MA[i], qA);
+                if (ND == 2) qB = fma(__ldg(prm.aux + ((size_t)i * ld + (size_t)jB)), MB[i], qB);
+            }
+            acc += qA;
+            if (ND == 2) acc += qB;
+            sacc[p * KST_NT] = acc;
+        } else if (UNI) {
+            double detA, detB = 1.0;
+            int signsA, signsB = 0;
+            kst_det_signs<R, INV0>(MA, inv0, detA, signsA);
+            if (ND == 2) kst_det_signs<R, INV0>(MB, inv0, detB, signsB);
+            const double run = srun[p * KST_NT];
+            const double pn = ND == 2 ? run * detA * detB : run * detA;
+            const unsigned key = ((unsigned)(signsA | signsB) & 0x80000000u) | (unsigned)__double2hiint(pn);
+            if (((key >> 20) - 423u) < 1200u) {
+                srun[p * KST_NT] = pn;
+            } else {
+                acc += kst_log(run, tab) + kst_log_checked(detA, signsA, tab);
+                if (ND == 2) acc += kst_log_checked(detB, signsB, tab);
+                sacc[p * KST_NT] = acc;
+                srun[p * KST_NT] = 1.0;
+            }
+        } else {
+            bool excA, excB = false;
+            const double vA = kst_criterion<R, (CRIT == KST_KCRIT_GD ? 0 : CRIT), T, INV0>(MA, prm.aux + jA, prm.ld, excA, inv0, tab);
+            acc += excA ? -KST_INF : pwA * vA;
+            if (ND == 2) {
+                const double vB = kst_criterion<R, (CRIT == KST_KCRIT_GD ? 0 : CRIT), T, INV0>(MB, prm.aux + jB, prm.ld, excB, inv0, tab);
+                acc += excB ? -KST_INF : pwB * vB;
+            }
+            sacc[p * KST_NT] = acc;
+        }
+    };
+    // all particles of the tile for one draw / one pair (uniform over the warp: all lanes work on the same particle)
+    auto tile = [&](auto nd_tag, const int jA, const int jB, const double *dcA, const double *dcB, const double pwA,
+                    const double pwB) {
+        constexpr int ND = decltype(nd_tag)::value;
+#pragma unroll 1
+        for (int p = 0; p < np; p++) {
+            if (!REG && CRIT != KST_KCRIT_GD && s_rank[p] < R) {
+                // fewer live rows than parameters: singular by construction (one-point designs etc.).  The reference
+                // reaches the same -Inf through an exactly zero pivot: weighted by the prior weight for log_det!
+                // (0 * -Inf = NaN, as there), unweighted where it throws.  (Dexp: exp(-Inf / t) = 0 for such a draw.)
+                double acc = sacc[p * KST_NT];
+                acc += T != 0 ? -KST_INF : (CRIT == 0 ? pwA * -KST_INF : (CRIT == 2 ? pwA * 0.0 : -KST_INF));
+                if (ND == 2) acc += T != 0 ? -KST_INF : (CRIT == 0 ? pwB * -KST_INF : (CRIT == 2 ? pwB * 0.0 : -KST_INF));
+                sacc[p * KST_NT] = acc;
+                continue;
+            }
+            if (DUAL && s_safe[p]) eval(KstFalse{}, nd_tag, p, jA, jB, dcA, dcB, pwA, pwB);
+            else eval(KstTrue{}, nd_tag, p, jA, jB, dcA, dcB, pwA, pwB);
+        }
+    };
+
+    // software prefetch: the next draws' constants are requested before the current ones go through the tile
+    double dcn[MF::NDC], pwn = 0.0, dcm[MF::NDC], pwm = 0.0;
+    if (j0 < n) {
+#pragma unroll
+        for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)j0));
+        pwn = __ldg(pw + j0);
+    }
+    int j = j0;
+    if constexpr (PAIRS) {
+        if (j0 + stride < n) {
+#pragma unroll
+            for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)(j0 + stride)));
+            pwm = __ldg(pw + j0 + stride);
+        }
+#pragma unroll 1
+        for (; j + stride < n; j += 2 * stride) {
+            double dcA[MF::NDC], dcB[MF::NDC];
+#pragma unroll
+            for (int c = 0; c < MF::NDC; c++) { dcA[c] = dcn[c]; dcB[c] = dcm[c]; }
+            const double pwA = pwn, pwB = pwm;
+            const int jn = j + 2 * stride;
+            if (jn < n) {
+#pragma unroll
+                for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
+                pwn = __ldg(pw + jn);
+                if (jn + stride < n) {
+#pragma unroll
+                    for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)(jn + stride)));
+                    pwm = __ldg(pw + jn + stride);
+                }
+            }
+            tile(KstInt<2>{}, j, j + stride, dcA, dcB, pwA, pwB);
+        }
+    }
+    // one draw at a time: everything for the families without pairs, else at most the odd last draw
+#pragma unroll 1
+    for (; j < n; j += stride) {
+        double dcA[MF::NDC];
+#pragma unroll
+        for (int c = 0; c < MF::NDC; c++) dcA[c] = dcn[c];
+        const double pwA = pwn;
+        const int jn = j + stride;
+        if (jn < n) {
+#pragma unroll
+            for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
+            pwn = __ldg(pw + jn);
+        }
+        tile(KstInt<1>{}, j, j, dcA, dcA, pwA, pwA);
+    }
+
+    // per particle: the thread's sum, then the fixed-order reduction over the CTA's draws
+#pragma unroll 1
+    for (int p = 0; p < np; p++) {
+        double acc = sacc[p * KST_NT];
+        if (UNI && (REG || CRIT == KST_KCRIT_GD || s_rank[p] >= R)) acc = prm.w_uniform * (acc + kst_log(srun[p * KST_NT], tab));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+        if (lane == 0) wsum[p * (KST_NT / 32) + warp] = acc;
+    }
+    __syncthreads();
+    if (threadIdx.x < np) {
+        double s = 0.0;
+#pragma unroll
+        for (int wi = 0; wi < KST_NT / 32; wi++) s += wsum[threadIdx.x * (KST_NT / 32) + wi];
+        partials[(size_t)bx * prm.S + (p0 + threadIdx.x)] = s;  // [nbx][S]: whoever finishes the sums reads coalesced
+    }
+}
+#else
 template <class MF, int CRIT, int T, bool UNI, bool REG>
 __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, double *smem, KstTab tab, const int p0,
                                                   const int bx, const int nbx, double *__restrict__ partials)
@@ -641,6 +841,8 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
         partials[(size_t)bx * prm.S + (p0 + threadIdx.x)] = s;  // [nbx][S]: whoever finishes the sums reads coalesced
     }
 }
+
+#endif
 
 template <class MF, int CRIT, int T, bool UNI, bool REG = false>
 __global__ void __launch_bounds__(KST_NT, KST_MINB) k_objective(const KstObjParams prm)
