@@ -579,14 +579,14 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
     if (j0 < n) {
 #pragma unroll
         for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)j0));
-        pwn = __ldg(pw + j0);
+        pwn = UNI ? prm.w_uniform : __ldg(pw + j0);  // (uniform weights: the array is never read)
     }
     int j = j0;
     if constexpr (PAIRS) {
         if (j0 + stride < n) {
 #pragma unroll
             for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)(j0 + stride)));
-            pwm = __ldg(pw + j0 + stride);
+            pwm = UNI ? prm.w_uniform : __ldg(pw + j0 + stride);
         }
 #pragma unroll 1
         for (; j + stride < n; j += 2 * stride) {
@@ -598,11 +598,11 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
             if (jn < n) {
 #pragma unroll
                 for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
-                pwn = __ldg(pw + jn);
+                pwn = UNI ? prm.w_uniform : __ldg(pw + jn);
                 if (jn + stride < n) {
 #pragma unroll
                     for (int c = 0; c < MF::NDC; c++) dcm[c] = __ldg(dc + (size_t)(c * ld + (unsigned)(jn + stride)));
-                    pwm = __ldg(pw + jn + stride);
+                    pwm = UNI ? prm.w_uniform : __ldg(pw + jn + stride);
                 }
             }
             tile(KstInt<2>{}, j, j + stride, dcA, dcB, pwA, pwB);
@@ -619,7 +619,7 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
         if (jn < n) {
 #pragma unroll
             for (int c = 0; c < MF::NDC; c++) dcn[c] = __ldg(dc + (size_t)(c * ld + (unsigned)jn));
-            pwn = __ldg(pw + jn);
+            pwn = UNI ? prm.w_uniform : __ldg(pw + jn);
         }
         tile(KstInt<1>{}, j, j, dcA, dcA, pwA, pwA);
     }
