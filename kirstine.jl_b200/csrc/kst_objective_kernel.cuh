@@ -624,14 +624,17 @@ __device__ __forceinline__ void kst_objective_cta(const KstObjParams &prm, doubl
         tile(KstInt<1>{}, j, j, dcA, dcA, pwA, pwA);
     }
 
-    // per particle: the thread's sum, then the fixed-order reduction over the CTA's draws
-#pragma unroll 1
-    for (int p = 0; p < np; p++) {
-        double acc = sacc[p * KST_NT];
-        if (UNI && (REG || CRIT == KST_KCRIT_GD || s_rank[p] >= R)) acc = prm.w_uniform * (acc + kst_log(srun[p * KST_NT], tab));
+    // per particle: the thread's sum, then the fixed-order reduction over the CTA's draws (unrolled over the tile's
+    // particles: their log + shuffle chains are independent and overlap)
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
-        if (lane == 0) wsum[p * (KST_NT / 32) + warp] = acc;
+    for (int p = 0; p < KST_TILE_P; p++) {
+        if (p < np) {
+            double acc = sacc[p * KST_NT];
+            if (UNI && (REG || CRIT == KST_KCRIT_GD || s_rank[p] >= R)) acc = prm.w_uniform * (acc + kst_log(srun[p * KST_NT], tab));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+            if (lane == 0) wsum[p * (KST_NT / 32) + warp] = acc;
+        }
     }
     __syncthreads();
     if (threadIdx.x < np) {

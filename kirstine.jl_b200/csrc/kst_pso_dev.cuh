@@ -176,10 +176,13 @@ __device__ __forceinline__ void kst_pso_best_cta(const KstPsoDev &s, int init, d
                                                  int slot, int *status, const double *__restrict__ partials,
                                                  int n_blk, double offset, int nan_fill)
 {
-    __shared__ double s_val[1024];
-    __shared__ int s_idx[1024];
+    __shared__ double s_val[32];
+    __shared__ int s_idx[32];
     __shared__ int s_notnan;
     const int K = s.K, d = s.d, tid = threadIdx.x;
+    // requested first, needed last: the best objective so far
+    double fg_old = -KST_DINF;
+    if (tid == 0 && !init) fg_old = *s.fg;
     if (tid == 0) s_notnan = 0;
     __syncthreads();
     double best = -KST_DINF;
@@ -190,7 +193,8 @@ __device__ __forceinline__ void kst_pso_best_cta(const KstPsoDev &s, int init, d
         double f;
         if (partials) {
             double acc = 0.0;
-            for (int b = 0; b < n_blk; b++) acc += partials[(size_t)b * s.S + i];
+#pragma unroll 8
+            for (int b = 0; b < n_blk; b++) acc += partials[(size_t)b * s.S + i];  // eight loads in flight, added in order
             f = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : acc + offset;
             s.fx[i] = f;
         } else {
@@ -210,23 +214,35 @@ __device__ __forceinline__ void kst_pso_best_cta(const KstPsoDev &s, int init, d
         }
     }
     if (notnan) atomicOr(&s_notnan, 1);
-    s_val[tid] = best;
-    s_idx[tid] = have ? bidx : -1;
-    __syncthreads();
-    for (int o = blockDim.x / 2; o > 0; o >>= 1) {
-        if (tid < o) {
-            const int ia = s_idx[tid], ib = s_idx[tid + o];
-            const double va = s_val[tid], vb = s_val[tid + o];
-            const bool take_b = ib >= 0 && (ia < 0 || vb > va || (vb == va && ib < ia));
-            if (take_b) { s_val[tid] = vb; s_idx[tid] = ib; }
-        }
-        __syncthreads();
+    // arg-max over the CTA (any multiple of 32 threads): the largest value, the lowest index among equals; -1 = none
+    int bi = have ? bidx : -1;
+    auto merge = [](double &va, int &ia, const double vb, const int ib) {
+        if (ib >= 0 && (ia < 0 || vb > va || (vb == va && ib < ia))) { va = vb; ia = ib; }
+    };
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double vb = __shfl_down_sync(0xffffffffu, best, o);
+        const int ib = __shfl_down_sync(0xffffffffu, bi, o);
+        merge(best, bi, vb, ib);
     }
-    const int gi = s_idx[0];
-    const double gv = s_val[0];
-    __shared__ int s_update;
+    if ((tid & 31) == 0) { s_val[tid >> 5] = best; s_idx[tid >> 5] = bi; }
+    __syncthreads();
+    __shared__ int s_update, s_gi;
+    if (tid < 32) {
+        const int nw = (blockDim.x + 31) >> 5;
+        best = tid < nw ? s_val[tid] : -KST_DINF;
+        bi = tid < nw ? s_idx[tid] : -1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double vb = __shfl_down_sync(0xffffffffu, best, o);
+            const int ib = __shfl_down_sync(0xffffffffu, bi, o);
+            merge(best, bi, vb, ib);
+        }
+    }
     if (tid == 0) {
-        const double fg_old = init ? (-KST_DINF) : *s.fg;
+        const int gi = bi;
+        const double gv = best;
+        s_gi = gi;
         s_update = (gi >= 0 && gv > fg_old) ? 1 : 0;
         const double fg_new = s_update ? gv : fg_old;
         *s.fg = fg_new;
@@ -238,16 +254,24 @@ __device__ __forceinline__ void kst_pso_best_cta(const KstPsoDev &s, int init, d
         }
     }
     __syncthreads();
-    if (s_update) {
-        const double *xp = s.x_pts + (size_t)gi * K * d, *xw = s.x_w + (size_t)gi * K;
-        for (int c = tid; c < K * d; c += blockDim.x) s.g_pts[c] = xp[c];
-        for (int k = tid; k < K; k += blockDim.x) s.g_w[k] = xw[k];
+    // the global best moves to the winner's position (or stays); the trace entry is written from the same registers
+    const int upd = s_update, gi = s_gi;
+    if (upd || tr_pts) {
+        const double *xp = s.x_pts + (size_t)(upd ? gi : 0) * K * d;
+        for (int c = tid; c < K * d; c += blockDim.x) {
+            const double v = upd ? xp[c] : s.g_pts[c];
+            if (upd) s.g_pts[c] = v;
+            if (tr_pts) tr_pts[(size_t)slot * K * d + c] = v;
+        }
     }
-    __syncthreads();
-    if (tr_pts)
-        for (int c = tid; c < K * d; c += blockDim.x) tr_pts[(size_t)slot * K * d + c] = s.g_pts[c];
-    if (tr_w)
-        for (int k = tid; k < K; k += blockDim.x) tr_w[(size_t)slot * K + k] = s.g_w[k];
+    if (upd || tr_w) {
+        const double *xw = s.x_w + (size_t)(upd ? gi : 0) * K;
+        for (int k = tid; k < K; k += blockDim.x) {
+            const double v = upd ? xw[k] : s.g_w[k];
+            if (upd) s.g_w[k] = v;
+            if (tr_w) tr_w[(size_t)slot * K + k] = v;
+        }
+    }
     if (status && tid == 0 && *status == 0 && !s_notnan) *status = 2;
     __syncthreads();
 }
