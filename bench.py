@@ -408,6 +408,7 @@ def main():
     h.profile_enable(False)
     st_after = h.pso_state()  # device -> host read of the step's result (best objective so far)
     assert st_after["fg"] >= fg_before and st_after["n_eval"] == S * (1 + args.warmup + args.steps)
+    ms_local = ms
     ms = max_over_ranks(ms)
     units_per_step = float(S) * float(n_total)
     value = units_per_step * args.steps / (ms * 1e-3)
@@ -487,6 +488,15 @@ def main():
                 "note": "served from L2 (shard <= 24 MB); HBM is not the bound"},
     }
 
+    # every rank's own numbers (N > 1): step time between its events and the evaluation kernel inside it.  The step
+    # ends with an exchange, so a rank that starts late or runs the kernel slower shows up in everybody's step time.
+    per_rank = None
+    if world > 1:
+        mine = torch.tensor([ms_local / args.steps, kern_avg_ms], dtype=torch.float64, device="cuda")
+        everyone = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(everyone, mine)
+        per_rank = {"step_ms": [float(t[0]) for t in everyone], "kernel_ms": [float(t[1]) for t in everyone]}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -531,6 +541,7 @@ def main():
         # kernel, not counted)
         "gpu_launches": int((4 if collective == "nccl" else 3) * args.steps),
         "roofline": roofline,
+        "per_rank": per_rank,
         "cpu_baseline": cpu,
         "parity_check": parity,
         "configs": configs,

@@ -147,7 +147,8 @@ __device__ __forceinline__ void kst_peer_allreduce_cta(double *buf, int count, c
         double v;
         if (partials) {
             double s = 0.0;
-            for (int b = 0; b < n_blk; b++) s += partials[(size_t)b * count + i];
+#pragma unroll 8
+            for (int b = 0; b < n_blk; b++) s += partials[(size_t)b * count + i];  // eight loads in flight, added in order
             v = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : s + offset;
         } else {
             v = buf[i];

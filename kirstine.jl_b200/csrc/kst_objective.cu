@@ -81,6 +81,7 @@ __global__ void k_obj_finish(const double *__restrict__ partials, int n_blk, dou
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= S) return;
     double s = 0.0;
+#pragma unroll 8
     for (int b = 0; b < n_blk; b++) s += partials[(size_t)b * S + p];
     fx[p] = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : s + offset;
 }
