@@ -72,17 +72,33 @@ __global__ void k_pso_init(KstPsoDev s, const double *__restrict__ proto_pts, co
     }
 }
 
-// velocity + constrained move, one thread per particle (kst_pso_move_particle, kst_pso_dev.cuh), in place in global
-// memory.  (Staging x, v and the personal best in shared memory first was measured: 24.5 us against 17.5 us for 1024
-// particles with cold caches -- the in-place accesses hit L1, the extra copy in and out does not pay.)
-__global__ void k_pso_move(KstPsoDev s, uint32_t iter, double c1, double c2, double chi)
+// velocity + constrained move.  A CTA takes `ppb` particles: one thread per (particle, component) draws the two random
+// numbers and updates the velocity (kst_pso_velocity; components are independent), then one thread per particle does
+// the constrained move, whose sums run in the reference's order (kst_pso_position) -- the same split as in the
+// persistent swarm kernel.  In place in global memory.  (One thread per particle for everything: 17.5 us for 1024
+// particles x 16 components with cold caches, two thirds of it the sixteen Philox blocks and velocities in series.
+// Staging x, v and the personal best in shared memory first was measured too: 24.5 us.)
+#define KST_MOVE_NT 128
+__global__ void __launch_bounds__(KST_MOVE_NT) k_pso_move(KstPsoDev s, uint32_t iter, double c1, double c2, double chi, int ppb)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= s.S) return;
-    const int K = s.K, d = s.d;
-    kst_pso_move_particle(K, d, s.x_w + (size_t)i * K, s.x_pts + (size_t)i * K * d, s.p_w + (size_t)i * K,
-                          s.p_pts + (size_t)i * K * d, s.v_w + (size_t)i * K, s.v_pts + (size_t)i * K * d, s.g_w, s.g_pts,
-                          s.fixw, s.fixp, s.lb, s.ub, c1, c2, chi, KstRndPhilox{s.seed, iter, (uint32_t)i});
+    const int K = s.K, d = s.d, KD = K * d, KC = K + KD;
+    const int i0 = blockIdx.x * ppb, np = min(ppb, s.S - i0);
+    for (int e = threadIdx.x; e < np * KC; e += KST_MOVE_NT) {
+        const int i = i0 + e / KC, c = e % KC;
+        double r1, r2;
+        kst_uniform2(s.seed, iter, (uint32_t)i, (uint32_t)c, 0, r1, r2);
+        const bool isw = c < K;
+        const size_t o = isw ? (size_t)i * K + c : (size_t)i * KD + (c - K);
+        double *v = isw ? s.v_w + o : s.v_pts + o;
+        *v = kst_pso_velocity(*v, isw ? s.x_w[o] : s.x_pts[o], isw ? s.p_w[o] : s.p_pts[o], isw ? s.g_w[c] : s.g_pts[c - K],
+                              r1, r2, c1, c2, chi);
+    }
+    __syncthreads();  // the velocities were written by this CTA's own threads
+    if ((int)threadIdx.x < np) {
+        const int i = i0 + threadIdx.x;
+        kst_pso_position(K, d, s.x_w + (size_t)i * K, s.x_pts + (size_t)i * KD, s.v_w + (size_t)i * K,
+                         s.v_pts + (size_t)i * KD, s.fixw, s.fixp, s.lb, s.ub);
+    }
 }
 
 // pso_update_best! as a kernel of its own (kst_pso_best_cta, kst_pso_dev.cuh)
@@ -218,7 +234,9 @@ int kst_launch_pso_move(kst_problem *h)
     const KstPsoDev s = make_dev(h);
     const double phi = h->pso.c1 + h->pso.c2;
     const double chi = 2 / fabs(2 - phi - sqrt(phi * phi - 4 * phi));  // src/pso.jl:134-135
-    k_pso_move<<<(s.S + 127) / 128, 128, 0, h->stream>>>(s, (uint32_t)h->pso.iter, h->pso.c1, h->pso.c2, chi);
+    const int kc = s.K * (s.d + 1);
+    const int ppb = kc >= KST_MOVE_NT ? 1 : KST_MOVE_NT / kc;  // particles per CTA: one thread per component where they fit
+    k_pso_move<<<(s.S + ppb - 1) / ppb, KST_MOVE_NT, 0, h->stream>>>(s, (uint32_t)h->pso.iter, h->pso.c1, h->pso.c2, chi, ppb);
     KST_CUDA(cudaGetLastError());
     return KST_OK;
 }
