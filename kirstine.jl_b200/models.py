@@ -1,5 +1,5 @@
 """Registered model families, their parameter types and covariate parameterizations (host side of
-csrc/kst_models.cuh); part of the API mirror described in api.py."""
+csrc/kst_models.cuh); part of the API mirror described in the package docstring (__init__.py)."""
 from collections import namedtuple
 
 import numpy as np

@@ -1,5 +1,5 @@
 """Criteria, transformations, normal approximations, prior samples, the design problem and its public evaluators
-(objective, gateauxderivative, efficiency, ...); part of the API mirror described in api.py."""
+(objective, gateauxderivative, efficiency, ...); part of the API mirror described in the package docstring (__init__.py)."""
 import math
 import warnings
 

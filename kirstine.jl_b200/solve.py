@@ -1,5 +1,5 @@
 """Optimizer (device-resident PSO), problem solving strategies and their results; part of the API mirror described
-in api.py."""
+in the package docstring (__init__.py)."""
 import math
 import time
 import warnings
