@@ -309,6 +309,10 @@ def main():
     ap.add_argument("--swarm", type=int, default=SWARM)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-configs", action="store_true", help="skip the `configs` array (the other BASELINE configs)")
+    ap.add_argument("--stage", type=int, default=1, choices=[1, 2, 3],
+                    help="which launch of the PSO step the engine's own events time (1 = evaluation kernel, the default "
+                         "the roofline needs; 2 = move, 3 = best update / multi-GPU tail: for the split of a step in "
+                         "profiles/, the roofline keys of such a run are meaningless)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -400,7 +404,7 @@ def main():
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    h.profile_enable(True)
+    h.profile_enable(args.stage)
     barrier()
     ms = timed_steps(lambda: h.pso_run_async(1), args.steps)
     barrier()
@@ -542,6 +546,7 @@ def main():
         "gpu_launches": int((4 if collective == "nccl" else 3) * args.steps),
         "roofline": roofline,
         "per_rank": per_rank,
+        "stage_timed": {1: "evaluation kernel", 2: "k_pso_move", 3: "k_pso_best / k_pso_tail"}[args.stage],
         "cpu_baseline": cpu,
         "parity_check": parity,
         "configs": configs,

@@ -316,8 +316,10 @@ KST_API int kst_exchange_run(kst_problem *h, const kst_exchange_options *opt, in
                              double *dir_trace_fx, double *dir_trace_x, double *w_trace_fx, double *w_trace_points,
                              double *w_trace_weights, int *w_K, double *dir_state0, double *w_state0, int *steps_done);
 
-/* measurement helpers (bench.py): CUDA-event timing of the evaluation kernel on the handle's
- * stream, and a DFMA micro-kernel that measures this GPU's FP64 pipe peak. */
+/* measurement helpers (bench.py): CUDA-event timing of one stage on the handle's stream -- on = 1 the evaluation
+ * kernel (k_objective / k_gateaux_eval), 2 the swarm move, 3 the best update (on several GPUs: the tail kernel with
+ * the peer exchange), 0 off; kst_profile_read returns the summed time and the number of launches since the last
+ * read -- and a DFMA micro-kernel that measures this GPU's FP64 pipe peak. */
 KST_API int kst_profile_enable(kst_problem *h, int on);
 KST_API int kst_profile_read(kst_problem *h, double *total_ms, int64_t *launches);
 KST_API int kst_fp64_peak_probe(int device_id, double *tflops);

@@ -661,7 +661,8 @@ extern "C" int kst_pso_get_state(kst_problem *h, double *x_points, double *x_wei
 extern "C" int kst_profile_enable(kst_problem *h, int on)
 {
     KST_CHECK_HANDLE(h);
-    h->prof_on = on != 0;
+    if (on < 0 || on > 3) { kst_set_error("profile_enable: stage must be 0 (off), 1 (evaluation), 2 (move) or 3 (best / tail)"); return KST_EINVAL; }
+    h->prof_on = on;
     return KST_OK;
 }
 

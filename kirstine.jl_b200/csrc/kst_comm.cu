@@ -101,7 +101,9 @@ extern "C" int kst_comm_init(kst_problem *h, int nranks, int rank, const void *i
 //   publish this rank's vector in its exchange block -> release flag -> wait for every peer's flag ->
 //   sum all vectors in RANK ORDER (P2P loads), so every rank ends with identical bits.
 // Replaces ncclAllReduce for the S partial objectives of a swarm evaluation (8 KB at S = 1024): one launch,
-// a few microseconds of NVLink latency, no proxy thread.  Two buffers alternate by sequence parity: a rank can
+// a few microseconds of NVLink latency, no proxy thread.  (A push version -- every rank writes its vector into its slot
+// of every peer's block, one system fence, flags, local polling and local loads -- was measured on two GPUs and is not
+// faster: the tail kernel takes 34 ... 43 us either way, 20 us of which are the finish and the best update.)  Two buffers alternate by sequence parity: a rank can
 // only reach collective n + 2 after every peer has published n + 1, i.e. finished reading n.
 // The flags carry the sequence number, so nothing has to be reset between calls.  A peer that never shows up
 // trips a 10 s timeout (error word set, result NaN) instead of hanging the GPU.
@@ -225,11 +227,13 @@ int kst_launch_pso_tail(kst_problem *h, int trace_slot, int n_blk, double offset
     kst_pso_make_dev(h, &s);
     KstPeerPtrs pp;
     for (int r = 0; r < KST_PEER_MAX; r++) pp.blk[r] = (KstPeerBlock *)h->peer_map[r];
+    const int rcp = kst_prof_begin(h, KST_PROF_BEST);
+    if (rcp) return rcp;
     k_pso_tail<<<1, 1024, 0, h->stream>>>(s, pp, h->nranks, h->rank, ++h->peer_seq, h->partials, n_blk, offset, nan_fill,
                                            trace_slot >= 0 ? p.tr_fx : nullptr, trace_slot >= 0 ? p.tr_pts : nullptr,
                                            trace_slot >= 0 ? p.tr_w : nullptr, trace_slot >= 0 ? trace_slot : 0);
     KST_CUDA(cudaGetLastError());
-    return KST_OK;
+    return kst_prof_end(h, KST_PROF_BEST);
 }
 
 int kst_allreduce_sum(kst_problem *h, double *d_buf, size_t count)

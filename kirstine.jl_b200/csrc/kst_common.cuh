@@ -144,7 +144,7 @@ struct kst_problem {
     unsigned long long peer_seq = 0;     // collectives issued so far (identical on every rank)
 
     // profiling of the evaluation kernel
-    int prof_on = 0;
+    int prof_on = 0;   // 0 off, 1 evaluation kernel, 2 swarm move, 3 best update / multi-GPU tail (kst_profile_enable)
     std::vector<cudaEvent_t> prof_events;  // start/stop pairs, resolved by kst_profile_read
 };
 
@@ -195,3 +195,25 @@ int kst_ensure_stage(kst_problem *h, size_t particles, size_t rows);
 int kst_pso_optimize_enqueue(kst_problem *h, int S, int K, int iterations, double c1, double c2, const double *proto_points,
                              const double *proto_weights, int P, const int *fixw, const int *fixp, uint64_t seed, int mode,
                              int want_snapshot);
+
+// kst_profile_enable: a pair of CUDA events around the launches of one stage, resolved by kst_profile_read
+#define KST_PROF_EVAL 1
+#define KST_PROF_MOVE 2
+#define KST_PROF_BEST 3
+static inline int kst_prof_begin(kst_problem *h, int stage)
+{
+    if (h->prof_on != stage) return KST_OK;
+    cudaEvent_t e0, e1;
+    KST_CUDA(cudaEventCreate(&e0));
+    KST_CUDA(cudaEventCreate(&e1));
+    h->prof_events.push_back(e0);
+    h->prof_events.push_back(e1);
+    KST_CUDA(cudaEventRecord(e0, h->stream));
+    return KST_OK;
+}
+static inline int kst_prof_end(kst_problem *h, int stage)
+{
+    if (h->prof_on != stage) return KST_OK;
+    KST_CUDA(cudaEventRecord(h->prof_events.back(), h->stream));
+    return KST_OK;
+}

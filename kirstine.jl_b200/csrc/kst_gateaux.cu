@@ -613,19 +613,14 @@ static int launch_gd(kst_problem *h, int64_t G, const double *d_dirs, size_t sme
     const dim3 grid((unsigned)gblocks, (unsigned)n_split);
     KstDcMax dm;
     for (int c = 0; c < 8; c++) dm.v[c] = h->dcmax[c];
-    if (h->prof_on) {  // kst_profile_enable: CUDA events around the evaluation kernel, read by kst_profile_read
-        cudaEvent_t e0, e1;
-        KST_CUDA(cudaEventCreate(&e0));
-        KST_CUDA(cudaEventCreate(&e1));
-        h->prof_events.push_back(e0);
-        h->prof_events.push_back(e1);
-        KST_CUDA(cudaEventRecord(e0, h->stream));
+    {  // kst_profile_enable: CUDA events around the evaluation kernel, read by kst_profile_read
+        const int rcp = kst_prof_begin(h, KST_PROF_EVAL);
+        if (rcp) return rcp;
     }
     k_gateaux_eval<MF, MR><<<grid, KST_GD_NT, smem, h->stream>>>(h->dc, h->gAp, h->ld, h->N, d_dirs, G, h->mp, dm,
                                                                  h->gd_partials);
     KST_CUDA(cudaGetLastError());
-    if (h->prof_on) KST_CUDA(cudaEventRecord(h->prof_events.back(), h->stream));
-    return KST_OK;
+    return kst_prof_end(h, KST_PROF_EVAL);
 }
 
 template <class MF>

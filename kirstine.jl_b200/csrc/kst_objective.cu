@@ -309,18 +309,13 @@ int kst_launch_objective(kst_problem *h, int S, int K, const double *d_pts, cons
     KstObjParams prm;
     kst_objective_params(h, S, K, d_pts, d_w, h->partials, tile_p, gd, &prm);
     const dim3 grid(n_blk, tiles);
-    if (h->prof_on) {
-        cudaEvent_t e0, e1;
-        KST_CUDA(cudaEventCreate(&e0));
-        KST_CUDA(cudaEventCreate(&e1));
-        h->prof_events.push_back(e0);
-        h->prof_events.push_back(e1);
-        KST_CUDA(cudaEventRecord(e0, h->stream));
-    }
+    rc = kst_prof_begin(h, KST_PROF_EVAL);
+    if (rc) return rc;
     KST_MODEL_SWITCH(h->model_id, rc = kst_obj_launch<MF>(h, prm, grid, K));
     if (rc) return rc;
     KST_CUDA(cudaGetLastError());
-    if (h->prof_on) KST_CUDA(cudaEventRecord(h->prof_events.back(), h->stream));
+    rc = kst_prof_end(h, KST_PROF_EVAL);
+    if (rc) return rc;
     if (defer_n_blk) {
         *defer_n_blk = n_blk;
         return KST_OK;

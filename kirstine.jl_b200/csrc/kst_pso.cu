@@ -236,15 +236,19 @@ int kst_launch_pso_move(kst_problem *h)
     const double chi = 2 / fabs(2 - phi - sqrt(phi * phi - 4 * phi));  // src/pso.jl:134-135
     const int kc = s.K * (s.d + 1);
     const int ppb = kc >= KST_MOVE_NT ? 1 : KST_MOVE_NT / kc;  // particles per CTA: one thread per component where they fit
+    int rc = kst_prof_begin(h, KST_PROF_MOVE);
+    if (rc) return rc;
     k_pso_move<<<(s.S + ppb - 1) / ppb, KST_MOVE_NT, 0, h->stream>>>(s, (uint32_t)h->pso.iter, h->pso.c1, h->pso.c2, chi, ppb);
     KST_CUDA(cudaGetLastError());
-    return KST_OK;
+    return kst_prof_end(h, KST_PROF_MOVE);
 }
 
 int kst_launch_pso_best(kst_problem *h, int init, int trace_slot)
 {
     const KstPsoDev s = make_dev(h);
     KstPso &p = h->pso;
+    int rc = kst_prof_begin(h, KST_PROF_BEST);
+    if (rc) return rc;
     k_pso_best<<<1, 1024, 0, h->stream>>>(s, init, trace_slot >= 0 ? p.tr_fx : nullptr,
                                            trace_slot >= 0 ? p.tr_pts : nullptr, trace_slot >= 0 ? p.tr_w : nullptr,
                                            trace_slot >= 0 ? trace_slot : 0, init ? p.d_status : nullptr,
@@ -252,5 +256,5 @@ int kst_launch_pso_best(kst_problem *h, int init, int trace_slot)
                                            p.pending_nan);
     p.pending_n_blk = 0;
     KST_CUDA(cudaGetLastError());
-    return KST_OK;
+    return kst_prof_end(h, KST_PROF_BEST);
 }
