@@ -280,3 +280,21 @@ def test_direction_pso_trajectory_matches_oracle(family):
         assert np.all(a["x_w"] == 1.0)
         h.pso_run(1)
         po.tick()
+
+
+def test_profile_stages_time_one_launch_each(monkeypatch):
+    """kst_profile_enable(h, stage): events around the evaluation kernel (1), the move (2) or the best update (3) of the
+    three-launch PSO step -- one pair per iteration each, none for the other stages; a stage outside 0..3 is refused."""
+    monkeypatch.setenv("KST_NO_FUSED", "1")   # the persistent kernel has no separate launches to time
+    h, _ = _emax_handles(wl.emax_prior(2000))
+    assert h.pso_init(64, 3, [[0.0], [5.0], [10.0]], [1 / 3] * 3, seed=3) == 0
+    for stage in (1, 2, 3):
+        h.profile_enable(stage)
+        h.pso_run(4)
+        ms, n = h.profile_read()
+        assert n == 4 and 0.0 < ms < 50.0, (stage, ms, n)
+    h.profile_enable(0)
+    h.pso_run(2)
+    assert h.profile_read()[1] == 0
+    with pytest.raises(kb.EngineError, match="stage"):
+        h.profile_enable(4)
