@@ -108,9 +108,11 @@ extern "C" int kst_comm_init(kst_problem *h, int nranks, int rank, const void *i
 // The flags carry the sequence number, so nothing has to be reset between calls.  A peer that never shows up
 // trips a 10 s timeout (error word set, result NaN) instead of hanging the GPU.
 // ---------------------------------------------------------------------------------------
+#define KST_TAIL_NT 128   // particles per CTA of the multi-CTA tail kernel (k_pso_tail)
 struct KstPeerBlock {
     double data[2][KST_PEER_CAP];
-    unsigned long long flag[2];
+    unsigned long long flag[2];                                // single-CTA collective (k_peer_allreduce)
+    unsigned long long flag_s[2][KST_PEER_CAP / KST_TAIL_NT];  // one per slice of KST_TAIL_NT elements (k_pso_tail)
     int error;
 };
 struct KstPeerPtrs {
@@ -203,20 +205,83 @@ __global__ void __launch_bounds__(1024) k_peer_allreduce(double *buf, int count,
     kst_peer_allreduce_cta(buf, count, peers, nranks, rank, seq, partials, n_blk, offset, 0);
 }
 
-// The tail of a swarm iteration on several GPUs in ONE single-CTA launch (after the evaluation kernel):
+// The tail of a swarm iteration on several GPUs in ONE launch (after the evaluation kernel), spread over CTAs of
+// KST_TAIL_NT particles like k_pso_best:
 //   1. fx = fixed-order sum of the evaluation's per-CTA partial sums (+ offset), summed over the ranks through the
-//      peer-memory exchange (kst_peer_allreduce_cta);
-//   2. pso_update_best! (kst_pso_best_cta).
-// An iteration is then move + evaluation + this: three launches, as on one GPU (where k_pso_best finishes the partial
-// sums).  Folding the next iteration's move in here as well was measured and dropped: one CTA moving 1024 particles
-// is a chain of dependent L2 round trips on a single SM (about 100 us against 40 us for the separate launches).
-__global__ void __launch_bounds__(1024) k_pso_tail(KstPsoDev s, KstPeerPtrs peers, int nranks, int rank,
-                                                   unsigned long long seq, const double *__restrict__ partials, int n_blk,
-                                                   double offset, int nan_fill, double *tr_fx, double *tr_pts, double *tr_w,
-                                                   int slot)
+//      peer-memory exchange -- per slice: the CTA publishes its KST_TAIL_NT values in this rank's block, releases the
+//      slice's flag, waits for the same slice's flag of every peer and sums the peers' values in rank order (the
+//      protocol of kst_peer_allreduce_cta with one flag per slice; the parity argument holds slice by slice, because
+//      a rank's launch n + 2 starts after its launch n + 1 has completed, i.e. after every slice has seen every
+//      peer's flag of n + 1, i.e. after every peer has finished launch n);
+//   2. pso_update_best!: personal bests per particle, the swarm-wide part by the CTA that arrives last
+//      (kst_pso_best_grid).
+// An iteration is then move + evaluation + this: three launches, as on one GPU.  (One CTA of 1024 threads did all of
+// this before: 46 us on 8 GPUs.  Folding the next iteration's move in as well was measured with that version and
+// dropped: about 100 us against 40 us for the separate launches.)
+__global__ void __launch_bounds__(KST_TAIL_NT) k_pso_tail(KstPsoDev s, KstPeerPtrs peers, int nranks, int rank,
+                                                          unsigned long long seq, const double *__restrict__ partials,
+                                                          int n_blk, double offset, int nan_fill, double *tr_fx,
+                                                          double *tr_pts, double *tr_w, int slot, KstBestScratch sc)
 {
-    kst_peer_allreduce_cta(s.fx, s.S, peers, nranks, rank, seq, partials, n_blk, offset, nan_fill);
-    kst_pso_best_cta(s, 0, tr_fx, tr_pts, tr_w, slot, nullptr, nullptr, 0, 0.0, 0);
+    __shared__ int s_fail;
+    const int tid = threadIdx.x, c = blockIdx.x, par = (int)(seq & 1ull);
+    const int i = c * KST_TAIL_NT + tid;
+    const bool live = i < s.S;
+    KstPeerBlock *mine = nullptr;
+#pragma unroll
+    for (int r = 0; r < KST_PEER_MAX; r++)
+        if (r == rank) mine = peers.blk[r];
+    double fg_old = -KST_DINF;
+    if (tid == 0) fg_old = *s.fg;   // requested first, needed last (by the last CTA only)
+    const double fpi = live ? kst_pso_best_prefetch(s, i, 0) : 0.0;
+    if (live) mine->data[par][i] = kst_obj_finish_value(partials, n_blk, s.S, i, offset, nan_fill);
+    if (tid == 0) s_fail = 0;
+    __syncthreads();
+    // the fence orders the whole CTA's stores (they happen before it through the barrier) ahead of the flag
+    if (tid == 0) {
+        __threadfence_system();
+        kst_st_release_sys(&mine->flag_s[par][c], seq);
+    }
+    // one waiting thread per peer
+#pragma unroll
+    for (int r = 0; r < KST_PEER_MAX; r++)
+        if (r < nranks && r != rank && tid == r) {
+            const unsigned long long *f = &peers.blk[r]->flag_s[par][c];
+            unsigned long long t0;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            while (kst_ld_acquire_sys(f) < seq) {
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 10000000000ull) {  // 10 s
+                    s_fail = 1;
+                    break;
+                }
+            }
+        }
+    __syncthreads();
+    double best = -KST_DINF;
+    int bi = -1;
+    bool notnan = false;
+    if (s_fail && tid == 0) mine->error = 1;
+    if (live) {
+        double f = __longlong_as_double(0x7ff8000000000000LL);
+        if (!s_fail) {
+            double v[KST_PEER_MAX];
+#pragma unroll
+            for (int r = 0; r < KST_PEER_MAX; r++)  // all loads in flight before the first use
+                if (r < nranks) v[r] = kst_ld_peer(&peers.blk[r]->data[par][i]);
+            f = 0.0;
+#pragma unroll
+            for (int r = 0; r < KST_PEER_MAX; r++)
+                if (r < nranks) f += v[r];
+        }
+        s.fx[i] = f;
+        bool improved;
+        kst_pso_best_update(s, i, 0, f, fpi, improved);
+        notnan = f == f;
+        if (improved) { best = f; bi = i; }
+    }
+    kst_pso_best_grid(s, best, bi, notnan, fg_old, sc, tr_fx, tr_pts, tr_w, slot, nullptr);
 }
 
 int kst_launch_pso_tail(kst_problem *h, int trace_slot, int n_blk, double offset, int nan_fill)
@@ -229,9 +294,11 @@ int kst_launch_pso_tail(kst_problem *h, int trace_slot, int n_blk, double offset
     for (int r = 0; r < KST_PEER_MAX; r++) pp.blk[r] = (KstPeerBlock *)h->peer_map[r];
     const int rcp = kst_prof_begin(h, KST_PROF_BEST);
     if (rcp) return rcp;
-    k_pso_tail<<<1, 1024, 0, h->stream>>>(s, pp, h->nranks, h->rank, ++h->peer_seq, h->partials, n_blk, offset, nan_fill,
-                                           trace_slot >= 0 ? p.tr_fx : nullptr, trace_slot >= 0 ? p.tr_pts : nullptr,
-                                           trace_slot >= 0 ? p.tr_w : nullptr, trace_slot >= 0 ? trace_slot : 0);
+    KstBestScratch sc;
+    sc.val = p.best_val; sc.idx = p.best_idx; sc.counter = p.best_counter;
+    k_pso_tail<<<(p.S + KST_TAIL_NT - 1) / KST_TAIL_NT, KST_TAIL_NT, 0, h->stream>>>(
+        s, pp, h->nranks, h->rank, ++h->peer_seq, h->partials, n_blk, offset, nan_fill, trace_slot >= 0 ? p.tr_fx : nullptr,
+        trace_slot >= 0 ? p.tr_pts : nullptr, trace_slot >= 0 ? p.tr_w : nullptr, trace_slot >= 0 ? trace_slot : 0, sc);
     KST_CUDA(cudaGetLastError());
     return kst_prof_end(h, KST_PROF_BEST);
 }

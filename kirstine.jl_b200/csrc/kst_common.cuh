@@ -68,6 +68,7 @@ struct KstPso {
            *v_w = nullptr, *g_pts = nullptr, *g_w = nullptr, *fx = nullptr, *fp = nullptr,
            *fg = nullptr;
     int *fixw = nullptr, *fixp = nullptr;
+    double *best_val = nullptr; int *best_idx = nullptr; unsigned int *best_counter = nullptr;  // k_pso_best scratch (arena)
     // persistent swarm kernel (kst_pso_fused.cuh): published positions [2][S][K*d] / [2][S][K], grid barrier counter
     // (+ error word) and how far it has counted
     double *x2_pts = nullptr, *x2_w = nullptr;

@@ -73,40 +73,74 @@ __global__ void k_pso_init(KstPsoDev s, const double *__restrict__ proto_pts, co
 }
 
 // velocity + constrained move.  A CTA takes `ppb` particles: one thread per (particle, component) draws the two random
-// numbers and updates the velocity (kst_pso_velocity; components are independent), then one thread per particle does
-// the constrained move, whose sums run in the reference's order (kst_pso_position) -- the same split as in the
-// persistent swarm kernel.  In place in global memory.  (One thread per particle for everything: 17.5 us for 1024
-// particles x 16 components with cold caches, two thirds of it the sixteen Philox blocks and velocities in series.
-// Staging x, v and the personal best in shared memory first was measured too: 24.5 us.)
+// numbers and updates the velocity (kst_pso_velocity; components are independent) and leaves position and new velocity
+// in a shared-memory slice of the particle; then one thread per particle does the constrained move on its slice, whose
+// sums run in the reference's order (kst_pso_position); then all threads write x and v back -- the same split as in
+// the persistent swarm kernel.
+// Why the slice: the move rewrites every component several times in loops of the form x[k] = f(x[k], v[k]).  A warp
+// issues in order, so in global memory each iteration is a dependent round trip (the store drops the line from L1
+// and the next iteration's load has to wait for it to issue): one thread per particle working in place took 17.5 us
+// for 1024 particles x 16 components with cold caches, velocities spread over the components 11.3 us.  (A first
+// staged version copied x, v, p into shared memory with plain per-element loops -- load -> store chains of the same
+// kind -- and took 24.5 us.)
 #define KST_MOVE_NT 128
 __global__ void __launch_bounds__(KST_MOVE_NT) k_pso_move(KstPsoDev s, uint32_t iter, double c1, double c2, double chi, int ppb)
 {
-    const int K = s.K, d = s.d, KD = K * d, KC = K + KD;
+    extern __shared__ double s_mv[];   // [ppb][2 KC + 1]: x_w | x_pts | v_w | v_pts of a particle, odd stride
+    const int K = s.K, d = s.d, KD = K * d, KC = K + KD, stride = 2 * KC + 1;
     const int i0 = blockIdx.x * ppb, np = min(ppb, s.S - i0);
     for (int e = threadIdx.x; e < np * KC; e += KST_MOVE_NT) {
-        const int i = i0 + e / KC, c = e % KC;
+        const int il = e / KC, c = e % KC, i = i0 + il;
         double r1, r2;
         kst_uniform2(s.seed, iter, (uint32_t)i, (uint32_t)c, 0, r1, r2);
         const bool isw = c < K;
         const size_t o = isw ? (size_t)i * K + c : (size_t)i * KD + (c - K);
-        double *v = isw ? s.v_w + o : s.v_pts + o;
-        *v = kst_pso_velocity(*v, isw ? s.x_w[o] : s.x_pts[o], isw ? s.p_w[o] : s.p_pts[o], isw ? s.g_w[c] : s.g_pts[c - K],
-                              r1, r2, c1, c2, chi);
+        const double x = isw ? s.x_w[o] : s.x_pts[o], v = isw ? s.v_w[o] : s.v_pts[o];
+        const double pb = isw ? s.p_w[o] : s.p_pts[o], gb = isw ? s.g_w[c] : s.g_pts[c - K];
+        double *sl = s_mv + (size_t)il * stride;
+        sl[c] = x;
+        sl[KC + c] = kst_pso_velocity(v, x, pb, gb, r1, r2, c1, c2, chi);
     }
-    __syncthreads();  // the velocities were written by this CTA's own threads
+    __syncthreads();
     if ((int)threadIdx.x < np) {
-        const int i = i0 + threadIdx.x;
-        kst_pso_position(K, d, s.x_w + (size_t)i * K, s.x_pts + (size_t)i * KD, s.v_w + (size_t)i * K,
-                         s.v_pts + (size_t)i * KD, s.fixw, s.fixp, s.lb, s.ub);
+        double *sl = s_mv + (size_t)threadIdx.x * stride;
+        kst_pso_position(K, d, sl, sl + K, sl + KC, sl + KC + K, s.fixw, s.fixp, s.lb, s.ub);
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < np * KC; e += KST_MOVE_NT) {
+        const int il = e / KC, c = e % KC, i = i0 + il;
+        const bool isw = c < K;
+        const size_t o = isw ? (size_t)i * K + c : (size_t)i * KD + (c - K);
+        const double *sl = s_mv + (size_t)il * stride;
+        if (isw) { s.x_w[o] = sl[c]; s.v_w[o] = sl[KC + c]; }
+        else { s.x_pts[o] = sl[c]; s.v_pts[o] = sl[KC + c]; }
     }
 }
 
-// pso_update_best! as a kernel of its own (kst_pso_best_cta, kst_pso_dev.cuh)
-__global__ void __launch_bounds__(1024) k_pso_best(KstPsoDev s, int init, double *tr_fx, double *tr_pts, double *tr_w,
-                                                   int slot, int *status, const double *__restrict__ partials,
-                                                   int n_blk, double offset, int nan_fill)
+// pso_update_best! as a kernel of its own, spread over CTAs of KST_BEST_NT particles: every CTA finishes the objective
+// values of its particles and updates their personal bests; the swarm-wide part is done by the CTA that arrives last
+// (kst_pso_best_grid, kst_pso_dev.cuh).
+// One CTA of 1024 threads did all of it before: 20 us for 1024 particles, because a single SM had to move the partial
+// sums, x and p (about 0.6 MB) on its own.
+#define KST_BEST_NT 128
+__global__ void __launch_bounds__(KST_BEST_NT) k_pso_best(KstPsoDev s, int init, double *tr_fx, double *tr_pts, double *tr_w,
+                                                          int slot, int *status, const double *__restrict__ partials,
+                                                          int n_blk, double offset, int nan_fill, KstBestScratch sc)
 {
-    kst_pso_best_cta(s, init, tr_fx, tr_pts, tr_w, slot, status, partials, n_blk, offset, nan_fill);
+    const int tid = threadIdx.x;
+    double fg_old = -KST_DINF;
+    if (tid == 0 && !init) fg_old = *s.fg;   // requested first, needed last (by the last CTA only)
+    const int i = blockIdx.x * KST_BEST_NT + tid;
+    double best = -KST_DINF;
+    int bi = -1;
+    bool notnan = false;
+    if (i < s.S) {
+        bool improved;
+        const double f = kst_pso_best_particle(s, i, init, partials, n_blk, offset, nan_fill, improved);
+        notnan = f == f;
+        if (improved) { best = f; bi = i; }
+    }
+    kst_pso_best_grid(s, best, bi, notnan, fg_old, sc, tr_fx, tr_pts, tr_w, slot, status);
 }
 
 void kst_pso_make_dev(const kst_problem *h, KstPsoDev *out)
@@ -143,8 +177,10 @@ int kst_pso_alloc(kst_problem *h, int S, int K)
 {
     KstPso &p = h->pso;
     const size_t np = (size_t)S * K * h->d, nw = (size_t)S * K, kd = (size_t)K * h->d;
-    // doubles: barrier words (2), x p v (3 np + 3 nw), published positions (2 np + 2 nw), g, fx, fp, fg, fixw / fixp
-    const size_t need = 2 + 5 * (np + nw) + kd + K + 2 * (size_t)S + 1 + (size_t)K + 2;
+    // doubles: barrier words (2), x p v (3 np + 3 nw), published positions (2 np + 2 nw), g, fx, fp, fg, fixw / fixp,
+    // best-update scratch (per CTA one candidate value, two ints; one counter word)
+    const size_t n_cta = ((size_t)S + 127) / 128;
+    const size_t need = 2 + 5 * (np + nw) + kd + K + 2 * (size_t)S + 1 + (size_t)K + 2 + 2 * n_cta + 1;
     if (need > p.arena_cap) {
         KST_CUDA(cudaStreamSynchronize(h->stream));
         if (p.arena) KST_CUDA(cudaFree(p.arena));
@@ -162,7 +198,9 @@ int kst_pso_alloc(kst_problem *h, int S, int K)
     p.x_w = q; q += nw; p.p_w = q; q += nw; p.v_w = q; q += nw; p.x2_w = q; q += 2 * nw;
     p.g_pts = q; q += kd; p.g_w = q; q += K;
     p.fx = q; q += S; p.fp = q; q += S; p.fg = q; q += 1;
-    p.fixw = (int *)q; p.fixp = p.fixw + K;
+    p.fixw = (int *)q; p.fixp = p.fixw + K; q += K + 2;
+    p.best_val = q; q += n_cta; p.best_idx = (int *)q; q += n_cta; p.best_counter = (unsigned int *)q;
+    KST_CUDA(cudaMemsetAsync(p.best_counter, 0, sizeof(double), h->stream));  // zero between launches (the last CTA resets it)
     p.fused_off = 0;
     p.S = S; p.K = K;
     p.tr_n = 0;  // the output block has to be carved again for this shape
@@ -238,7 +276,9 @@ int kst_launch_pso_move(kst_problem *h)
     const int ppb = kc >= KST_MOVE_NT ? 1 : KST_MOVE_NT / kc;  // particles per CTA: one thread per component where they fit
     int rc = kst_prof_begin(h, KST_PROF_MOVE);
     if (rc) return rc;
-    k_pso_move<<<(s.S + ppb - 1) / ppb, KST_MOVE_NT, 0, h->stream>>>(s, (uint32_t)h->pso.iter, h->pso.c1, h->pso.c2, chi, ppb);
+    const size_t smem = sizeof(double) * ppb * (2 * (size_t)kc + 1);
+    if (smem > 48 * 1024) { kst_set_error("pso: %d components per particle exceed the move kernel's shared memory", kc); return KST_ELIMIT; }
+    k_pso_move<<<(s.S + ppb - 1) / ppb, KST_MOVE_NT, smem, h->stream>>>(s, (uint32_t)h->pso.iter, h->pso.c1, h->pso.c2, chi, ppb);
     KST_CUDA(cudaGetLastError());
     return kst_prof_end(h, KST_PROF_MOVE);
 }
@@ -249,11 +289,13 @@ int kst_launch_pso_best(kst_problem *h, int init, int trace_slot)
     KstPso &p = h->pso;
     int rc = kst_prof_begin(h, KST_PROF_BEST);
     if (rc) return rc;
-    k_pso_best<<<1, 1024, 0, h->stream>>>(s, init, trace_slot >= 0 ? p.tr_fx : nullptr,
+    KstBestScratch sc;
+    sc.val = p.best_val; sc.idx = p.best_idx; sc.counter = p.best_counter;
+    k_pso_best<<<(s.S + KST_BEST_NT - 1) / KST_BEST_NT, KST_BEST_NT, 0, h->stream>>>(s, init, trace_slot >= 0 ? p.tr_fx : nullptr,
                                            trace_slot >= 0 ? p.tr_pts : nullptr, trace_slot >= 0 ? p.tr_w : nullptr,
                                            trace_slot >= 0 ? trace_slot : 0, init ? p.d_status : nullptr,
                                            p.pending_n_blk ? h->partials : nullptr, p.pending_n_blk, p.pending_offset,
-                                           p.pending_nan);
+                                           p.pending_nan, sc);
     p.pending_n_blk = 0;
     KST_CUDA(cudaGetLastError());
     return kst_prof_end(h, KST_PROF_BEST);

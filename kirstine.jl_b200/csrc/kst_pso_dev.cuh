@@ -166,92 +166,127 @@ __device__ __forceinline__ void kst_pso_position(const int K, const int d, doubl
     }
 }
 
+// dst[0..n) = src[0..n) by one thread, eight loads in flight: written as load batch, then store batch, because a warp
+// issues in order and a plain `dst[c] = src[c]` loop is one dependent load -> store round trip per element (the
+// compiler may not move a load above an earlier store that could alias it): 13 of k_pso_best's 20 us with cold caches.
+__device__ __forceinline__ void kst_copy8(double *dst, const double *src, int n)
+{
+    for (int c0 = 0; c0 < n; c0 += 8) {
+        double t[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+            if (c0 + u < n) t[u] = src[c0 + u];
+#pragma unroll
+        for (int u = 0; u < 8; u++)
+            if (c0 + u < n) dst[c0 + u] = t[u];
+    }
+}
+
 // pso_update_best!: strict '>', sequential semantics => the lowest index attaining the maximum
 // among improved particles becomes the global best iff it beats fg; NaN never wins.
 // status (init only): 1 = fg == +Inf, 2 = all fx NaN.
 // partials != nullptr: the evaluation kernel's per-CTA partial sums are still unfinished; fx[i] is their fixed-order
 // sum plus `offset` (what k_obj_finish would have written), computed here to save a launch per iteration.
-// One CTA of up to 1024 threads; ends with the CTA synchronised and g, fg, fp, p up to date.
-__device__ __forceinline__ void kst_pso_best_cta(const KstPsoDev &s, int init, double *tr_fx, double *tr_pts, double *tr_w,
-                                                 int slot, int *status, const double *__restrict__ partials,
-                                                 int n_blk, double offset, int nan_fill)
+// The pieces below are shared by the single-CTA form (kst_pso_best_cta: persistent swarm kernel, multi-GPU tail) and
+// the multi-CTA kernel k_pso_best (kst_pso.cu).
+
+// arg-max merge: the larger value, the lower index among equals; index -1 = no candidate
+__device__ __forceinline__ void kst_argmax_merge(double &va, int &ia, const double vb, const int ib)
 {
-    __shared__ double s_val[32];
-    __shared__ int s_idx[32];
-    __shared__ int s_notnan;
-    const int K = s.K, d = s.d, tid = threadIdx.x;
-    // requested first, needed last: the best objective so far
-    double fg_old = -KST_DINF;
-    if (tid == 0 && !init) fg_old = *s.fg;
-    if (tid == 0) s_notnan = 0;
-    __syncthreads();
-    double best = -KST_DINF;
-    int bidx = -1;
-    bool have = false;
-    bool notnan = false;
-    for (int i = tid; i < s.S; i += blockDim.x) {
-        double f;
-        if (partials) {
-            double acc = 0.0;
-#pragma unroll 8
-            for (int b = 0; b < n_blk; b++) acc += partials[(size_t)b * s.S + i];  // eight loads in flight, added in order
-            f = nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : acc + offset;
-            s.fx[i] = f;
-        } else {
-            f = s.fx[i];
-        }
-        const double fpi = init ? (-KST_DINF) : s.fp[i];
-        notnan = notnan || (f == f);
-        if (f > fpi) {
-            const double *xp = s.x_pts + (size_t)i * K * d, *xw = s.x_w + (size_t)i * K;
-            double *pp = s.p_pts + (size_t)i * K * d, *pw = s.p_w + (size_t)i * K;
-            for (int c = 0; c < K * d; c++) pp[c] = xp[c];
-            for (int k = 0; k < K; k++) pw[k] = xw[k];
-            s.fp[i] = f;
-            if (!have || f > best) { best = f; bidx = i; have = true; }
-        } else if (init) {
-            s.fp[i] = fpi;
-        }
-    }
-    if (notnan) atomicOr(&s_notnan, 1);
-    // arg-max over the CTA (any multiple of 32 threads): the largest value, the lowest index among equals; -1 = none
-    int bi = have ? bidx : -1;
-    auto merge = [](double &va, int &ia, const double vb, const int ib) {
-        if (ib >= 0 && (ia < 0 || vb > va || (vb == va && ib < ia))) { va = vb; ia = ib; }
-    };
+    if (ib >= 0 && (ia < 0 || vb > va || (vb == va && ib < ia))) { va = vb; ia = ib; }
+}
+__device__ __forceinline__ void kst_argmax_warp(double &best, int &bi)
+{
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const double vb = __shfl_down_sync(0xffffffffu, best, o);
         const int ib = __shfl_down_sync(0xffffffffu, bi, o);
-        merge(best, bi, vb, ib);
+        kst_argmax_merge(best, bi, vb, ib);
     }
+}
+// arg-max over a CTA of any multiple of 32 threads (<= 1024); result valid in thread 0.  s_val / s_idx: 32 entries.
+__device__ __forceinline__ void kst_argmax_cta(double &best, int &bi, double *s_val, int *s_idx)
+{
+    const int tid = threadIdx.x;
+    kst_argmax_warp(best, bi);
     if ((tid & 31) == 0) { s_val[tid >> 5] = best; s_idx[tid >> 5] = bi; }
     __syncthreads();
-    __shared__ int s_update, s_gi;
     if (tid < 32) {
         const int nw = (blockDim.x + 31) >> 5;
         best = tid < nw ? s_val[tid] : -KST_DINF;
         bi = tid < nw ? s_idx[tid] : -1;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const double vb = __shfl_down_sync(0xffffffffu, best, o);
-            const int ib = __shfl_down_sync(0xffffffffu, bi, o);
-            merge(best, bi, vb, ib);
-        }
+        kst_argmax_warp(best, bi);
     }
+}
+
+// Requested before a particle's value is finished, needed after: its personal best value, and its position in
+// L2 / L1 (cold when a bench flushes L2 between iterations).
+__device__ __forceinline__ double kst_pso_best_prefetch(const KstPsoDev &s, const int i, const int init)
+{
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(s.x_pts + (size_t)i * s.K * s.d));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(s.x_w + (size_t)i * s.K));
+    return init ? (-KST_DINF) : s.fp[i];
+}
+// this rank's part of a particle's objective value: the fixed-order sum of the evaluation kernel's per-CTA partial sums
+// plus `offset` (exactly what k_obj_finish computes)
+__device__ __forceinline__ double kst_obj_finish_value(const double *__restrict__ partials, const int n_blk, const int S,
+                                                       const int i, const double offset, const int nan_fill)
+{
+    double acc = 0.0;
+#pragma unroll 8
+    for (int b = 0; b < n_blk; b++) acc += partials[(size_t)b * S + i];  // eight loads in flight, added in order
+    return nan_fill ? __longlong_as_double(0x7ff8000000000000LL) : acc + offset;
+}
+__device__ __forceinline__ void kst_pso_best_update(const KstPsoDev &s, const int i, const int init, const double f,
+                                                    const double fpi, bool &improved);
+
+// One particle: finish its objective value (when partials), store it, update the personal best.  Returns the value;
+// `improved` says whether it is a candidate for the global best.
+__device__ __forceinline__ double kst_pso_best_particle(const KstPsoDev &s, const int i, const int init,
+                                                        const double *__restrict__ partials, const int n_blk,
+                                                        const double offset, const int nan_fill, bool &improved)
+{
+    const double fpi = kst_pso_best_prefetch(s, i, init);
+    double f;
+    if (partials) {
+        f = kst_obj_finish_value(partials, n_blk, s.S, i, offset, nan_fill);
+        s.fx[i] = f;
+    } else {
+        f = s.fx[i];
+    }
+    kst_pso_best_update(s, i, init, f, fpi, improved);
+    return f;
+}
+// the personal-best half of pso_update_best! for one particle whose value f is known (fpi = its personal best value)
+__device__ __forceinline__ void kst_pso_best_update(const KstPsoDev &s, const int i, const int init, const double f,
+                                                    const double fpi, bool &improved)
+{
+    const int K = s.K, d = s.d;
+    improved = f > fpi;
+    if (improved) {
+        kst_copy8(s.p_pts + (size_t)i * K * d, s.x_pts + (size_t)i * K * d, K * d);
+        kst_copy8(s.p_w + (size_t)i * K, s.x_w + (size_t)i * K, K);
+        s.fp[i] = f;
+    } else if (init) {
+        s.fp[i] = fpi;
+    }
+}
+
+// The swarm-wide part, by one CTA that knows the arg-max (gv, gi; valid in thread 0), the best value so far (fg_old,
+// thread 0) and whether any value was not NaN: global best, trace entry, status.  Ends with the CTA synchronised.
+__device__ __forceinline__ void kst_pso_best_finish(const KstPsoDev &s, const double gv, const int gi_in, const double fg_old,
+                                                    const int any_notnan, double *tr_fx, double *tr_pts, double *tr_w,
+                                                    const int slot, int *status)
+{
+    __shared__ int s_update, s_gi;
+    const int K = s.K, d = s.d, tid = threadIdx.x;
     if (tid == 0) {
-        const int gi = bi;
-        const double gv = best;
-        s_gi = gi;
-        s_update = (gi >= 0 && gv > fg_old) ? 1 : 0;
+        s_gi = gi_in;
+        s_update = (gi_in >= 0 && gv > fg_old) ? 1 : 0;
         const double fg_new = s_update ? gv : fg_old;
         *s.fg = fg_new;
         if (tr_fx) tr_fx[slot] = fg_new;
-        if (status) {
-            int st = 0;
-            if (fg_new == KST_DINF) st = 1;
-            *status = st;
-        }
+        if (status) *status = fg_new == KST_DINF ? 1 : (any_notnan ? 0 : 2);
     }
     __syncthreads();
     // the global best moves to the winner's position (or stays); the trace entry is written from the same registers
@@ -272,7 +307,87 @@ __device__ __forceinline__ void kst_pso_best_cta(const KstPsoDev &s, int init, d
             if (tr_w) tr_w[(size_t)slot * K + k] = v;
         }
     }
-    if (status && tid == 0 && *status == 0 && !s_notnan) *status = 2;
     __syncthreads();
 }
 
+// The whole update by ONE CTA of up to 1024 threads; ends with the CTA synchronised and g, fg, fp, p up to date.
+__device__ __forceinline__ void kst_pso_best_cta(const KstPsoDev &s, int init, double *tr_fx, double *tr_pts, double *tr_w,
+                                                 int slot, int *status, const double *__restrict__ partials,
+                                                 int n_blk, double offset, int nan_fill)
+{
+    __shared__ double s_val[32];
+    __shared__ int s_idx[32];
+    __shared__ int s_notnan;
+    const int tid = threadIdx.x;
+    // requested first, needed last: the best objective so far
+    double fg_old = -KST_DINF;
+    if (tid == 0 && !init) fg_old = *s.fg;
+    if (tid == 0) s_notnan = 0;
+    __syncthreads();
+    double best = -KST_DINF;
+    int bi = -1;
+    bool notnan = false;
+    for (int i = tid; i < s.S; i += blockDim.x) {
+        bool improved;
+        const double f = kst_pso_best_particle(s, i, init, partials, n_blk, offset, nan_fill, improved);
+        notnan = notnan || (f == f);
+        if (improved && (bi < 0 || f > best)) { best = f; bi = i; }
+    }
+    if (__any_sync(0xffffffffu, notnan) && (tid & 31) == 0) atomicOr(&s_notnan, 1);
+    kst_argmax_cta(best, bi, s_val, s_idx);   // one barrier inside: s_notnan is complete after it
+    __syncthreads();
+    kst_pso_best_finish(s, best, bi, fg_old, s_notnan, tr_fx, tr_pts, tr_w, slot, status);
+}
+
+// Scratch of the multi-CTA best update: one candidate per CTA and the arrival counter (zero between launches).
+struct KstBestScratch {
+    double *val;
+    int *idx;       // [n_cta] candidate index, then [n_cta] "some value was not NaN"
+    unsigned int *counter;
+};
+
+// The swarm-wide half of pso_update_best! for a grid of CTAs that have each updated the personal bests of their own
+// particles: (best, bi) = the thread's candidate (its improved particle or -1), notnan = its value was not NaN.
+// Every CTA leaves its arg-max candidate in global memory; the CTA that arrives last (one atomic counter) merges the
+// candidates -- the merge rule is order independent: largest value, lowest index among equals -- and does the
+// swarm-wide part (global best, trace entry, status).  fg_old: the best value so far, read by thread 0 at kernel start.
+__device__ __forceinline__ void kst_pso_best_grid(const KstPsoDev &s, double best, int bi, const bool notnan,
+                                                  const double fg_old, const KstBestScratch &sc, double *tr_fx,
+                                                  double *tr_pts, double *tr_w, const int slot, int *status)
+{
+    __shared__ double s_val[32];
+    __shared__ int s_idx[32];
+    __shared__ int s_notnan, s_last;
+    const int tid = threadIdx.x, n_cta = gridDim.x;
+    if (tid == 0) s_notnan = 0;
+    __syncthreads();
+    if (__any_sync(0xffffffffu, notnan) && (tid & 31) == 0) atomicOr(&s_notnan, 1);
+    kst_argmax_cta(best, bi, s_val, s_idx);
+    __syncthreads();
+    if (tid == 0) {
+        sc.val[blockIdx.x] = best;
+        sc.idx[blockIdx.x] = bi;
+        sc.idx[n_cta + blockIdx.x] = s_notnan;
+        __threadfence();
+        s_last = atomicAdd(sc.counter, 1u) == (unsigned)(n_cta - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // the last CTA: merge the candidates (written by other SMs: volatile reads)
+    best = -KST_DINF;
+    bi = -1;
+    int nn = 0;
+    for (int c = tid; c < n_cta; c += blockDim.x) {
+        kst_argmax_merge(best, bi, ((volatile double *)sc.val)[c], ((volatile int *)sc.idx)[c]);
+        nn |= ((volatile int *)sc.idx)[n_cta + c];
+    }
+    nn = __any_sync(0xffffffffu, nn != 0);
+    __syncthreads();   // s_notnan, s_val, s_idx are reused
+    if (tid == 0) { s_notnan = 0; *sc.counter = 0u; }   // the counter is zero again for the next launch
+    __syncthreads();
+    if (nn && (tid & 31) == 0) atomicOr(&s_notnan, 1);
+    kst_argmax_cta(best, bi, s_val, s_idx);
+    __syncthreads();
+    kst_pso_best_finish(s, best, bi, fg_old, s_notnan, tr_fx, tr_pts, tr_w, slot, status);
+}
