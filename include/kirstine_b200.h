@@ -158,7 +158,8 @@ KST_API int kst_comm_init(kst_problem *h, int nranks, int rank, const void *id12
  * The same all-reduce over NVLink peer memory instead of NCCL (one box, GPUs with peer access): every rank
  * publishes its S partial sums in an exchange block that all peers map through CUDA IPC, and ONE single-CTA
  * kernel per evaluation publishes, waits for the peers' sequence flags and sums all vectors in rank order
- * (identical bits on every rank).  kst_comm_peer_handle allocates this rank's block and returns its 64-byte
+ * (identical bits on every rank; swarm iterations run the same exchange per slice of 128 particles inside the
+ * kernel that updates the bests).  kst_comm_peer_handle allocates this rank's block and returns its 64-byte
  * cudaIpcMemHandle_t; the host gathers the nranks handles (rank order, 64 bytes each) and every rank calls
  * kst_comm_peer_open.  Vectors longer than 16384 doubles still go through NCCL (kst_comm_init).  A peer that
  * does not arrive within 10 s makes the result NaN and sets the error word read by kst_comm_peer_error.

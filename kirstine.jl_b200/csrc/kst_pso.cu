@@ -4,7 +4,7 @@
 //   pso_update_velocity! src/pso.jl:143-164  \
 //   pso_update_position! src/pso.jl:166-171   >  -> k_pso_move (one thread per particle)
 //   ap_add!(p, v, c)     src/designmeasure-abstractpoint.jl:164-285 /
-//   pso_update_best!     src/pso.jl:181-193      -> k_pso_best (one CTA, fixed-order arg-max)
+//   pso_update_best!     src/pso.jl:181-193      -> k_pso_best (CTAs of 128 particles, order-independent arg-max merge)
 //
 // Random numbers come from Philox4x32-10 keyed on (seed; iteration, particle, component, stream),
 // so every replica of the swarm (one per GPU) advances identically without any broadcast, and the
