@@ -298,3 +298,34 @@ def test_profile_stages_time_one_launch_each(monkeypatch):
     assert h.profile_read()[1] == 0
     with pytest.raises(kb.EngineError, match="stage"):
         h.profile_enable(4)
+
+
+@pytest.mark.parametrize("S", [300, 1000])
+def test_pso_many_particles_cross_cta_best_matches_oracle(S, monkeypatch):
+    """Swarms of more than 128 particles: the best update runs as several CTAs whose candidates the last-arriving one
+    merges (k_pso_best), and the move takes its particles in groups.  Every prototype appears twice, 150 indices
+    apart, so equal objective values meet across CTAs and the lower index has to win as in the reference's sequential
+    pso_update_best! (src/pso.jl:181-193); positions, velocities and bests follow the oracle tick by tick."""
+    monkeypatch.setenv("KST_NO_FUSED", "1")
+    h, o = _emax_handles(wl.emax_prior(300, seed=11))
+    K, half = 3, 150
+    rng = np.random.default_rng(7)
+    pts = np.sort(rng.uniform(0.0, 10.0, (half, K, 1)), axis=1)
+    w = rng.dirichlet(np.ones(K), half)
+    pts, w = np.concatenate([pts, pts]), np.concatenate([w, w])      # particle i + 150 == particle i
+    assert h.pso_init(S, K, pts, w, seed=5) == 0
+    po = ko.Pso(o, S, K, [0.0], [10.0], seed=5)
+    po.init(pts, w)
+    a, b = h.pso_state(), po.state()
+    for key in ("x_pts", "x_w", "p_pts", "p_w", "g_pts", "g_w"):
+        # (the random particles' weights go through log: device and host libm may differ in the last bit)
+        np.testing.assert_allclose(a[key], b[key], rtol=1e-14, atol=0, err_msg=key)
+    assert np.array_equal(a["fx"][:half], a["fx"][half:2 * half])     # the duplicates really tie
+    for it in range(4):
+        h.pso_run(1)
+        po.tick()
+        a, b = h.pso_state(), po.state()
+        for key in ("x_pts", "x_w", "v_pts", "v_w", "p_pts", "p_w", "g_pts", "g_w"):
+            np.testing.assert_allclose(a[key], b[key], rtol=1e-12, atol=1e-14, err_msg="%s at tick %d" % (key, it))
+        assert a["fg"] == a["fp"].max()
+    assert a["n_eval"] == S * 5
