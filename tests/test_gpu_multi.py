@@ -54,10 +54,15 @@ def _worker(rank, world, port, out_dir, peer=False):
     _, gfx, gpx, _, _ = h.pso_optimize(12, 1, 5, pts[0][[1, 4, 6]].reshape(3, 1, 1), np.ones((3, 1)), seed=3,
                                        mode=kb._ffi.PSO_MODE_GATEAUX, state0=False)
     ex = h.exchange_run(pts[0], w[0], 2, (12, 4, 2.05, 2.05), (10, 4, 2.05, 2.05), seed=8, state0=False)
+    # a swarm of several 128-particle slices: the tail kernel exchanges and updates the bests slice by slice
+    assert h.pso_init(300, 8, pts[0], w[0], seed=12) == 0
+    btfx, _, _ = h.pso_run(3)
+    bst = h.pso_state()
     if peer:
         assert h.comm_peer_error() == 0
     np.savez(os.path.join(out_dir, "r%d.npz" % rank), fx=fx, tfx=tfx, tp=tp, tw=tw, x=st["x_pts"], xw=st["x_w"], gd=gd,
-             gfx=gfx, gpx=gpx, exw=ex["weights"], exp=ex["points"], exfx=ex["w_fx"])
+             gfx=gfx, gpx=gpx, exw=ex["weights"], exp=ex["points"], exfx=ex["w_fx"], btfx=btfx, bx=bst["x_pts"],
+             bfx=bst["fx"], bg=bst["g_pts"])
     dist.destroy_process_group()
 
 
@@ -93,6 +98,13 @@ def test_two_gpu_sharded_run_matches_single_gpu(tmp_path, peer):
     np.testing.assert_allclose(a["exfx"], ex["w_fx"], rtol=1e-10)
     np.testing.assert_allclose(a["exp"], ex["points"], rtol=1e-8)
     np.testing.assert_allclose(a["exw"], ex["weights"], rtol=1e-7, atol=1e-9)
+    assert h.pso_init(300, 8, pts[0], w[0], seed=12) == 0
+    btfx, _, _ = h.pso_run(3)
+    bst = h.pso_state()
+    np.testing.assert_allclose(a["btfx"], btfx, rtol=1e-11)
+    np.testing.assert_allclose(a["bfx"], bst["fx"], rtol=1e-9)
+    np.testing.assert_allclose(a["bx"], bst["x_pts"], rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(a["bg"], bst["g_pts"], rtol=1e-9, atol=1e-12)
     # the sharded result against the CPU oracle on the whole prior
     import oracle as ko
     want = ko.Problem(ko.SIGEMAX, [1.0], theta).objective_batch(pts, w, nthreads=8)
