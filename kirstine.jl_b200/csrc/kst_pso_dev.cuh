@@ -1,6 +1,7 @@
 // Device-side pieces of the particle swarm shared by the stand-alone kernels (kst_pso.cu) and the persistent swarm
-// kernel (kst_pso_fused.cuh): the counter-based random numbers, the device view of the swarm state, and the
-// velocity update + constrained move of ONE particle.
+// kernel (kst_pso_fused.cuh) and the multi-GPU tail (kst_comm.cu): the counter-based random numbers, the device view
+// of the swarm state, the velocity update of one component, the constrained move of one particle, and the pieces of
+// pso_update_best!.
 //
 // The move must round exactly like the scalar reference arithmetic (src/pso.jl:143-171,
 // src/designmeasure-abstractpoint.jl:164-285, src/designregion.jl:114-135) whatever -fmad setting the including
@@ -46,15 +47,6 @@ struct KstPsoDev {
     uint64_t seed;
 };
 
-// the two uniforms of a velocity component straight from the counter-based generator
-struct KstRndPhilox {
-    uint64_t seed;
-    uint32_t iter, particle;
-    __device__ __forceinline__ void operator()(int c, double &r1, double &r2) const
-    {
-        kst_uniform2(seed, iter, particle, (uint32_t)c, 0, r1, r2);
-    }
-};
 // pso_update_velocity! (src/pso.jl:143-164) for ONE component: v = ((v + (p-x) r1 c1) + (g-x) r2 c2) chi.  Components
 // are independent of each other, so a caller may spread them over threads.
 __device__ __forceinline__ double kst_pso_velocity(double v, double x, double pb, double gb, double r1, double r2,
@@ -68,32 +60,6 @@ __device__ __forceinline__ double kst_pso_velocity(double v, double x, double pb
     v = __dadd_rn(v, diffp);
     v = __dadd_rn(v, diffg);
     return __dmul_rn(v, chi);
-}
-
-__device__ __forceinline__ void kst_pso_position(const int K, const int d, double *xw, double *xp, double *vw, double *vp,
-                                                 const int *fixw, const int *fixp, const double *lb, const double *ub);
-
-// pso_update_velocity! + pso_update_position! for one particle.  x, v are updated in place; p (personal best) and g
-// (global best) are read.  rnd(c, r1, r2) yields the two uniforms of component c (weights first, then atoms:
-// ap_rand!(v, lb, ub), src/designmeasure-abstractpoint.jl:136-144).  All pointers may be global or shared memory.
-template <class RND>
-__device__ __forceinline__ void kst_pso_move_particle(const int K, const int d, double *xw, double *xp, const double *pw,
-                                                      const double *pp, double *vw, double *vp, const double *gw,
-                                                      const double *gp, const int *fixw, const int *fixp,
-                                                      const double *lb, const double *ub, const double c1,
-                                                      const double c2, const double chi, RND rnd)
-{
-    // fresh r1, r2 per component
-    for (int c = 0; c < K * (d + 1); c++) {
-        double r1, r2;
-        rnd(c, r1, r2);
-        const double x = c < K ? xw[c] : xp[c - K];
-        const double pb = c < K ? pw[c] : pp[c - K];
-        const double gb = c < K ? gw[c] : gp[c - K];
-        double *v = c < K ? &vw[c] : &vp[c - K];
-        *v = kst_pso_velocity(*v, x, pb, gb, r1, r2, c1, c2, chi);
-    }
-    kst_pso_position(K, d, xw, xp, vw, vp, fixw, fixp, lb, ub);
 }
 
 // pso_update_position! (src/pso.jl:166-171) = ap_add!(x, v, constraints) for one particle whose velocity has been
@@ -187,8 +153,9 @@ __device__ __forceinline__ void kst_copy8(double *dst, const double *src, int n)
 // status (init only): 1 = fg == +Inf, 2 = all fx NaN.
 // partials != nullptr: the evaluation kernel's per-CTA partial sums are still unfinished; fx[i] is their fixed-order
 // sum plus `offset` (what k_obj_finish would have written), computed here to save a launch per iteration.
-// The pieces below are shared by the single-CTA form (kst_pso_best_cta: persistent swarm kernel, multi-GPU tail) and
-// the multi-CTA kernel k_pso_best (kst_pso.cu).
+// The pieces below are shared by k_pso_best (kst_pso.cu) and the multi-GPU tail k_pso_tail (kst_comm.cu), which run as
+// CTAs of 128 particles; the persistent swarm kernel (kst_pso_fused.cuh), where every CTA needs the whole result, has
+// its own copy of the update.
 
 // arg-max merge: the larger value, the lower index among equals; index -1 = no candidate
 __device__ __forceinline__ void kst_argmax_merge(double &va, int &ia, const double vb, const int ib)
@@ -308,35 +275,6 @@ __device__ __forceinline__ void kst_pso_best_finish(const KstPsoDev &s, const do
         }
     }
     __syncthreads();
-}
-
-// The whole update by ONE CTA of up to 1024 threads; ends with the CTA synchronised and g, fg, fp, p up to date.
-__device__ __forceinline__ void kst_pso_best_cta(const KstPsoDev &s, int init, double *tr_fx, double *tr_pts, double *tr_w,
-                                                 int slot, int *status, const double *__restrict__ partials,
-                                                 int n_blk, double offset, int nan_fill)
-{
-    __shared__ double s_val[32];
-    __shared__ int s_idx[32];
-    __shared__ int s_notnan;
-    const int tid = threadIdx.x;
-    // requested first, needed last: the best objective so far
-    double fg_old = -KST_DINF;
-    if (tid == 0 && !init) fg_old = *s.fg;
-    if (tid == 0) s_notnan = 0;
-    __syncthreads();
-    double best = -KST_DINF;
-    int bi = -1;
-    bool notnan = false;
-    for (int i = tid; i < s.S; i += blockDim.x) {
-        bool improved;
-        const double f = kst_pso_best_particle(s, i, init, partials, n_blk, offset, nan_fill, improved);
-        notnan = notnan || (f == f);
-        if (improved && (bi < 0 || f > best)) { best = f; bi = i; }
-    }
-    if (__any_sync(0xffffffffu, notnan) && (tid & 31) == 0) atomicOr(&s_notnan, 1);
-    kst_argmax_cta(best, bi, s_val, s_idx);   // one barrier inside: s_notnan is complete after it
-    __syncthreads();
-    kst_pso_best_finish(s, best, bi, fg_old, s_notnan, tr_fx, tr_pts, tr_w, slot, status);
 }
 
 // Scratch of the multi-CTA best update: one candidate per CTA and the arrival counter (zero between launches).
