@@ -357,6 +357,8 @@ class ProblemHandle:
 
     # -- measurement --------------------------------------------------------------------------
     def profile_enable(self, on=True):
+        """CUDA events around one stage's launches (kst_profile_enable): 1 / True = evaluation kernel, 2 = swarm move,
+        3 = best update (several GPUs: the tail kernel with the peer exchange), 0 / False = off."""
         check(lib().kst_profile_enable(self._h, int(on)))
 
     def profile_read(self):
