@@ -2,7 +2,7 @@
 //
 //   optimizer_state      src/pso.jl:83-125       -> k_pso_init + evaluation + k_pso_best(init)
 //   pso_update_velocity! src/pso.jl:143-164  \
-//   pso_update_position! src/pso.jl:166-171   >  -> k_pso_move (one thread per particle)
+//   pso_update_position! src/pso.jl:166-171   >  -> k_pso_move (a thread per component, then one per particle)
 //   ap_add!(p, v, c)     src/designmeasure-abstractpoint.jl:164-285 /
 //   pso_update_best!     src/pso.jl:181-193      -> k_pso_best (CTAs of 128 particles, order-independent arg-max merge)
 //
